@@ -1,0 +1,59 @@
+"""Top-k magnitude sparsification -- CPU/torch oracle and user-facing compressor.
+
+Semantics of ``src/Compresssor/TopK.py:5-35``: flatten, ``k = max(1, int(numel*ratio))``, keep the k
+largest |values| with their signs and flat indices; decompress scatters into zeros and restores
+the shape.  Ties at the threshold: the oracle keeps the lowest indices (deterministic); the CUDA
+kernel keeps an arbitrary subset of the tied elements of the same size, so dense results agree
+whenever the k-th magnitude is unique.
+"""
+from __future__ import annotations
+
+from typing import Tuple
+
+import torch
+
+from .base import Compressor
+
+
+def topk_count(numel: int, ratio: float) -> int:
+    return max(1, int(numel * ratio))
+
+
+def sparsify(tensor: torch.Tensor, compress_ratio: float) -> Tuple[torch.Tensor, torch.Tensor]:
+    flat = tensor.detach().reshape(-1)
+    k = topk_count(flat.numel(), compress_ratio)
+    mag = flat.abs()
+    # stable descending sort => ties broken by lowest index
+    order = torch.sort(mag, descending=True, stable=True).indices[:k]
+    order = torch.sort(order).values
+    return flat[order], order
+
+
+def desparsify(tensors, numel: int) -> torch.Tensor:
+    values, indices = tensors
+    out = torch.zeros(numel, dtype=values.dtype, device=values.device)
+    out[indices.long()] = values
+    return out
+
+
+class TopKCompressor(Compressor):
+    name = "topk"
+
+    def __init__(self, compress_ratio: float = 0.5):
+        self.compress_ratio = float(compress_ratio)
+
+    def compress(self, tensor: torch.Tensor):
+        values, indices = sparsify(tensor, self.compress_ratio)
+        return (values, indices.to(torch.int32)), (tensor.numel(), tensor.size())
+
+    def decompress(self, tensors, ctx):
+        numel, shape = ctx
+        return desparsify(tensors, numel).view(shape)
+
+    def payload_nbytes(self, tensors, ctx=None) -> int:
+        values, _ = tensors
+        k = values.numel()
+        numel = ctx[0] if ctx is not None else k
+        # index list (u16 tile-local) vs bitmap, whichever the wire format would pick
+        idx_bytes = 2 * k if k * 16 <= numel else (numel + 7) // 8
+        return idx_bytes + 4 * k

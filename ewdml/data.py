@@ -1,0 +1,234 @@
+"""Datasets and loaders.
+
+Capability parity with ``prepare_data`` (``PyTorch-parameter-server/src/util.py:20-106``): MNIST,
+Cifar10, Cifar100 and SVHN with the same normalisation constants and augmentation, when the real
+image blobs are on disk (``--data real``).  The build box has no datasets and no network, so the
+default (``--data auto``) falls back to a *learnable synthetic* set of the same shape: class
+conditional patterns plus noise from a fixed teacher, so "accuracy after N steps" is a meaningful
+number.
+
+Fixes relative to the reference: every worker gets its own shard
+(``shard_data``; the reference iterates the full set on every worker, see the commented stub at
+``distributed_worker.py:175-181``) and shuffling is seeded.
+
+The GPU path does not use a Python ``DataLoader`` at all: :class:`DeviceFeeder` keeps the (small)
+dataset in pinned host memory and issues one ``cudaMemcpyAsync`` per batch on a copy stream, one
+step ahead of compute.
+"""
+from __future__ import annotations
+
+import math
+import os
+from dataclasses import dataclass
+from typing import Iterator, Optional, Tuple
+
+import torch
+
+# (channels, height, width, classes, mean, std)
+_SHAPES = {
+    "MNIST": (1, 28, 28, 10, (0.1307,), (0.3081,)),
+    "Cifar10": (3, 32, 32, 10, tuple(x / 255.0 for x in (125.3, 123.0, 113.9)),
+                tuple(x / 255.0 for x in (63.0, 62.1, 66.7))),
+    "Cifar100": (3, 32, 32, 100, tuple(x / 255.0 for x in (125.3, 123.0, 113.9)),
+                 tuple(x / 255.0 for x in (63.0, 62.1, 66.7))),
+    "SVHN": (3, 32, 32, 10, (0.4914, 0.4822, 0.4465), (0.2023, 0.1994, 0.2010)),
+}
+
+
+def dataset_shape(name: str) -> Tuple[int, int, int, int]:
+    c, h, w, k = _SHAPES[name][:4]
+    return c, h, w, k
+
+
+class SyntheticImageDataset(torch.utils.data.Dataset):
+    """Class-conditional patterns + Gaussian noise, already normalised.
+
+    ``x = pattern[y] * signal + noise`` with one fixed low-frequency random pattern per class.
+    A linear probe reaches ~100 % on it, a randomly initialised CNN starts at chance, so
+    convergence differences between compressors show up within tens of steps.
+    """
+
+    def __init__(self, name: str, n: int, train: bool = True, seed: int = 1234,
+                 signal: float = 0.6) -> None:
+        c, h, w, k = dataset_shape(name)
+        g = torch.Generator().manual_seed(seed)
+        # low-frequency class templates (upsampled 7x7 / 8x8 random fields)
+        base = torch.randn(k, c, max(1, h // 4), max(1, w // 4), generator=g)
+        templ = torch.nn.functional.interpolate(base, size=(h, w), mode="bilinear",
+                                                align_corners=False)
+        g2 = torch.Generator().manual_seed(seed + (1 if train else 2))
+        self.targets = torch.randint(0, k, (n,), generator=g2)
+        noise = torch.randn(n, c, h, w, generator=g2)
+        self.data = (templ[self.targets] * signal + noise).contiguous()
+        self.num_classes = k
+
+    def __len__(self) -> int:
+        return self.data.shape[0]
+
+    def __getitem__(self, i: int):
+        return self.data[i], self.targets[i]
+
+
+def _real_datasets(cfg):
+    """torchvision datasets with the reference's transforms (util.py:22-104)."""
+    from torchvision import datasets, transforms
+    import torch.nn.functional as F
+
+    name = cfg.dataset
+    _, _, _, _, mean, std = _SHAPES[name]
+    norm = transforms.Normalize(mean, std)
+    root = cfg.data_root
+    if name == "MNIST":
+        tf = transforms.Compose([transforms.ToTensor(), norm])
+        return (datasets.MNIST(os.path.join(root, "mnist_data"), train=True, download=False, transform=tf),
+                datasets.MNIST(os.path.join(root, "mnist_data"), train=False, download=False, transform=tf))
+    if name in ("Cifar10", "Cifar100"):
+        reflect = transforms.Lambda(
+            lambda x: F.pad(x.unsqueeze(0), (4, 4, 4, 4), mode="reflect").squeeze(0))
+        tf_train = transforms.Compose([transforms.ToTensor(), reflect, transforms.ToPILImage(),
+                                       transforms.RandomCrop(32), transforms.RandomHorizontalFlip(),
+                                       transforms.ToTensor(), norm])
+        tf_test = transforms.Compose([transforms.ToTensor(), norm])
+        cls = datasets.CIFAR10 if name == "Cifar10" else datasets.CIFAR100
+        sub = "cifar10_data" if name == "Cifar10" else "cifar100_data"
+        return (cls(os.path.join(root, sub), train=True, download=False, transform=tf_train),
+                cls(os.path.join(root, sub), train=False, download=False, transform=tf_test))
+    if name == "SVHN":
+        tf_train = transforms.Compose([transforms.RandomCrop(32, padding=4),
+                                       transforms.RandomHorizontalFlip(), transforms.ToTensor(), norm])
+        tf_test = transforms.Compose([transforms.ToTensor(), norm])
+        return (datasets.SVHN(os.path.join(root, "svhn_data"), split="train", download=False, transform=tf_train),
+                datasets.SVHN(os.path.join(root, "svhn_data"), split="test", download=False, transform=tf_test))
+    raise ValueError(name)
+
+
+def build_datasets(cfg):
+    """Return (train_set, test_set); synthetic unless real blobs are present/forced."""
+    if cfg.data in ("real", "auto"):
+        try:
+            return _real_datasets(cfg)
+        except Exception:
+            if cfg.data == "real":
+                raise
+    n_train = cfg.synthetic_size
+    return (SyntheticImageDataset(cfg.dataset, n_train, train=True, seed=1234),
+            SyntheticImageDataset(cfg.dataset, max(cfg.test_batch_size, n_train // 4), train=False,
+                                  seed=1234))
+
+
+def prepare_data(cfg, shard_rank: int = 0, num_shards: int = 1):
+    """(train_loader, test_loader) — the ``prepare_data(args)`` entry point of util.py:20.
+
+    ``shard_rank``/``num_shards`` select this worker's partition (DistributedSampler semantics,
+    as in ``horvod_pytorch.py:154-157``); pass 0/1 for the reference's unsharded behaviour.
+    """
+    train_set, test_set = build_datasets(cfg)
+    gen = torch.Generator().manual_seed(cfg.seed)
+    sampler = None
+    if num_shards > 1 and cfg.shard_data:
+        sampler = torch.utils.data.distributed.DistributedSampler(
+            train_set, num_replicas=num_shards, rank=shard_rank, shuffle=True, seed=cfg.seed)
+    train_loader = torch.utils.data.DataLoader(
+        train_set, batch_size=cfg.batch_size, shuffle=(sampler is None), sampler=sampler,
+        generator=gen, drop_last=True)
+    test_loader = torch.utils.data.DataLoader(test_set, batch_size=cfg.test_batch_size, shuffle=False)
+    return train_loader, test_loader
+
+
+@dataclass
+class _Slot:
+    x: torch.Tensor
+    y: torch.Tensor
+    ev: "torch.cuda.Event"
+
+
+class DeviceFeeder:
+    """Pinned-host -> device batch pipeline for the GPU path (double-buffered, copy stream).
+
+    Holds the whole (sharded) dataset in pinned memory; every ``next()`` enqueues the H2D copy of
+    the *following* batch on a side stream and returns the batch copied one call earlier, so the
+    copy overlaps the previous step's compute.  ``h2d_bytes_per_step`` is what bench.py reports.
+    """
+
+    def __init__(self, data: torch.Tensor, targets: torch.Tensor, batch_size: int,
+                 device: torch.device, dtype: torch.dtype = torch.float32,
+                 channels_last: bool = True, seed: int = 1, shard_rank: int = 0,
+                 num_shards: int = 1) -> None:
+        n = data.shape[0]
+        idx = torch.arange(shard_rank, n, num_shards)
+        self.data = data[idx].to(dtype).contiguous()
+        self.targets = targets[idx].to(torch.int64).contiguous()
+        if channels_last and self.data.dim() == 4:
+            self.data = self.data.contiguous(memory_format=torch.channels_last)
+        if device.type == "cuda":
+            self.data = self.data.pin_memory()
+            self.targets = self.targets.pin_memory()
+        self.n = self.data.shape[0]
+        self.bs = batch_size
+        self.device = device
+        self.gen = torch.Generator().manual_seed(seed + 7919 * shard_rank)
+        self.steps_per_epoch = max(1, self.n // batch_size)
+        self._pos = 0
+        self._perm = torch.randperm(self.n, generator=self.gen)
+        self.h2d_bytes_per_step = batch_size * (self.data[0].numel() * self.data.element_size()
+                                                + self.targets.element_size())
+        self._cuda = device.type == "cuda"
+        if self._cuda:
+            self._stream = torch.cuda.Stream(device=device)
+            # staging buffers (pinned) so a shuffled batch is one contiguous copy
+            shape = (batch_size,) + tuple(self.data.shape[1:])
+            mf = torch.channels_last if (channels_last and self.data.dim() == 4) else torch.contiguous_format
+            self._hx = [torch.empty(shape, dtype=dtype).contiguous(memory_format=mf).pin_memory() for _ in range(2)]
+            self._hy = [torch.empty(batch_size, dtype=torch.int64).pin_memory() for _ in range(2)]
+            self._dx = [torch.empty(shape, dtype=dtype, device=device).contiguous(memory_format=mf) for _ in range(2)]
+            self._dy = [torch.empty(batch_size, dtype=torch.int64, device=device) for _ in range(2)]
+            self._ev = [torch.cuda.Event() for _ in range(2)]
+            self._consumed = [None, None]
+            self._k = 0
+            self._prefetch()
+
+    def _next_indices(self) -> torch.Tensor:
+        if self._pos + self.bs > self.n:
+            self._perm = torch.randperm(self.n, generator=self.gen)
+            self._pos = 0
+        sel = self._perm[self._pos:self._pos + self.bs]
+        self._pos += self.bs
+        return sel
+
+    def _prefetch(self) -> None:
+        k = self._k
+        sel = self._next_indices()
+        if self._consumed[k] is not None:
+            # the device buffer may still be read by the step that consumed it
+            self._stream.wait_event(self._consumed[k])
+        torch.index_select(self.data, 0, sel, out=self._hx[k])
+        torch.index_select(self.targets, 0, sel, out=self._hy[k])
+        with torch.cuda.stream(self._stream):
+            self._dx[k].copy_(self._hx[k], non_blocking=True)
+            self._dy[k].copy_(self._hy[k], non_blocking=True)
+            self._ev[k].record(self._stream)
+
+    def next(self) -> Tuple[torch.Tensor, torch.Tensor]:
+        if not self._cuda:
+            sel = self._next_indices()
+            return self.data[sel], self.targets[sel]
+        k = self._k
+        torch.cuda.current_stream(self.device).wait_event(self._ev[k])
+        x, y = self._dx[k], self._dy[k]
+        self._k ^= 1
+        # the host staging buffer k^1 was consumed by the copy issued two calls ago
+        self._ev[self._k].synchronize()
+        self._prefetch()
+        return x, y
+
+    def mark_consumed(self) -> None:
+        """Record that the batch returned by the previous next() has been consumed."""
+        if self._cuda:
+            k = self._k ^ 1
+            ev = torch.cuda.Event()
+            ev.record(torch.cuda.current_stream(self.device))
+            self._consumed[k] = ev
+
+    def __iter__(self) -> Iterator[Tuple[torch.Tensor, torch.Tensor]]:
+        for _ in range(self.steps_per_epoch):
+            yield self.next()

@@ -1,0 +1,100 @@
+"""Layer modules used by every model in :mod:`ewdml.models`.
+
+They subclass the ``torch.nn`` modules of the same name, so parameter names, shapes and
+``state_dict`` keys are those of the reference models (``src/model_ops/*.py``) and checkpoints
+load both ways.  What differs is *execution*: when a module's ``compute`` is ``"native"`` and the
+input lives on a CUDA device, forward/backward run the hand-written sm_100a kernels in
+:mod:`ewdml.ops.native` (tcgen05 GEMM, implicit-GEMM convolution, fused BatchNorm/ReLU, pooling);
+otherwise they defer to torch (CPU plumbing path and the eager baseline).
+"""
+from __future__ import annotations
+
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+_COMPUTE = {"mode": "torch"}
+
+
+def set_compute(mode: str) -> None:
+    """Select ``"torch"`` or ``"native"`` execution for all ewdml layers (process-wide)."""
+    if mode not in ("torch", "native"):
+        raise ValueError(mode)
+    _COMPUTE["mode"] = mode
+
+
+def get_compute() -> str:
+    return _COMPUTE["mode"]
+
+
+def _native(x: torch.Tensor) -> bool:
+    return _COMPUTE["mode"] == "native" and x.is_cuda
+
+
+class Conv2d(nn.Conv2d):
+    def forward(self, x):
+        if _native(x):
+            from . import native
+            return native.conv2d(x, self.weight, self.bias, self.stride, self.padding)
+        return super().forward(x)
+
+
+class Linear(nn.Linear):
+    def forward(self, x):
+        if _native(x):
+            from . import native
+            return native.linear(x, self.weight, self.bias)
+        return super().forward(x)
+
+
+class BatchNorm2d(nn.BatchNorm2d):
+    def forward(self, x, relu: bool = False, residual=None):
+        """BatchNorm with optional fused residual-add and ReLU (``y = relu(bn(x) + residual)``)."""
+        if _native(x):
+            from . import native
+            return native.batch_norm(self, x, relu=relu, residual=residual)
+        y = super().forward(x)
+        if residual is not None:
+            y = y + residual
+        return F.relu(y) if relu else y
+
+
+class ReLU(nn.ReLU):
+    def forward(self, x):
+        if _native(x):
+            from . import native
+            return native.relu(x)
+        return super().forward(x)
+
+
+class MaxPool2d(nn.MaxPool2d):
+    def forward(self, x, relu: bool = False):
+        if _native(x):
+            from . import native
+            return native.max_pool2x2(x, relu=relu)
+        y = super().forward(x)
+        return F.relu(y) if relu else y
+
+
+class AvgPool2d(nn.AvgPool2d):
+    def forward(self, x):
+        if _native(x):
+            from . import native
+            return native.avg_pool(x, self.kernel_size)
+        return super().forward(x)
+
+
+class Dropout(nn.Dropout):
+    def forward(self, x):
+        if _native(x) and self.training and self.p > 0:
+            from . import native
+            return native.dropout(x, self.p)
+        return super().forward(x)
+
+
+def cross_entropy(logits: torch.Tensor, target: torch.Tensor) -> torch.Tensor:
+    """Mean softmax cross-entropy (``nn.CrossEntropyLoss`` at ``distributed_worker.py:103``)."""
+    if _native(logits):
+        from . import native
+        return native.cross_entropy(logits, target)
+    return F.cross_entropy(logits.float(), target)

@@ -1,0 +1,9 @@
+from .sgd import SGD
+from .adam import Adam
+
+
+def build_optimizer(cfg, params):
+    if cfg.optimizer == "adam":
+        return Adam(params, lr=cfg.lr, weight_decay=cfg.weight_decay)
+    return SGD(params, lr=cfg.lr, momentum=cfg.momentum, weight_decay=cfg.weight_decay,
+               nesterov=cfg.nesterov)

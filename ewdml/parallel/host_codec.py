@@ -1,0 +1,171 @@
+"""Host-side (torch, CPU or any device) codec for whole-model gradient messages.
+
+Used by the gloo plumbing path (BASELINE.json config 1) and as the oracle for the CUDA exchange
+kernels.  It turns the flat gradient buffer of a :class:`~ewdml.parallel.flat.FlatModel` into ONE
+fixed-size byte message per step (the reference sends one blocking collective per parameter
+tensor per direction, ``distributed_worker.py:350`` / ``sync_replicas_master_nn.py:212,223``), with
+per-tensor compressor semantics kept through the segment table:
+
+=========== ==================================================================================
+compressor  per-segment message
+=========== ==================================================================================
+none        ``numel`` fp32
+qsgd        norm fp32 + ``numel`` packed signed levels            (``qsgd.py:12-32``)
+topk        ``k`` fp32 values + ``k`` int32 indices               (``TopK.py:5-10``)
+topk-qsgd   norm fp32 + ``k`` packed signed levels + ``k`` int32  (``qsgd.py:14-15`` enabled)
+=========== ==================================================================================
+
+Signed levels in ``[-s, s]`` are stored as int8 when ``s <= 127``, as uint8 magnitude plus a
+bit-packed sign plane when ``s <= 255`` (the reference default s = 128), else int16.
+"""
+from __future__ import annotations
+
+from typing import List, Optional, Tuple
+
+import numpy as np
+import torch
+
+from ..compress.qsgd import qsgd_dequantize, qsgd_quantize
+from ..compress.rng import uniform_for_indices
+from ..compress.topk import sparsify, topk_count
+from .flat import Segment
+
+
+def _r4(x: int) -> int:
+    return (x + 3) // 4 * 4
+
+
+def _levels_nbytes(n: int, s: int) -> int:
+    """Bytes of the packed level block, rounded up to 4 so later fields stay 4-byte aligned."""
+    if s <= 127:
+        return _r4(n)
+    if s <= 255:
+        return _r4(n + (n + 7) // 8)
+    return _r4(2 * n)
+
+
+def _pack_levels(q: torch.Tensor, s: int) -> torch.Tensor:
+    q = q.detach().cpu()
+    n = q.numel()
+    if s <= 127:
+        raw = q.to(torch.int8).view(torch.uint8)
+    elif s <= 255:
+        mag = q.abs().to(torch.uint8)
+        signs = torch.from_numpy(np.packbits((q < 0).numpy().astype(np.uint8), bitorder="little"))
+        raw = torch.cat([mag, signs])
+    else:
+        raw = q.to(torch.int16).view(torch.uint8)
+    out = torch.zeros(_levels_nbytes(n, s), dtype=torch.uint8)
+    out[:raw.numel()] = raw
+    return out
+
+
+def _unpack_levels(buf: torch.Tensor, n: int, s: int) -> torch.Tensor:
+    if s <= 127:
+        return buf[:n].view(torch.int8).to(torch.float32)
+    if s <= 255:
+        mag = buf[:n].to(torch.float32)
+        bits = np.unpackbits(buf[n:n + (n + 7) // 8].numpy(), bitorder="little")[:n]
+        return mag * (1.0 - 2.0 * torch.from_numpy(bits.astype(np.float32)))
+    return buf[:2 * n].clone().view(torch.int16).to(torch.float32)
+
+
+class HostCodec:
+    """Encode/decode a flat gradient vector <-> one uint8 message."""
+
+    def __init__(self, segments: List[Segment], compressor: str, qsgd_levels: int = 128,
+                 topk_ratio: float = 0.5, seed: int = 0, rank: int = 0):
+        self.segments = segments
+        self.compressor = compressor
+        self.s = int(qsgd_levels)
+        self.ratio = float(topk_ratio)
+        self.seed = seed
+        self.rank = rank
+        self.sizes = [self._seg_nbytes(seg) for seg in segments]
+        self.offsets = np.concatenate([[0], np.cumsum(self.sizes)]).astype(np.int64)
+        self.nbytes = int(self.offsets[-1])
+        self.dense_nbytes = 4 * sum(seg.numel for seg in segments)
+
+    def _k(self, seg: Segment) -> int:
+        return topk_count(seg.numel, self.ratio)
+
+    def _seg_nbytes(self, seg: Segment) -> int:
+        n = seg.numel
+        c = self.compressor
+        if c == "none":
+            return 4 * n
+        if c == "qsgd":
+            return 4 + _levels_nbytes(n, self.s)
+        if c == "topk":
+            return 8 * self._k(seg)
+        if c == "topk-qsgd":
+            k = self._k(seg)
+            return 4 + _levels_nbytes(k, self.s) + 4 * k
+        raise ValueError(c)
+
+    # stream id separates the draws of different senders (rank) so workers are independent
+    def _uniform(self, idx: torch.Tensor, step: int) -> torch.Tensor:
+        return uniform_for_indices(idx, self.seed, step, stream=self.rank)
+
+    def encode(self, flat: torch.Tensor, step: int = 0, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+        flat = flat.detach().cpu()
+        msg = out if out is not None else torch.empty(self.nbytes, dtype=torch.uint8)
+        for i, seg in enumerate(self.segments):
+            g = flat[seg.offset:seg.offset + seg.numel]
+            dst = msg[int(self.offsets[i]):int(self.offsets[i + 1])]
+            c = self.compressor
+            if c == "none":
+                dst.copy_(g.contiguous().view(torch.uint8))
+            elif c == "qsgd":
+                idx = torch.arange(seg.offset, seg.offset + seg.numel)
+                q, norm = qsgd_quantize(g, self.s, self._uniform(idx, step))
+                dst[:4].copy_(norm.view(torch.uint8))
+                dst[4:].copy_(_pack_levels(q, self.s))
+            elif c == "topk":
+                vals, idx = sparsify(g, self.ratio)
+                k = vals.numel()
+                dst[:4 * k].copy_(vals.contiguous().view(torch.uint8))
+                dst[4 * k:].copy_(idx.to(torch.int32).view(torch.uint8))
+            else:  # topk-qsgd
+                vals, idx = sparsify(g, self.ratio)
+                k = vals.numel()
+                q, norm = qsgd_quantize(vals, self.s, self._uniform(idx + seg.offset, step))
+                lb = _levels_nbytes(k, self.s)
+                dst[:4].copy_(norm.view(torch.uint8))
+                dst[4:4 + lb].copy_(_pack_levels(q, self.s))
+                dst[4 + lb:].copy_(idx.to(torch.int32).view(torch.uint8))
+        return msg
+
+    def decode(self, msg: torch.Tensor, out: Optional[torch.Tensor] = None, accumulate: bool = False,
+               total: Optional[int] = None) -> torch.Tensor:
+        """Dense flat fp32 vector (segment layout of the FlatModel)."""
+        if total is None:
+            last = self.segments[-1]
+            total = last.offset + last.numel
+        dense = out if out is not None else torch.zeros(total, dtype=torch.float32)
+        if out is not None and not accumulate:
+            dense.zero_()
+        msg = msg.cpu()
+        for i, seg in enumerate(self.segments):
+            src = msg[int(self.offsets[i]):int(self.offsets[i + 1])]
+            tgt = dense[seg.offset:seg.offset + seg.numel]
+            c = self.compressor
+            if c == "none":
+                tgt.add_(src.view(torch.float32))
+            elif c == "qsgd":
+                norm = src[:4].view(torch.float32)
+                q = _unpack_levels(src[4:], seg.numel, self.s)
+                tgt.add_(qsgd_dequantize(q, norm, self.s))
+            elif c == "topk":
+                k = self._k(seg)
+                vals = src[:4 * k].view(torch.float32)
+                idx = src[4 * k:].view(torch.int32).long()
+                tgt.index_add_(0, idx, vals)
+            else:
+                k = self._k(seg)
+                lb = _levels_nbytes(k, self.s)
+                norm = src[:4].view(torch.float32)
+                q = _unpack_levels(src[4:4 + lb], k, self.s)
+                idx = src[4 + lb:].view(torch.int32).long()
+                tgt.index_add_(0, idx, qsgd_dequantize(q, norm, self.s))
+        return dense

@@ -1,0 +1,47 @@
+"""Flag surface (distributed_nn.py:30-70) and the env-override registry."""
+import pytest
+
+from ewdml.config import TrainConfig, parse_args, registry, Registry
+
+
+def test_reference_flag_surface_and_defaults():
+    c = parse_args([])
+    assert (c.batch_size, c.test_batch_size, c.epochs, c.max_steps) == (128, 500, 100, 10000)
+    assert (c.lr, c.momentum, c.seed, c.log_interval) == (0.01, 0.5, 1, 10)
+    assert (c.network, c.dataset, c.mode, c.comm_type) == ("LeNet", "MNIST", "normal", "Bcast")
+    assert (c.num_aggregate, c.eval_freq, c.train_dir) == (5, 50, "output/models/")
+    assert (c.compress_grad, c.gather_type, c.kill_threshold) == ("compress", "gather", 7.0)
+
+
+def test_reference_script_command_line_parses():
+    # flags of src/run_pytorch_single.sh:4-17, including the empty --enable-gpu=
+    c = parse_args(["--lr=0.01", "--momentum=0.9", "--max-steps=10000", "--epochs=10", "--network=LeNet",
+                    "--dataset=MNIST", "--batch-size=64", "--comm-type=Bcast", "--num-aggregate=5",
+                    "--mode=normal", "--eval-freq=20", "--gather-type=gather", "--compress-grad=compress",
+                    "--enable-gpu=", "--train-dir=/tmp/x/", "--local_rank=0"])
+    assert c.enable_gpu is False and c.batch_size == 64 and c.local_rank == 0
+    assert parse_args(["--enable-gpu=1"]).enable_gpu is True
+    assert parse_args(["--enable-gpu"]).enable_gpu is True
+
+
+def test_methods_resolve():
+    assert parse_args(["--method", "1"]).resolved_compressor() == "none"
+    assert parse_args(["--method", "1"]).resolved_pull() == "weights"
+    m4 = parse_args(["--method", "4"])
+    assert m4.resolved_compressor() == "qsgd" and m4.resolved_compress_pull() and m4.resolved_pull() == "grads"
+    m6 = parse_args(["--method", "6"])
+    assert m6.resolved_compressor() == "topk-qsgd" and m6.resolved_sync_period() == 20
+    assert parse_args(["--compress-grad", "none"]).resolved_compressor() == "none"
+    with pytest.raises(ValueError):
+        TrainConfig(network="AlexNet").validate()
+
+
+def test_env_override_precedence(monkeypatch):
+    monkeypatch.setenv("EWDML_QSGD_LEVELS", "64")
+    assert parse_args([]).qsgd_levels == 64
+    assert parse_args(["--qsgd-levels", "16"]).qsgd_levels == 16      # CLI beats env
+    monkeypatch.setenv("EWDML_MY_TUNABLE", "7")
+    r = Registry()
+    assert r.register("my_tunable", 3, "x") == 7 and r.dump()["my_tunable"]["source"] == "env"
+    r.set("my_tunable", "9"); assert r.get("my_tunable") == 9
+    assert "select_tile" in registry.dump()

@@ -1,0 +1,110 @@
+"""World-size 2/3 gloo/CPU plumbing tests of the PS loop and the other exchange strategies
+(BASELINE.json config 1; SURVEY.md section 4 implication (b))."""
+import json
+import os
+import socket
+import subprocess
+import sys
+
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from ewdml.config import TrainConfig
+from ewdml.data import build_datasets, prepare_data
+from ewdml.train.roles import DistributedWorker, SyncReplicasMaster_NN, planned_steps
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _free_port():
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); p = s.getsockname()[1]; s.close(); return p
+
+
+def _run(rank, world, port, cfg_kwargs, out_dir):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    torch.set_num_threads(1)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    cfg = TrainConfig(**cfg_kwargs).validate()
+    ps = cfg.exchange == "ps"
+    nw = world - 1 if ps else world
+    train_set, _ = build_datasets(cfg)
+    total = planned_steps(cfg, len(train_set), nw)
+    if ps and rank == 0:
+        m = SyncReplicasMaster_NN(cfg, world).build_model(cfg.num_classes())
+        stats = m.start(total_steps=total)
+        res = {"role": "server", "steps": len(stats), "bytes_recv": [s.bytes_recv for s in stats]}
+    else:
+        loader, test_loader = prepare_data(cfg, shard_rank=(rank - 1 if ps else rank), num_shards=nw)
+        w = DistributedWorker(cfg, rank, world).build_model(cfg.num_classes())
+        hist = w.train(loader, test_loader, total_steps=total)
+        res = {"role": "worker", "loss": [h["loss"] for h in hist],
+               "bytes_sent": [h["bytes_sent"] for h in hist],
+               "checksum": float(w.flat.param.double().sum()), "dense": w.flat.dense_nbytes(),
+               "codec_bytes": getattr(getattr(w.exchange, "push", None), "nbytes", None)}
+    with open(os.path.join(out_dir, f"r{rank}.json"), "w") as f:
+        json.dump(res, f)
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def _launch(world, tmp_path, **kw):
+    base = dict(network="LeNet", dataset="MNIST", batch_size=16, max_steps=8, epochs=2, lr=0.02,
+                momentum=0.9, synthetic_size=256, data="synthetic", eval_freq=4,
+                train_dir=str(tmp_path) + "/", log_interval=100)
+    base.update(kw)
+    mp.spawn(_run, args=(world, _free_port(), base, str(tmp_path)), nprocs=world, join=True)
+    return [json.load(open(os.path.join(str(tmp_path), f"r{r}.json"))) for r in range(world)]
+
+
+@pytest.mark.parametrize("method", [1, 2, 3, 4, 5, 6])
+def test_ps_all_six_methods(tmp_path, method):
+    extra = dict(topk_ratio=0.4) if method >= 5 else {}
+    if method == 6:
+        extra["sync_period"] = 4
+    res = _launch(3, tmp_path, method=method, **extra)
+    server, w1, w2 = res
+    assert server["role"] == "server" and server["steps"] == 8
+    for w in (w1, w2):
+        assert len(w["loss"]) == 8 and all(l == l for l in w["loss"])       # no NaNs
+    if method != 6:
+        # synchronous methods keep the replicas identical
+        assert w1["checksum"] == pytest.approx(w2["checksum"], rel=1e-9)
+        assert all(b == w1["codec_bytes"] for b in w1["bytes_sent"])
+    else:
+        assert [b > 0 for b in w1["bytes_sent"]] == [True, False, False, False] * 2
+    dense = w1["dense"]
+    ratio = dense / max(w1["bytes_sent"])
+    if method in (1, 3):
+        assert ratio == pytest.approx(1.0)
+    elif method in (2, 4):
+        assert ratio > 3.5            # ~1.125 B/elem at s=128 on the host codec
+    else:
+        assert ratio > 1.5
+    assert os.path.isfile(os.path.join(str(tmp_path), "model_step_"))
+
+
+def test_ps_world_size_2_loss_decreases(tmp_path):
+    res = _launch(2, tmp_path, method=3, max_steps=30, epochs=4, synthetic_size=512, batch_size=32, lr=0.05)
+    losses = res[1]["loss"]
+    assert sum(losses[-5:]) / 5 < sum(losses[:5]) / 5 - 0.1
+
+
+@pytest.mark.parametrize("exchange,compressor", [("allgather", "topk-qsgd"), ("allgather", "qsgd"),
+                                                 ("allgather", "topk"), ("allreduce", "none")])
+def test_serverless_exchanges(tmp_path, exchange, compressor):
+    res = _launch(2, tmp_path, exchange=exchange, compressor=compressor, topk_ratio=0.1)
+    assert res[0]["checksum"] == pytest.approx(res[1]["checksum"], rel=1e-9)
+    assert len(res[0]["loss"]) == 8
+
+
+def test_cli_entrypoint_under_torchrun(tmp_path):
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
+           "--master-addr", "127.0.0.1", "--master-port", str(_free_port()),
+           os.path.join(ROOT, "distributed_nn.py"), "--network=LeNet", "--dataset=MNIST", "--batch-size=16",
+           "--max-steps=3", "--epochs=1", "--method=5", "--topk-ratio=0.4", "--synthetic-size=128",
+           "--data=synthetic", "--enable-gpu=", f"--train-dir={tmp_path}/"]
+    out = subprocess.run(cmd, capture_output=True, text=True, timeout=240, cwd=ROOT)
+    assert out.returncode == 0, out.stderr[-2000:]
+    assert "I am the master" in out.stdout and "I am worker: 1 in all 1 workers" in out.stdout
