@@ -1,0 +1,256 @@
+#!/usr/bin/env python
+"""Headline benchmark: images/s of one compressed-gradient data-parallel training step.
+
+    python bench.py --gpus N --steps K --warmup W            # this framework
+    python bench.py --impl reference --gpus N ...             # the unmodified reference (baseline/_ref)
+
+Config (BASELINE.json config 2): VGG-11 (BatchNorm variant, the reference's "VGG11") on synthetic
+CIFAR-10-shaped data, random-init weights, per-GPU batch 128 (the reference entry point's default
+``--batch-size``), top-k 1 % + QSGD (s = 128) sparse allgather, bf16 compute over fp32 master weights,
+weak scaling.  One process per GPU; for N > 1 the driver launches this file under
+``torch.distributed.run``.
+
+Two timed regions, both W warm-up steps then exactly K steps between barrier + synchronize:
+``value`` uses a device-resident batch (CUDA events, max over ranks); ``e2e`` goes through the
+public API with, every step, the pinned-host -> device copy of that step's batch and a device ->
+host read of the loss.  A 256 MiB buffer is overwritten every step inside the timed region to
+flush L2.  ``gpu_launches`` counts the launches of this repo's own kernels (libewdml.so) inside
+the first timed region.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+REFERENCE_CPU_IMG_S_PER_WORKER = 104.0     # derived VGG11 M1 throughput of the reference (CPU)
+
+
+def parse():
+    p = argparse.ArgumentParser()
+    p.add_argument("--gpus", type=int, default=1)
+    p.add_argument("--steps", type=int, default=30)
+    p.add_argument("--warmup", type=int, default=5)
+    p.add_argument("--impl", type=str, default="ewdml", choices=["ewdml", "reference", "nccl"])
+    p.add_argument("--model", type=str, default="VGG11")
+    p.add_argument("--batch-size", type=int, default=128, help="per-GPU batch")
+    p.add_argument("--compressor", type=str, default="topk-qsgd")
+    p.add_argument("--topk-ratio", type=float, default=0.01)
+    p.add_argument("--qsgd-levels", type=int, default=128)
+    p.add_argument("--exchange", type=str, default="allgather", choices=["allgather", "allreduce", "ps"])
+    p.add_argument("--compute", type=str, default=os.environ.get("EWDML_BENCH_COMPUTE", "torch"),
+                   choices=["torch", "native"])
+    p.add_argument("--dtype", type=str, default="bf16")
+    p.add_argument("--no-e2e", action="store_true")
+    p.add_argument("--no-flush", action="store_true")
+    return p.parse_args()
+
+
+class ClockSampler:
+    """nvidia-smi sampler running during the timed region (B200_PROFILING.md clocks line)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int):
+        self.gpu_index, self.proc, self.path = gpu_index, None, f"/tmp/ewdml_clocks_{os.getpid()}.csv"
+
+    def start(self):
+        try:
+            self.f = open(self.path, "w")
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "100", "-i", str(self.gpu_index)], stdout=self.f,
+                                         stderr=subprocess.DEVNULL)
+        except Exception:
+            self.proc = None
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        if self.proc is None:
+            return out
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        self.f.close()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        try:
+            for line in open(self.path):
+                parts = [x.strip() for x in line.split(",")]
+                if len(parts) < 9:
+                    continue
+                try:
+                    sm.append(float(parts[1])); mx.append(float(parts[2]))
+                except ValueError:
+                    continue
+                for nm, v in zip(names, parts[5:9]):
+                    if v.lower().startswith("active"):
+                        reasons.add(nm)
+            os.remove(self.path)
+        except Exception:
+            pass
+        if sm:
+            out.update(sm_mhz=statistics.median(sm), sm_max_mhz=max(mx), reasons=sorted(reasons), samples=len(sm))
+        return out
+
+
+def run_ewdml(a):
+    import torch
+    import torch.distributed as dist
+    from ewdml.config import TrainConfig
+    from ewdml.data import DeviceFeeder, SyntheticImageDataset
+    from ewdml.parallel.peer import PeerGroup
+    from ewdml.runtime import lib as L
+    from ewdml.train.gpu import GpuTrainer
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != a.gpus:
+        if world == 1 and a.gpus > 1:
+            raise SystemExit("launch with: python -m torch.distributed.run --nproc-per-node N bench.py --gpus N ...")
+    device = torch.device("cuda", local_rank)
+    torch.cuda.set_device(device)
+    if world > 1:
+        dist.init_process_group("nccl", rank=rank, world_size=world, device_id=device)
+
+    dataset = "MNIST" if a.model.lower() in ("lenet", "mnistnet") else "Cifar10"
+    cfg = TrainConfig(network=a.model, dataset=dataset, batch_size=a.batch_size, lr=0.01, momentum=0.9,
+                      compressor=a.compressor, topk_ratio=a.topk_ratio, qsgd_levels=a.qsgd_levels,
+                      exchange=a.exchange, dtype=a.dtype, compute=a.compute, enable_gpu=True, seed=1).validate()
+    pg = PeerGroup.from_env(device)
+    role = "server" if (a.exchange == "ps" and rank == 0) else "worker"
+    tr = GpuTrainer(cfg, device, pg, role=role)
+    n_workers = world - 1 if a.exchange == "ps" else world
+
+    ds = SyntheticImageDataset(dataset, 4096, train=True, seed=1234)
+    feeder = DeviceFeeder(ds.data, ds.targets, a.batch_size, device, dtype=torch.float32, channels_last=True,
+                          seed=1, shard_rank=rank, num_shards=world)
+    flush = None if a.no_flush else torch.empty(256 << 20, dtype=torch.uint8, device=device)
+    x0, y0 = feeder.next()
+    x0, y0 = x0.clone(), y0.clone()
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def one_step(x, y):
+        if flush is not None:
+            flush.zero_()
+        if role == "server":
+            tr.server_step()
+            return None
+        loss, _ = tr.step(x, y)
+        return loss
+
+    def timed(nsteps, e2e):
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        host_loss = torch.zeros(1, dtype=torch.float32).pin_memory()
+        barrier()
+        t0 = time.perf_counter()
+        ev0.record()
+        last = None
+        for _ in range(nsteps):
+            if e2e:
+                x, y = feeder.next()
+                loss = one_step(x, y)
+                feeder.mark_consumed()
+                if loss is not None:
+                    host_loss.copy_(loss.reshape(1), non_blocking=False)   # D2H read of the step's result
+                    last = float(host_loss[0])
+            else:
+                one_step(x0, y0)
+        ev1.record()
+        barrier()
+        wall = (time.perf_counter() - t0) * 1e3
+        ms = ev0.elapsed_time(ev1)
+        t = torch.tensor([ms, wall], dtype=torch.float64, device=device)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t[0]), float(t[1]), last
+
+    # ---- warm-up -----------------------------------------------------------------------------
+    for _ in range(max(3, a.warmup)):
+        one_step(x0, y0)
+    barrier()
+    err = tr.check_device_error()
+    if err:
+        raise SystemExit(f"device error word {err:#x} after warm-up")
+
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    if sampler:
+        sampler.start()
+    l0 = L.launches()
+    ms, wall_ms, _ = timed(a.steps, e2e=False)
+    launches = L.launches() - l0
+    clocks = sampler.stop() if sampler else None
+    stats = tr.exchange.step  # noqa: F841 (keep reference alive)
+    e2e = None
+    if not a.no_e2e:
+        for _ in range(3):
+            x, y = feeder.next(); one_step(x, y); feeder.mark_consumed()
+        ms_e, wall_e, last_loss = timed(a.steps, e2e=True)
+        e2e = {"value": a.batch_size * n_workers * a.steps / (wall_e / 1e3), "unit": "images/s",
+               "h2d_bytes_per_step": feeder.h2d_bytes_per_step, "d2h_bytes_per_step": 4,
+               "ms_per_step": wall_e / a.steps, "timed_with": "host wall clock around barrier+synchronize, max over ranks",
+               "last_loss": last_loss}
+    # exchange statistics (one extra step with stats collection, outside the timed regions)
+    st = None
+    if role == "worker":
+        _, st = tr.step(x0, y0, want_stats=True)
+    else:
+        st = tr.server_step(want_stats=True)
+    barrier()
+    err = tr.check_device_error()
+    value = a.batch_size * n_workers * a.steps / (ms / 1e3)
+    out = {
+        "metric": f"{a.model} images/sec ({a.compressor} k={a.topk_ratio} s={a.qsgd_levels} {a.exchange})",
+        "value": value, "unit": "images/s", "n_gpus": a.gpus, "steps": a.steps, "warmup": max(3, a.warmup),
+        "ms_per_step": ms / a.steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": value / (REFERENCE_CPU_IMG_S_PER_WORKER * max(1, n_workers)),
+        "vs_baseline_note": "BASELINE.md publishes no GPU throughput; denominator is its derived 104 images/s per worker (VGG11 M1, Colab CPU)",
+        "dtype": a.dtype, "data": "synthetic (CIFAR-10 shape, random-init weights)", "impl": "ewdml",
+        "config": {"model": a.model, "global_batch": a.batch_size * n_workers, "per_gpu_batch": a.batch_size,
+                   "seq_len": None, "image": list(tr.input_spec()[1:]),
+                   "parallelism": f"dp{world}" + ("(1 server)" if a.exchange == "ps" else ""),
+                   "compressor": a.compressor, "topk_ratio": a.topk_ratio, "qsgd_levels": a.qsgd_levels,
+                   "exchange": a.exchange, "compute": a.compute,
+                   "l2": "none" if a.no_flush else "256 MiB buffer overwritten every step inside the timed region"},
+        "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "device_ms_total": ms, "wall_ms_total": wall_ms,
+        "exchange": None if st is None else {"bytes_sent_per_step": st.bytes_sent, "bytes_recv_per_step": st.bytes_recv,
+                                             "dense_bytes": tr.flat.dense_nbytes(),
+                                             "ms_send": st.t_send * 1e3, "ms_recv_apply": st.t_recv * 1e3},
+        "device_error": err,
+    }
+    if rank == 0:
+        print(json.dumps(out), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    pg.close()
+
+
+def main():
+    a = parse()
+    if a.impl == "reference":
+        from baseline.run_reference import main as ref_main
+        return ref_main(a)
+    if a.impl == "nccl":
+        from baseline.nccl_same_algorithm import main as nccl_main
+        return nccl_main(a)
+    return run_ewdml(a)
+
+
+if __name__ == "__main__":
+    main()

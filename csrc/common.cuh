@@ -1,0 +1,174 @@
+// Shared device/host helpers for the ewdml sm_100a kernels.
+#pragma once
+
+#include <cuda_runtime.h>
+#include <cuda_bf16.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+
+#include "../include/ewdml.h"
+
+// ---------------------------------------------------------------------------------------------
+// host-side error plumbing
+// ---------------------------------------------------------------------------------------------
+void ewdml_set_error(const char* fmt, ...);
+void ewdml_count_launch(int n = 1);
+extern "C" uint32_t* ewdml_device_error_word();      // device pointer, lazily allocated per device
+extern "C" uint64_t ewdml_spin_limit();
+
+#define EWDML_CUDA(expr)                                                                   \
+    do {                                                                                   \
+        cudaError_t _e = (expr);                                                           \
+        if (_e != cudaSuccess) {                                                           \
+            ewdml_set_error("%s:%d: %s -> %s", __FILE__, __LINE__, #expr, cudaGetErrorString(_e)); \
+            return (int)_e;                                                                \
+        }                                                                                  \
+    } while (0)
+
+#define EWDML_CHECK_ARG(cond)                                                              \
+    do {                                                                                   \
+        if (!(cond)) {                                                                     \
+            ewdml_set_error("%s:%d: bad argument: %s", __FILE__, __LINE__, #cond);         \
+            return EWDML_ERR_ARG;                                                          \
+        }                                                                                  \
+    } while (0)
+
+#define EWDML_LAUNCH_CHECK()                                                               \
+    do {                                                                                   \
+        cudaError_t _e = cudaGetLastError();                                               \
+        if (_e != cudaSuccess) {                                                           \
+            ewdml_set_error("%s:%d: launch failed: %s", __FILE__, __LINE__, cudaGetErrorString(_e)); \
+            return (int)_e;                                                                \
+        }                                                                                  \
+        ewdml_count_launch();                                                              \
+    } while (0)
+
+// ---------------------------------------------------------------------------------------------
+// memory-ordering primitives for the cross-GPU flag protocol (signal/wait over NVLink)
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+    uint32_t v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ uint32_t ld_relaxed_sys(const uint32_t* p) {
+    uint32_t v;
+    asm volatile("ld.relaxed.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_na_v4(void* p, uint4 v) {
+    asm volatile("st.global.L1::no_allocate.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(v.x), "r"(v.y),
+                 "r"(v.z), "r"(v.w)
+                 : "memory");
+}
+__device__ __forceinline__ uint4 ld_nc_v4(const void* p) {
+    uint4 v;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0, %1, %2, %3}, [%4];"
+                 : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+                 : "l"(p));
+    return v;
+}
+// plain (coherent) 16-byte load: payload slots are written by peers, never use .nc on them
+__device__ __forceinline__ uint4 ld_v4(const void* p) {
+    uint4 v;
+    asm volatile("ld.global.v4.u32 {%0, %1, %2, %3}, [%4];"
+                 : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+                 : "l"(p)
+                 : "memory");
+    return v;
+}
+
+// Spin until *flag >= seq (sequence numbers only grow).  Returns false on timeout and records it.
+__device__ __forceinline__ bool wait_flag_ge(const uint32_t* flag, uint32_t seq, uint64_t limit,
+                                             uint32_t* err_word, uint32_t err_code) {
+    uint64_t it = 0;
+    while ((int32_t)(ld_acquire_sys(flag) - seq) < 0) {
+        if (++it > limit) {
+            atomicExch(err_word, err_code);
+            return false;
+        }
+        if ((it & 63) == 0) __nanosleep(64);
+    }
+    return true;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Philox4x32-10 (Random123); must match ewdml/compress/rng.py bit for bit.
+// counter = (idx/4 low, stream, idx/4 high, 0); key = (seed, step); lane idx%4; u = (x>>8)*2^-24
+// ---------------------------------------------------------------------------------------------
+struct Philox4 {
+    uint32_t v[4];
+};
+__device__ __forceinline__ Philox4 philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3,
+                                                 uint32_t k0, uint32_t k1) {
+#pragma unroll
+    for (int r = 0; r < 10; ++r) {
+        uint32_t hi0 = __umulhi(0xD2511F53u, c0), lo0 = 0xD2511F53u * c0;
+        uint32_t hi1 = __umulhi(0xCD9E8D57u, c2), lo1 = 0xCD9E8D57u * c2;
+        uint32_t n0 = hi1 ^ c1 ^ k0, n2 = hi0 ^ c3 ^ k1;
+        c0 = n0; c1 = lo1; c2 = n2; c3 = lo0;
+        k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
+    }
+    Philox4 o;
+    o.v[0] = c0; o.v[1] = c1; o.v[2] = c2; o.v[3] = c3;
+    return o;
+}
+__device__ __forceinline__ float philox_to_uniform(uint32_t x) {
+    return (float)(x >> 8) * 5.9604644775390625e-08f;   // 2^-24, exact
+}
+
+// ---------------------------------------------------------------------------------------------
+// block-level helpers (blockDim.x threads, power of two multiple of 32, <= 1024)
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t warp_incl_scan(uint32_t v) {
+    const int lane = threadIdx.x & 31;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        uint32_t t = __shfl_up_sync(0xffffffffu, v, d);
+        if (lane >= d) v += t;
+    }
+    return v;
+}
+// exclusive prefix of v over the block; *total receives the block sum.  smem: >= 33 words.
+__device__ __forceinline__ uint32_t block_excl_scan(uint32_t v, uint32_t* smem, uint32_t* total) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
+    uint32_t inc = warp_incl_scan(v);
+    if (lane == 31) smem[warp] = inc;
+    __syncthreads();
+    if (warp == 0) {
+        uint32_t w = lane < nw ? smem[lane] : 0;
+        uint32_t wi = warp_incl_scan(w);
+        smem[lane] = wi - w;
+        if (lane == 31) smem[32] = wi;
+    }
+    __syncthreads();
+    uint32_t res = smem[warp] + inc - v;
+    *total = smem[32];
+    __syncthreads();
+    return res;
+}
+template <typename T>
+__device__ __forceinline__ T warp_sum(T v) {
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) v += __shfl_xor_sync(0xffffffffu, v, d);
+    return v;
+}
+// deterministic block sum (fixed tree); result valid in all threads.  smem: >= 32 T.
+template <typename T>
+__device__ __forceinline__ T block_sum(T v, T* smem) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
+    v = warp_sum(v);
+    if (lane == 0) smem[warp] = v;
+    __syncthreads();
+    T r = lane < nw ? smem[lane] : T(0);
+    r = warp_sum(r);
+    __syncthreads();
+    return r;
+}
+
+__host__ __device__ __forceinline__ int64_t round_up_i64(int64_t x, int64_t a) { return (x + a - 1) / a * a; }
+__host__ __device__ __forceinline__ uint32_t align16(uint32_t x) { return (x + 15u) & ~15u; }

@@ -1,0 +1,230 @@
+// N1: rendezvous key-value store over TCP (rank 0 hosts a server thread).
+//
+// What the job needs at start-up -- exchange of IPC handles and device pointers, and a host
+// barrier -- is what Open MPI gets from the PMIx "modex" + fence (ompi:ompi/runtime/
+// ompi_mpi_init.c:657-724) over ORTE's out-of-band TCP tree (orte/mca/oob/tcp).  This is the
+// minimal equivalent: set / blocking get / barrier, length-prefixed binary protocol.
+#include <arpa/inet.h>
+#include <netinet/in.h>
+#include <netinet/tcp.h>
+#include <poll.h>
+#include <sys/socket.h>
+#include <unistd.h>
+
+#include <atomic>
+#include <chrono>
+#include <condition_variable>
+#include <cstring>
+#include <map>
+#include <mutex>
+#include <string>
+#include <thread>
+#include <vector>
+
+#include "../../include/ewdml.h"
+
+void ewdml_set_error(const char* fmt, ...);
+
+namespace {
+
+bool send_all(int fd, const void* buf, size_t n) {
+    const char* p = (const char*)buf;
+    while (n) {
+        ssize_t k = ::send(fd, p, n, MSG_NOSIGNAL);
+        if (k <= 0) return false;
+        p += k; n -= (size_t)k;
+    }
+    return true;
+}
+bool recv_all(int fd, void* buf, size_t n) {
+    char* p = (char*)buf;
+    while (n) {
+        ssize_t k = ::recv(fd, p, n, 0);
+        if (k <= 0) return false;
+        p += k; n -= (size_t)k;
+    }
+    return true;
+}
+bool send_blob(int fd, const std::string& s) {
+    uint32_t n = (uint32_t)s.size();
+    return send_all(fd, &n, 4) && (n == 0 || send_all(fd, s.data(), n));
+}
+bool recv_blob(int fd, std::string* s) {
+    uint32_t n = 0;
+    if (!recv_all(fd, &n, 4)) return false;
+    if (n > (64u << 20)) return false;
+    s->resize(n);
+    return n == 0 || recv_all(fd, &(*s)[0], n);
+}
+
+enum : uint8_t { OP_SET = 1, OP_GET = 2, OP_ADD = 3 };
+
+struct Server {
+    int listen_fd = -1;
+    std::thread accept_thread;
+    std::vector<std::thread> workers;
+    std::mutex mu;
+    std::condition_variable cv;
+    std::map<std::string, std::string> kv;
+    std::map<std::string, int64_t> counters;
+    std::atomic<bool> stop{false};
+    std::vector<int> fds;
+
+    void serve(int fd) {
+        for (;;) {
+            uint8_t op;
+            std::string key, val;
+            if (!recv_all(fd, &op, 1) || !recv_blob(fd, &key)) break;
+            if (op == OP_SET) {
+                if (!recv_blob(fd, &val)) break;
+                { std::lock_guard<std::mutex> lk(mu); kv[key] = val; }
+                cv.notify_all();
+                uint8_t ok = 1;
+                if (!send_all(fd, &ok, 1)) break;
+            } else if (op == OP_GET) {
+                std::unique_lock<std::mutex> lk(mu);
+                cv.wait(lk, [&] { return stop.load() || kv.count(key); });
+                if (stop.load() && !kv.count(key)) break;
+                std::string v = kv[key];
+                lk.unlock();
+                if (!send_blob(fd, v)) break;
+            } else if (op == OP_ADD) {
+                int64_t delta = 0, now = 0;
+                if (!recv_all(fd, &delta, 8)) break;
+                { std::lock_guard<std::mutex> lk(mu); now = (counters[key] += delta); kv["__ctr__" + key + "#" + std::to_string(now)] = "1"; }
+                cv.notify_all();
+                if (!send_all(fd, &now, 8)) break;
+            } else {
+                break;
+            }
+        }
+        ::close(fd);
+    }
+
+    void accept_loop() {
+        while (!stop.load()) {
+            pollfd p{listen_fd, POLLIN, 0};
+            if (::poll(&p, 1, 100) <= 0) continue;
+            int fd = ::accept(listen_fd, nullptr, nullptr);
+            if (fd < 0) continue;
+            int one = 1;
+            setsockopt(fd, IPPROTO_TCP, TCP_NODELAY, &one, sizeof(one));
+            std::lock_guard<std::mutex> lk(mu);
+            fds.push_back(fd);
+            workers.emplace_back([this, fd] { serve(fd); });
+        }
+    }
+};
+
+}  // namespace
+
+struct ewdml_store {
+    int rank = 0, world = 1;
+    int fd = -1;
+    Server* server = nullptr;
+    std::mutex mu;
+    std::map<std::string, int> barrier_epoch;
+};
+
+extern "C" int ewdml_store_create(ewdml_store** out, const char* addr, int port, int rank, int world, double timeout_s) {
+    if (!out || !addr || port <= 0 || rank < 0 || world < 1 || rank >= world) { ewdml_set_error("store_create: bad args"); return EWDML_ERR_ARG; }
+    ewdml_store* s = new ewdml_store();
+    s->rank = rank; s->world = world;
+    if (rank == 0) {
+        Server* sv = new Server();
+        sv->listen_fd = ::socket(AF_INET, SOCK_STREAM, 0);
+        int one = 1;
+        setsockopt(sv->listen_fd, SOL_SOCKET, SO_REUSEADDR, &one, sizeof(one));
+        sockaddr_in sa{};
+        sa.sin_family = AF_INET; sa.sin_port = htons((uint16_t)port); sa.sin_addr.s_addr = htonl(INADDR_ANY);
+        if (::bind(sv->listen_fd, (sockaddr*)&sa, sizeof(sa)) != 0 || ::listen(sv->listen_fd, 128) != 0) {
+            ewdml_set_error("store: cannot listen on port %d: %s", port, strerror(errno));
+            ::close(sv->listen_fd); delete sv; delete s;
+            return EWDML_ERR_IO;
+        }
+        sv->accept_thread = std::thread([sv] { sv->accept_loop(); });
+        s->server = sv;
+    }
+    auto deadline = std::chrono::steady_clock::now() + std::chrono::duration<double>(timeout_s > 0 ? timeout_s : 60.0);
+    for (;;) {
+        s->fd = ::socket(AF_INET, SOCK_STREAM, 0);
+        sockaddr_in sa{};
+        sa.sin_family = AF_INET; sa.sin_port = htons((uint16_t)port);
+        if (inet_pton(AF_INET, rank == 0 ? "127.0.0.1" : addr, &sa.sin_addr) != 1) {
+            ewdml_set_error("store: address must be an IPv4 literal, got %s", addr);
+            ::close(s->fd); ewdml_store_destroy(s);
+            return EWDML_ERR_ARG;
+        }
+        if (::connect(s->fd, (sockaddr*)&sa, sizeof(sa)) == 0) break;
+        ::close(s->fd); s->fd = -1;
+        if (std::chrono::steady_clock::now() > deadline) {
+            ewdml_set_error("store: rank %d could not reach %s:%d", rank, addr, port);
+            ewdml_store_destroy(s);
+            return EWDML_ERR_TIMEOUT;
+        }
+        std::this_thread::sleep_for(std::chrono::milliseconds(50));
+    }
+    int one = 1;
+    setsockopt(s->fd, IPPROTO_TCP, TCP_NODELAY, &one, sizeof(one));
+    *out = s;
+    return 0;
+}
+
+extern "C" int ewdml_store_set(ewdml_store* s, const char* key, const void* val, size_t len) {
+    if (!s || !key) return EWDML_ERR_ARG;
+    std::lock_guard<std::mutex> lk(s->mu);
+    uint8_t op = OP_SET, ok = 0;
+    if (!send_all(s->fd, &op, 1) || !send_blob(s->fd, key) || !send_blob(s->fd, std::string((const char*)val, len)) ||
+        !recv_all(s->fd, &ok, 1)) { ewdml_set_error("store_set(%s): connection lost", key); return EWDML_ERR_IO; }
+    return 0;
+}
+
+extern "C" int ewdml_store_get(ewdml_store* s, const char* key, void* val, size_t cap, size_t* len) {
+    if (!s || !key) return EWDML_ERR_ARG;
+    std::lock_guard<std::mutex> lk(s->mu);
+    uint8_t op = OP_GET;
+    std::string v;
+    if (!send_all(s->fd, &op, 1) || !send_blob(s->fd, key) || !recv_blob(s->fd, &v)) {
+        ewdml_set_error("store_get(%s): connection lost", key);
+        return EWDML_ERR_IO;
+    }
+    if (len) *len = v.size();
+    if (v.size() > cap) { ewdml_set_error("store_get(%s): value of %zu bytes exceeds buffer %zu", key, v.size(), cap); return EWDML_ERR_OVERFLOW; }
+    if (val && !v.empty()) memcpy(val, v.data(), v.size());
+    return 0;
+}
+
+extern "C" int ewdml_store_barrier(ewdml_store* s, const char* name) {
+    if (!s || !name) return EWDML_ERR_ARG;
+    int epoch;
+    { std::lock_guard<std::mutex> lk(s->mu); epoch = ++s->barrier_epoch[name]; }
+    std::string key = std::string("__bar__") + name;
+    {
+        std::lock_guard<std::mutex> lk(s->mu);
+        uint8_t op = OP_ADD;
+        int64_t one = 1, now = 0;
+        if (!send_all(s->fd, &op, 1) || !send_blob(s->fd, key) || !send_all(s->fd, &one, 8) || !recv_all(s->fd, &now, 8)) {
+            ewdml_set_error("store_barrier(%s): connection lost", name);
+            return EWDML_ERR_IO;
+        }
+    }
+    std::string wait_key = "__ctr__" + key + "#" + std::to_string((int64_t)epoch * s->world);
+    return ewdml_store_get(s, wait_key.c_str(), nullptr, 16, nullptr);
+}
+
+extern "C" int ewdml_store_destroy(ewdml_store* s) {
+    if (!s) return 0;
+    if (s->fd >= 0) { ::shutdown(s->fd, SHUT_RDWR); ::close(s->fd); }
+    if (s->server) {
+        Server* sv = s->server;
+        sv->stop.store(true);
+        sv->cv.notify_all();
+        { std::lock_guard<std::mutex> lk(sv->mu); for (int fd : sv->fds) ::shutdown(fd, SHUT_RDWR); }
+        if (sv->accept_thread.joinable()) sv->accept_thread.join();
+        for (auto& t : sv->workers) if (t.joinable()) t.join();
+        ::close(sv->listen_fd);
+        delete sv;
+    }
+    delete s;
+    return 0;
+}

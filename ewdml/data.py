@@ -145,9 +145,11 @@ class _Slot:
 class DeviceFeeder:
     """Pinned-host -> device batch pipeline for the GPU path (double-buffered, copy stream).
 
-    Holds the whole (sharded) dataset in pinned memory; every ``next()`` enqueues the H2D copy of
-    the *following* batch on a side stream and returns the batch copied one call earlier, so the
-    copy overlaps the previous step's compute.  ``h2d_bytes_per_step`` is what bench.py reports.
+    Holds the (sharded) dataset in host memory in NHWC order; every ``next()`` gathers the
+    *following* shuffled batch into a pinned staging buffer, enqueues its H2D copy on a side stream
+    and returns the batch copied one call earlier, so the copy overlaps the previous step's compute.
+    Batches are returned as NCHW-shaped channels-last views.  ``h2d_bytes_per_step`` is what
+    bench.py reports.
     """
 
     def __init__(self, data: torch.Tensor, targets: torch.Tensor, batch_size: int,
@@ -156,13 +158,10 @@ class DeviceFeeder:
                  num_shards: int = 1) -> None:
         n = data.shape[0]
         idx = torch.arange(shard_rank, n, num_shards)
-        self.data = data[idx].to(dtype).contiguous()
+        self.nhwc = bool(channels_last and data.dim() == 4)
+        d = data[idx].to(dtype)
+        self.data = (d.permute(0, 2, 3, 1) if self.nhwc else d).contiguous()
         self.targets = targets[idx].to(torch.int64).contiguous()
-        if channels_last and self.data.dim() == 4:
-            self.data = self.data.contiguous(memory_format=torch.channels_last)
-        if device.type == "cuda":
-            self.data = self.data.pin_memory()
-            self.targets = self.targets.pin_memory()
         self.n = self.data.shape[0]
         self.bs = batch_size
         self.device = device
@@ -175,12 +174,10 @@ class DeviceFeeder:
         self._cuda = device.type == "cuda"
         if self._cuda:
             self._stream = torch.cuda.Stream(device=device)
-            # staging buffers (pinned) so a shuffled batch is one contiguous copy
             shape = (batch_size,) + tuple(self.data.shape[1:])
-            mf = torch.channels_last if (channels_last and self.data.dim() == 4) else torch.contiguous_format
-            self._hx = [torch.empty(shape, dtype=dtype).contiguous(memory_format=mf).pin_memory() for _ in range(2)]
+            self._hx = [torch.empty(shape, dtype=dtype).pin_memory() for _ in range(2)]
             self._hy = [torch.empty(batch_size, dtype=torch.int64).pin_memory() for _ in range(2)]
-            self._dx = [torch.empty(shape, dtype=dtype, device=device).contiguous(memory_format=mf) for _ in range(2)]
+            self._dx = [torch.empty(shape, dtype=dtype, device=device) for _ in range(2)]
             self._dy = [torch.empty(batch_size, dtype=torch.int64, device=device) for _ in range(2)]
             self._ev = [torch.cuda.Event() for _ in range(2)]
             self._consumed = [None, None]
@@ -194,6 +191,9 @@ class DeviceFeeder:
         sel = self._perm[self._pos:self._pos + self.bs]
         self._pos += self.bs
         return sel
+
+    def _as_nchw(self, x: torch.Tensor) -> torch.Tensor:
+        return x.permute(0, 3, 1, 2) if self.nhwc else x
 
     def _prefetch(self) -> None:
         k = self._k
@@ -211,12 +211,12 @@ class DeviceFeeder:
     def next(self) -> Tuple[torch.Tensor, torch.Tensor]:
         if not self._cuda:
             sel = self._next_indices()
-            return self.data[sel], self.targets[sel]
+            return self._as_nchw(self.data[sel]), self.targets[sel]
         k = self._k
         torch.cuda.current_stream(self.device).wait_event(self._ev[k])
-        x, y = self._dx[k], self._dy[k]
+        x, y = self._as_nchw(self._dx[k]), self._dy[k]
         self._k ^= 1
-        # the host staging buffer k^1 was consumed by the copy issued two calls ago
+        # the pinned staging buffer of the other slot was consumed by the copy issued two calls ago
         self._ev[self._k].synchronize()
         self._prefetch()
         return x, y

@@ -1,0 +1,156 @@
+"""Process group over the symmetric peer heap (the ``ProcessGroup`` object of SURVEY.md 2E).
+
+A :class:`PeerGroup` knows (rank, world, device), performs the start-up rendezvous and hands out
+*symmetric buffers*: every rank allocates the same number of bytes, IPC handles are exchanged once
+through the native TCP store (or ``torch.distributed`` when it is already initialised) and every
+peer's allocation is mapped into this process, after which kernels address peer memory with plain
+pointers over NVLink.  This replaces communicator construction + PMIx modex + BTL endpoint set-up
+(``ompi:ompi/runtime/ompi_mpi_init.c:428-800``) and the smcuda IPC handshake.
+
+:class:`LocalPeerGroup` emulates ``world`` ranks inside ONE process on ONE GPU (every "peer" buffer
+is a local allocation).  It exists for single-GPU tests: kernels that wait on each other must never
+run as separate launches on one GPU (B200_PROFILING.md), so the emulation runs all senders first
+and all receivers afterwards on one stream.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from typing import List, Optional
+
+import torch
+
+from ..runtime import lib as L
+
+
+class _CudaArray:
+    """Minimal ``__cuda_array_interface__`` carrier so torch can wrap raw device memory."""
+
+    def __init__(self, ptr: int, nbytes: int, owner=None):
+        self.__cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (ptr, False),
+                                         "version": 2, "strides": None}
+        self._owner = owner
+
+
+def wrap_device_memory(ptr: int, nbytes: int, device: torch.device, owner=None) -> torch.Tensor:
+    with torch.cuda.device(device):
+        t = torch.as_tensor(_CudaArray(ptr, nbytes, owner), device=device)
+    return t
+
+
+class SymmetricBuffer:
+    """``ptrs[r]`` = address of rank r's copy as mapped in this process; ``local`` = own bytes tensor."""
+
+    def __init__(self, name: str, nbytes: int, ptrs: List[int], rank: int, device: torch.device, owner):
+        self.name, self.nbytes, self.ptrs, self.rank = name, nbytes, ptrs, rank
+        self.local = wrap_device_memory(ptrs[rank], nbytes, device, owner)
+
+    def view(self, dtype: torch.dtype, offset_bytes: int = 0, numel: Optional[int] = None) -> torch.Tensor:
+        es = torch.empty((), dtype=dtype).element_size()
+        end = self.nbytes if numel is None else offset_bytes + numel * es
+        return self.local[offset_bytes:end].view(dtype)
+
+
+class _Alloc:
+    def __init__(self, lib, ptr):
+        self.lib, self.ptr = lib, ptr
+
+    def __del__(self):
+        try:
+            if self.ptr:
+                self.lib.ewdml_heap_free(C.c_void_p(self.ptr))
+        except Exception:
+            pass
+
+
+class PeerGroup:
+    def __init__(self, rank: int, world: int, device: torch.device, store: Optional[L.Store] = None):
+        self.lib = L.load()
+        self.rank, self.world, self.device = rank, world, device
+        self.store = store
+        self._allocs = []
+        self._n = 0
+        torch.cuda.set_device(device)
+        if world > L.MAX_PEERS:
+            raise ValueError(f"world size {world} exceeds EWDML_MAX_PEERS={L.MAX_PEERS}")
+
+    @classmethod
+    def from_env(cls, device: torch.device) -> "PeerGroup":
+        rank = int(os.environ.get("RANK", "0"))
+        world = int(os.environ.get("WORLD_SIZE", "1"))
+        store = None
+        if world > 1:
+            addr = os.environ.get("MASTER_ADDR", "127.0.0.1")
+            port = int(os.environ.get("EWDML_STORE_PORT", int(os.environ.get("MASTER_PORT", "29500")) + 17))
+            store = L.Store(addr, port, rank, world, timeout_s=120.0)
+        return cls(rank, world, device, store)
+
+    def _all_gather_bytes(self, name: str, val: bytes) -> List[bytes]:
+        if self.world == 1:
+            return [val]
+        if self.store is not None:
+            return self.store.all_gather(name, val)
+        import torch.distributed as dist
+        out = [None] * self.world
+        dist.all_gather_object(out, val)
+        return out
+
+    def host_barrier(self, name: str = "pg") -> None:
+        if self.world == 1:
+            return
+        if self.store is not None:
+            self.store.barrier(name)
+        else:
+            import torch.distributed as dist
+            dist.barrier()
+
+    def alloc(self, name: str, nbytes: int) -> SymmetricBuffer:
+        nbytes = (nbytes + 255) // 256 * 256
+        base = C.c_void_p()
+        L.check(self.lib.ewdml_heap_alloc(C.byref(base), nbytes), f"heap_alloc({name}, {nbytes})")
+        owner = _Alloc(self.lib, base.value)
+        handle = C.create_string_buffer(64)
+        L.check(self.lib.ewdml_heap_export(base, handle), "heap_export")
+        self._n += 1
+        handles = self._all_gather_bytes(f"ipc/{self._n}/{name}", handle.raw)
+        ptrs = []
+        for r, h in enumerate(handles):
+            if r == self.rank:
+                ptrs.append(base.value)
+            else:
+                mapped = C.c_void_p()
+                L.check(self.lib.ewdml_heap_import(h, C.byref(mapped)), f"heap_import(rank {r})")
+                ptrs.append(mapped.value)
+        self.host_barrier(f"alloc/{self._n}")
+        buf = SymmetricBuffer(name, nbytes, ptrs, self.rank, self.device, owner)
+        self._allocs.append(buf)
+        return buf
+
+    def close(self) -> None:
+        for b in self._allocs:
+            for r, p in enumerate(b.ptrs):
+                if r != self.rank and p:
+                    self.lib.ewdml_heap_unmap(C.c_void_p(p))
+        self._allocs.clear()
+        if self.store is not None:
+            self.store.close()
+            self.store = None
+
+
+class LocalPeerGroup:
+    """``world`` emulated ranks in one process on one GPU; ``alloc`` returns one buffer per rank."""
+
+    def __init__(self, world: int, device: torch.device):
+        self.lib = L.load()
+        self.world, self.device = world, device
+        torch.cuda.set_device(device)
+
+    def alloc(self, name: str, nbytes: int) -> List[SymmetricBuffer]:
+        nbytes = (nbytes + 255) // 256 * 256
+        owners, ptrs = [], []
+        for _ in range(self.world):
+            base = C.c_void_p()
+            L.check(self.lib.ewdml_heap_alloc(C.byref(base), nbytes), f"heap_alloc({name})")
+            owners.append(_Alloc(self.lib, base.value))
+            ptrs.append(base.value)
+        return [SymmetricBuffer(name, nbytes, list(ptrs), r, self.device, owners[r]) for r in range(self.world)]

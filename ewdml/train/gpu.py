@@ -1,0 +1,91 @@
+"""GPU training engine: the public API behind ``bench.py`` and ``distributed_nn.py --enable-gpu``.
+
+One process per GPU.  A step is: wait for the prefetched batch (pinned host -> device copy issued
+one step earlier on a copy stream) -> forward/backward (bf16 autocast over fp32 master weights on
+the torch compute path, or the hand-written sm_100a kernels with ``compute="native"``) writing
+gradients straight into the flat gradient buffer -> exchange kernels (select + QSGD + pack + P2P
+stores, then unpack + average + momentum-SGD) on the same stream.  Nothing in the step synchronises
+with the host; the loss is read back only when the caller asks for it.
+
+This is the B200 equivalent of ``DistributedWorker.train_updated`` (``distributed_worker.py:162-239``)
+with its per-tensor D2H copies, blocking gloo collectives and Python optimizer loop removed.
+"""
+from __future__ import annotations
+
+from typing import Optional
+
+import torch
+
+from ..config import TrainConfig
+from ..models import build_model, input_shape
+from ..ops import layers as Lyr
+from ..parallel.flat import FlatModel
+from ..parallel.native_exchange import (NativeAllgather, NativeAllreduce, NativePSServer, NativePSWorker,
+                                        native_allocator)
+from ..parallel.peer import PeerGroup
+from ..runtime import lib as L
+
+
+class GpuTrainer:
+    def __init__(self, cfg: TrainConfig, device: torch.device, pg: Optional[PeerGroup] = None,
+                 role: str = "worker"):
+        self.cfg, self.device, self.role = cfg, device, role
+        torch.cuda.set_device(device)
+        self.pg = pg or PeerGroup(0, 1, device)
+        self.rank, self.world = self.pg.rank, self.pg.world
+        torch.manual_seed(cfg.seed)                      # identical initial weights on every rank
+        Lyr.set_compute(cfg.compute)
+        self.model = build_model(cfg.network, cfg.num_classes())
+        hint = {}
+        self.flat = FlatModel(self.model, device, channels_last=True, with_bf16=(cfg.compute == "native"),
+                              allocator=native_allocator(self.pg, hint) if cfg.exchange == "allreduce" else None)
+        self.flat.grad_sym = hint.get("grad_sym")
+        for b in self.model.buffers():
+            b.data = b.data.to(device)
+        if cfg.exchange == "ps":
+            cls = NativePSServer if role == "server" else NativePSWorker
+            self.exchange = cls(self.flat, cfg, None, self.pg)
+        elif cfg.exchange == "allgather":
+            self.exchange = NativeAllgather(self.flat, cfg, None, self.pg)
+        else:
+            self.exchange = NativeAllreduce(self.flat, cfg, None, self.pg, self.flat.grad_sym)
+        self.autocast = cfg.dtype == "bf16" and cfg.compute == "torch"
+        self.step_idx = 0
+        self.period = cfg.resolved_sync_period()
+        self.model.train()
+        self.last_loss = None
+        self.last_logits = None
+        # seeds differ per rank for dropout etc. after the common initialisation
+        torch.manual_seed(cfg.seed + 1000 * (self.rank + 1))
+
+    # -- one optimisation step on a device-resident batch ------------------------------------
+    def step(self, x: torch.Tensor, y: torch.Tensor, want_stats: bool = False):
+        f = self.flat
+        f.grad.zero_()
+        if self.autocast:
+            with torch.autocast("cuda", dtype=torch.bfloat16):
+                logits = self.model(x)
+            loss = torch.nn.functional.cross_entropy(logits.float(), y)
+        else:
+            logits = self.model(x)
+            loss = Lyr.cross_entropy(logits, y)
+        loss.backward()
+        st = self.exchange.step(self.step_idx, is_sync_step=(self.step_idx % self.period == 0), want_stats=want_stats)
+        self.step_idx += 1
+        self.last_loss, self.last_logits = loss.detach(), logits.detach()
+        return self.last_loss, st
+
+    def server_step(self, want_stats: bool = False):
+        st = self.exchange.step(self.step_idx, is_sync_step=(self.step_idx % self.period == 0), want_stats=want_stats)
+        self.step_idx += 1
+        return st
+
+    def input_spec(self):
+        c, h, w = input_shape(self.cfg.network)
+        return (self.cfg.batch_size, c, h, w)
+
+    def check_device_error(self) -> int:
+        import ctypes as C
+        err = C.c_uint32(0)
+        L.check(L.load().ewdml_get_device_error(C.byref(err), C.c_void_p(torch.cuda.current_stream().cuda_stream)))
+        return err.value

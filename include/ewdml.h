@@ -1,0 +1,175 @@
+/* ewdml -- C ABI of the native runtime and the sm_100a kernels.
+ *
+ * Everything here is callable through ctypes (ewdml/runtime/lib.py) or from C/C++.  All entry
+ * points return 0 on success or a negative ewdml error code / positive cudaError_t value; the text
+ * of the last error on the calling thread is available from ewdml_last_error().
+ *
+ * Reference citations name what each group replaces in
+ * AnirudhKaushik10/Efficient-Workers-in-Distributed-Machine-Learning (paths relative to its root;
+ * "ompi:" = openmpi-4.1.0/).
+ */
+#ifndef EWDML_H_
+#define EWDML_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define EWDML_MAX_PEERS 16
+#define EWDML_TILE 8192          /* elements per tile (one CTA) in the select/encode/apply kernels */
+#define EWDML_HIST_BINS 2048     /* 11-bit radix digit                                             */
+
+/* wire modes of a payload slot (see DESIGN.md "wire format") */
+enum { EWDML_MODE_DENSE = 0, EWDML_MODE_IDX16 = 1, EWDML_MODE_BITMAP = 2 };
+/* element selection */
+enum { EWDML_SEL_ALL = 0, EWDML_SEL_TOPK = 1 };
+/* value coding: QSGD level codes of `code_bits` bits, or raw fp32 */
+enum { EWDML_VAL_QSGD = 0, EWDML_VAL_RAW32 = 1 };
+/* what the receive kernel does with the averaged gradient */
+enum { EWDML_OUT_SGD = 0,        /* momentum-SGD update of param/momentum (+bf16 shadow)          */
+       EWDML_OUT_GRAD = 1,       /* write the dense averaged gradient                              */
+       EWDML_OUT_ASSIGN = 2 };   /* param = average (weight pull in parameter-server mode)         */
+
+enum { EWDML_ERR_ARG = -1, EWDML_ERR_CUDA = -2, EWDML_ERR_TIMEOUT = -3, EWDML_ERR_OVERFLOW = -4,
+       EWDML_ERR_IO = -5, EWDML_ERR_STATE = -6 };
+
+const char* ewdml_last_error(void);
+int ewdml_version(void);
+
+/* ------------------------------------------------------------------------------------------
+ * Exchange plan: static description of one gradient group (segments = parameter tensors).
+ * Replaces the per-tensor Python loops of distributed_worker.py:317-351 / :269-279 and
+ * sync_replicas_master_nn.py:218-232, and the compressor objects of Compresssor/{qsgd,TopK}.py.
+ * ------------------------------------------------------------------------------------------ */
+typedef struct ewdml_plan ewdml_plan;
+
+typedef struct {
+    int mode;            /* EWDML_MODE_*                                                        */
+    int sel;             /* EWDML_SEL_*                                                         */
+    int val;             /* EWDML_VAL_*                                                         */
+    int levels;          /* QSGD s (qsgd.py:9 default 128)                                      */
+    int code_bits;       /* bits per transmitted code (sign + ceil(log2 s)); 32 for RAW32       */
+    double topk_ratio;   /* k = max(1, (int)(numel * ratio)) per segment (TopK.py:7)            */
+} ewdml_codec;
+
+/* seg_offset/seg_numel: element offsets (multiples of 32) and sizes of each segment in the flat
+ * fp32 buffer.  Allocates the device tables and the scratch (histograms, candidates, counters). */
+int ewdml_plan_create(ewdml_plan** out, int nseg, const int64_t* seg_offset, const int64_t* seg_numel,
+                      const ewdml_codec* codec);
+int ewdml_plan_destroy(ewdml_plan* plan);
+/* bytes a receive slot must provide for one sender's payload of this plan */
+int64_t ewdml_plan_slot_bytes(const ewdml_plan* plan);
+int64_t ewdml_plan_num_tiles(const ewdml_plan* plan);
+int64_t ewdml_plan_scratch_bytes(const ewdml_plan* plan);
+/* byte offsets of the regions inside a slot: [0]=norms [1]=tile directory [2]=bitmap [3]=data */
+int ewdml_plan_slot_layout(const ewdml_plan* plan, int64_t out[4]);
+
+typedef struct {
+    int n;                                   /* number of destination slots                       */
+    void* slot[EWDML_MAX_PEERS];             /* peer-mapped (or local) slot base addresses        */
+    uint32_t* flag[EWDML_MAX_PEERS];         /* peer-mapped flag words, set to `seq` when done    */
+} ewdml_dests;
+
+typedef struct {
+    int n;                                   /* number of source slots (local memory)             */
+    const void* slot[EWDML_MAX_PEERS];
+    const uint32_t* flag[EWDML_MAX_PEERS];   /* local flag words to wait on (>= seq); may be NULL */
+} ewdml_sources;
+
+/* K1: select (top-k radix select) + QSGD quantise + bit-pack + store into every destination slot
+ * and publish the per-destination flag.  `grad` is this rank's flat gradient.  `rng_stream`
+ * separates the random draws of different senders (use the rank).  Enqueues on `stream`.        */
+int ewdml_send(ewdml_plan* plan, const float* grad, const ewdml_dests* dests, uint32_t seq,
+               uint64_t seed, uint32_t step, uint32_t rng_stream, void* stream);
+
+typedef struct {
+    float lr, momentum, dampening, weight_decay;
+    int nesterov;
+    int first_step;       /* 1: momentum buffer := gradient (optim/sgd.py:79-82)                 */
+} ewdml_sgd;
+
+/* K2: wait for the sources' flags, unpack + dequantise each payload with its own norm,
+ * accumulate, divide by `divisor`, then per `out_mode` update param/momentum (and the optional
+ * bf16 shadow copy) or write the dense average to `out`.                                        */
+int ewdml_recv_apply(ewdml_plan* plan, const ewdml_sources* srcs, uint32_t seq, float divisor,
+                     int out_mode, const ewdml_sgd* sgd, float* param, float* momentum,
+                     void* param_bf16, float* out, void* stream);
+
+/* Local fused momentum-SGD on flat buffers (optim/sgd.py:59-92), no exchange.                   */
+int ewdml_sgd_apply(const float* grad, float* param, float* momentum, void* param_bf16, int64_t n,
+                    const ewdml_sgd* sgd, float grad_scale, void* stream);
+
+/* {entries, data bytes, total payload bytes, error word} of the plan's last ewdml_send; syncs the
+ * stream.                                                                                        */
+int ewdml_plan_read_stats(ewdml_plan* plan, int64_t out[4], void* stream);
+/* Debug/test access to the per-segment selection results of the last send:
+ * out[4*i+0]=threshold key, +1=ties taken, +2=norm bits, +3=candidate count                     */
+int ewdml_plan_read_seginfo(ewdml_plan* plan, uint32_t* out, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * K4: dense fused-scale allreduce over peer memory (replaces hvd.allreduce(Average) and
+ * ompi:ompi/mca/coll/base/coll_base_allreduce.c:341 + ompi:ompi/mca/op/avx/op_avx_functions.c).
+ * `bufs[r]` is rank r's buffer as mapped in THIS process; `flags` is this rank's local flag block
+ * (>= 4*EWDML_MAX_PEERS words) and `peer_flags[r]` the same block of rank r mapped here.
+ * ------------------------------------------------------------------------------------------ */
+typedef struct {
+    int rank, world;
+    float* bufs[EWDML_MAX_PEERS];
+    uint32_t* peer_flags[EWDML_MAX_PEERS];
+    uint32_t* flags;
+} ewdml_comm;
+
+enum { EWDML_AR_AUTO = 0, EWDML_AR_ONESHOT = 1, EWDML_AR_TWOSHOT = 2 };
+/* in-place: every rank ends with scale * sum_r bufs[r][0..n) in its own buffer                  */
+int ewdml_allreduce(const ewdml_comm* comm, int64_t n, float scale, int algo, uint32_t seq,
+                    uint32_t* work_counter, void* stream);
+/* device-side barrier across ranks (flag exchange)                                              */
+int ewdml_barrier(const ewdml_comm* comm, uint32_t seq, void* stream);
+/* device error word (0 = ok) set by kernels whose flag spin exceeded the limit                  */
+int ewdml_get_device_error(uint32_t* out, void* stream);
+int ewdml_set_spin_limit(uint64_t iters);
+
+/* ------------------------------------------------------------------------------------------
+ * N1: symmetric peer heap (replaces BTL smcuda + common_cuda.c IPC paths,
+ * ompi:opal/mca/common/cuda/common_cuda.c:1006-1152, and OSHMEM memheap).
+ * ------------------------------------------------------------------------------------------ */
+int ewdml_heap_alloc(void** base, size_t bytes);                 /* zero-initialised            */
+int ewdml_heap_free(void* base);
+int ewdml_heap_export(void* base, uint8_t handle[64]);           /* cudaIpcMemHandle_t          */
+int ewdml_heap_import(const uint8_t handle[64], void** mapped);  /* enables peer access lazily  */
+int ewdml_heap_unmap(void* mapped);
+int ewdml_can_access_peer(int dev, int peer, int* out);
+
+/* N1: rendezvous key-value store over TCP (replaces the PMIx modex / ORTE oob,
+ * ompi:ompi/runtime/ompi_mpi_init.c:657-724).  Rank 0 hosts the server thread.                  */
+typedef struct ewdml_store ewdml_store;
+int ewdml_store_create(ewdml_store** out, const char* addr, int port, int rank, int world,
+                       double timeout_s);
+int ewdml_store_set(ewdml_store* s, const char* key, const void* val, size_t len);
+int ewdml_store_get(ewdml_store* s, const char* key, void* val, size_t cap, size_t* len); /* blocks */
+int ewdml_store_barrier(ewdml_store* s, const char* name);
+int ewdml_store_destroy(ewdml_store* s);
+
+/* N4: launcher + watchdog (replaces orterun/plm/odls/errmgr: start local ranks with the
+ * RANK/WORLD_SIZE/LOCAL_RANK/MASTER_* contract, tear the job down when one exits non-zero).
+ * Returns the job's exit status.                                                                 */
+int ewdml_launch(int nproc, const char* master_addr, int master_port, char* const argv[],
+                 double grace_s, int* failed_rank);
+
+/* N5: counters (replaces SPC_RECORD / pml+coll monitoring, ompi:ompi/runtime/ompi_spc.h).       */
+enum { EWDML_CTR_LAUNCHES = 0, EWDML_CTR_SEND_CALLS, EWDML_CTR_RECV_CALLS, EWDML_CTR_ALLREDUCE_CALLS,
+       EWDML_CTR_BYTES_SENT, EWDML_CTR_BYTES_RECV, EWDML_CTR_COMPUTE_LAUNCHES, EWDML_CTR_COUNT };
+int64_t ewdml_counter_get(int id);
+void ewdml_counter_add(int id, int64_t v);
+void ewdml_counters_reset(void);
+void ewdml_peer_matrix_add(int peer, int64_t bytes);             /* per-peer byte matrix row     */
+int ewdml_peer_matrix_get(int64_t out[EWDML_MAX_PEERS]);
+void ewdml_set_trace(int on);                                    /* libompitrace analogue        */
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* EWDML_H_ */
