@@ -36,7 +36,7 @@ REFERENCE_CPU_IMG_S_PER_WORKER = 104.0     # derived VGG11 M1 throu
 def parse():
     p = argparse.ArgumentParser()
     p.add_argument("--gpus", type=int, default=1)
-    p.add_argument("--steps", type=int, default=30)
+    p.add_argument("--steps", type=int, default=200)
     p.add_argument("--warmup", type=int, default=5)
     p.add_argument("--impl", type=str, default="ewdml", choices=["ewdml", "reference", "nccl"])
     p.add_argument("--model", type=str, default="VGG11")
@@ -66,7 +66,7 @@ class ClockSampler:
         try:
             self.f = open(self.path, "w")
             self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                                          "-lms", "100", "-i", str(self.gpu_index)], stdout=self.f,
+                                          "-lms", "50", "-i", str(self.gpu_index)], stdout=self.f,
                                          stderr=subprocess.DEVNULL)
         except Exception:
             self.proc = None

@@ -217,7 +217,11 @@ __global__ void __launch_bounds__(1024) k_refine(const float* __restrict__ grad,
     bool fallback = false;
     if (cnt_hi <= sg.k && sg.k - cnt_hi <= ncand) {
         uint32_t r = sg.k - cnt_hi;
-        if (r == 0) { thr = si.key_hi - 1; need_eq = 0; }
+        if (r == 0) {
+            // everything at or above key_hi is selected and nothing else; key_hi == 0 means "all"
+            if (si.key_hi == 0) { thr = 0; need_eq = 0xFFFFFFFFu; }
+            else { thr = si.key_hi - 1; need_eq = 0; }
+        }
         else exact_select<false>(keys, raw, ncand, r, h, scan_smem, &s_digit, &s_r, &thr, &need_eq);
     } else {
         fallback = true;                           // the sampled band missed: exact scan of the raw segment

@@ -1,0 +1,343 @@
+// K6 / core of K5: bf16 GEMM on the 5th-generation tensor cores (tcgen05 + TMEM), fed by TMA.
+//
+//   C[M,N] (+)= A[M,K] * B[N,K]^T        A, B: bf16, K contiguous ("K-major");  fp32 accumulation
+//
+// Used for nn.Linear forward/backward (lenet.py:20-21, vgg.py:24-29, resnet.py:77) and, through
+// im2col operands (conv.cu), for every convolution pass (vgg.py:53, resnet.py:19-55).  The reference
+// reaches these through ATen -> cuBLAS/cuDNN library calls; here the kernel is written out:
+//
+//   warp 0   TMA producer: cp.async.bulk.tensor 2D loads of a 128x64 A tile and a BNx64 B tile
+//            (128-byte swizzle) into a STAGES-deep shared-memory ring, completion on mbarriers
+//   warp 1   allocates TMEM, then ONE elected thread issues tcgen05.mma (M=128, N=BN, K=16) four
+//            times per stage with shared-memory descriptors; tcgen05.commit releases the stage and
+//            finally signals the epilogue
+//   warps 2-5  epilogue: tcgen05.ld 32 lanes x 32 columns per warp from TMEM -> registers ->
+//            bias / convert -> global (bf16 store, fp32 store, or fp32 atomic add for split-K and
+//            for weight gradients accumulated straight into the flat gradient buffer)
+//
+// One output tile per CTA, up to two CTAs per SM (3 stages x 32 KB + 128 TMEM columns each), so one
+// CTA's epilogue overlaps the other's main loop.  grid = (M/128, N/BN, split_k).
+#include <cuda.h>
+
+#include <map>
+#include <mutex>
+#include <tuple>
+
+#include "../common.cuh"
+
+namespace {
+
+constexpr int BM = 128;
+constexpr int BK = 64;              // 64 bf16 = 128 bytes = one swizzle row
+constexpr int UMMA_K = 16;
+
+struct GemmArgs {
+    void* C;
+    const float* bias;
+    int M, N, K, ldc;
+    int out_mode;                   // 0: bf16 store, 1: fp32 store, 2: fp32 atomic add
+    int kb_per_split, kb_total;
+    float alpha;
+};
+
+// ---- PTX wrappers -----------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "LAB_WAIT:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra LAB_DONE;\n"
+        "bra LAB_WAIT;\n"
+        "LAB_DONE:\n"
+        "}\n" ::"r"(bar),
+        "r"(parity)
+        : "memory");
+}
+__device__ __forceinline__ void tma_load_2d(uint32_t smem_dst, const CUtensorMap* tmap, uint32_t bar, int c0, int c1) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(smem_dst),
+        "l"(reinterpret_cast<uint64_t>(tmap)), "r"(bar), "r"(c0), "r"(c1)
+        : "memory");
+}
+__device__ __forceinline__ void tcgen05_alloc(uint32_t smem_slot, uint32_t ncols) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_slot), "r"(ncols) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tcgen05_dealloc(uint32_t taddr, uint32_t ncols) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
+}
+__device__ __forceinline__ void tcgen05_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tcgen05_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tcgen05_commit(uint32_t bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void tcgen05_mma_f16(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "setp.ne.b32 p, %4, 0;\n"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n"
+        "}\n" ::"r"(d_tmem),
+        "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+__device__ __forceinline__ void tcgen05_ld_32x32(uint32_t taddr, uint32_t (&r)[32]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+          "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
+          "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
+          "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+        : "r"(taddr)
+        : "memory");
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+// K-major, 128-byte swizzle shared-memory matrix descriptor (rows of 128 B, 8-row groups 1024 B apart)
+__device__ __forceinline__ uint64_t make_smem_desc(uint32_t smem_addr) {
+    uint64_t d = 0;
+    d |= (uint64_t)((smem_addr & 0x3FFFF) >> 4);          // start address        bits [0,14)
+    d |= (uint64_t)1 << 16;                               // leading byte offset  (unused for SW128 K-major)
+    d |= (uint64_t)(1024 >> 4) << 32;                     // stride byte offset   bits [32,46)
+    d |= (uint64_t)1 << 46;                               // descriptor version (sm_100)
+    d |= (uint64_t)2 << 61;                               // layout: SWIZZLE_128B
+    return d;
+}
+// kind::f16 instruction descriptor: D=f32, A=B=bf16, both K-major, M=128, N=BN
+__host__ __device__ constexpr uint32_t make_idesc(int n) {
+    return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+}
+
+template <int BN, int STAGES>
+struct Smem {
+    static constexpr int A_BYTES = BM * BK * 2;
+    static constexpr int B_BYTES = BN * BK * 2;
+    static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+    static constexpr int BAR_OFF = STAGES * STAGE_BYTES;
+    static constexpr int TOTAL = BAR_OFF + 8 * (2 * STAGES + 1) + 16 + 1024;   // + alignment slack
+};
+
+template <int BN, int STAGES>
+__global__ void __launch_bounds__(192) k_gemm_tn_tcgen05(const __grid_constant__ CUtensorMap tmA,
+                                                         const __grid_constant__ CUtensorMap tmB, const GemmArgs g) {
+    using S = Smem<BN, STAGES>;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    const uint32_t smem_base = smem_u32(smem);
+    const uint32_t bar_base = smem_base + S::BAR_OFF;
+    auto full_bar = [&](int s) { return bar_base + 8 * s; };
+    auto empty_bar = [&](int s) { return bar_base + 8 * (STAGES + s); };
+    const uint32_t tmem_full_bar = bar_base + 8 * (2 * STAGES);
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + S::BAR_OFF + 8 * (2 * STAGES + 1));
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int m_tile = blockIdx.x, n_tile = blockIdx.y;
+    const int kb0 = blockIdx.z * g.kb_per_split;
+    const int kb1 = min(g.kb_total, kb0 + g.kb_per_split);
+    const int nkb = kb1 - kb0;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < STAGES; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
+        mbar_init(tmem_full_bar, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    }
+    if (warp == 1) tcgen05_alloc(smem_u32(tmem_slot), BN);
+    tcgen05_fence_before();
+    __syncthreads();
+    tcgen05_fence_after();
+    const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(tmem_slot);
+
+    if (warp == 0) {
+        if (lane == 0 && nkb > 0) {
+            for (int i = 0; i < nkb; ++i) {
+                const int s = i % STAGES;
+                const uint32_t ph = (i / STAGES) & 1;
+                mbar_wait(empty_bar(s), ph ^ 1);
+                mbar_expect_tx(full_bar(s), S::STAGE_BYTES);
+                const uint32_t a_dst = smem_base + s * S::STAGE_BYTES;
+                tma_load_2d(a_dst, &tmA, full_bar(s), (kb0 + i) * BK, m_tile * BM);
+                tma_load_2d(a_dst + S::A_BYTES, &tmB, full_bar(s), (kb0 + i) * BK, n_tile * BN);
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0 && nkb > 0) {
+            constexpr uint32_t idesc = make_idesc(BN);
+            for (int i = 0; i < nkb; ++i) {
+                const int s = i % STAGES;
+                const uint32_t ph = (i / STAGES) & 1;
+                mbar_wait(full_bar(s), ph);
+                tcgen05_fence_after();
+                const uint32_t a_addr = smem_base + s * S::STAGE_BYTES;
+                const uint64_t a_desc = make_smem_desc(a_addr);
+                const uint64_t b_desc = make_smem_desc(a_addr + S::A_BYTES);
+#pragma unroll
+                for (int k = 0; k < BK / UMMA_K; ++k) {
+                    // advance 32 bytes (16 bf16) inside the 128-byte swizzle row: +2 in the (addr >> 4) field
+                    tcgen05_mma_f16(tmem_base, a_desc + (uint64_t)(2 * k), b_desc + (uint64_t)(2 * k), idesc,
+                                    (i > 0 || k > 0) ? 1u : 0u);
+                }
+                tcgen05_commit(empty_bar(s));          // frees the smem stage when these MMAs retire
+            }
+            tcgen05_commit(tmem_full_bar);             // accumulator complete
+        }
+    } else {
+        // ---- epilogue: warps 2..5 own TMEM lane quadrant (warp % 4) -----------------------------
+        const int quad = warp & 3;
+        const int row = m_tile * BM + quad * 32 + lane;
+        if (nkb > 0) {
+            mbar_wait(tmem_full_bar, 0);
+            tcgen05_fence_after();
+        }
+#pragma unroll 1
+        for (int c = 0; c < BN / 32; ++c) {
+            uint32_t v[32];
+            if (nkb > 0) {
+                tcgen05_ld_32x32(tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(c * 32), v);
+            } else {
+#pragma unroll
+                for (int j = 0; j < 32; ++j) v[j] = 0;
+            }
+            const int col0 = n_tile * BN + c * 32;
+            if (row >= g.M || col0 >= g.N) continue;
+            float f[32];
+#pragma unroll
+            for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]) * g.alpha;
+            if (g.bias != nullptr && blockIdx.z == 0) {
+#pragma unroll
+                for (int j = 0; j < 32; ++j)
+                    if (col0 + j < g.N) f[j] += g.bias[col0 + j];
+            }
+            const bool full = col0 + 32 <= g.N;
+            if (g.out_mode == 0) {
+                __nv_bfloat16* out = reinterpret_cast<__nv_bfloat16*>(g.C) + (size_t)row * g.ldc + col0;
+                if (full && (g.ldc % 8 == 0)) {
+#pragma unroll
+                    for (int j = 0; j < 32; j += 8) {
+                        uint4 pk;
+                        __nv_bfloat162 p0 = __floats2bfloat162_rn(f[j], f[j + 1]), p1 = __floats2bfloat162_rn(f[j + 2], f[j + 3]);
+                        __nv_bfloat162 p2 = __floats2bfloat162_rn(f[j + 4], f[j + 5]), p3 = __floats2bfloat162_rn(f[j + 6], f[j + 7]);
+                        pk.x = *reinterpret_cast<uint32_t*>(&p0); pk.y = *reinterpret_cast<uint32_t*>(&p1);
+                        pk.z = *reinterpret_cast<uint32_t*>(&p2); pk.w = *reinterpret_cast<uint32_t*>(&p3);
+                        *reinterpret_cast<uint4*>(out + j) = pk;
+                    }
+                } else {
+                    for (int j = 0; j < 32 && col0 + j < g.N; ++j) out[j] = __float2bfloat16_rn(f[j]);
+                }
+            } else if (g.out_mode == 1) {
+                float* out = reinterpret_cast<float*>(g.C) + (size_t)row * g.ldc + col0;
+                if (full && (g.ldc % 4 == 0)) {
+#pragma unroll
+                    for (int j = 0; j < 32; j += 4) *reinterpret_cast<float4*>(out + j) = make_float4(f[j], f[j + 1], f[j + 2], f[j + 3]);
+                } else {
+                    for (int j = 0; j < 32 && col0 + j < g.N; ++j) out[j] = f[j];
+                }
+            } else {
+                float* out = reinterpret_cast<float*>(g.C) + (size_t)row * g.ldc + col0;
+                for (int j = 0; j < 32 && col0 + j < g.N; ++j) atomicAdd(out + j, f[j]);
+            }
+        }
+    }
+    tcgen05_fence_before();
+    __syncthreads();
+    if (warp == 1) tcgen05_dealloc(tmem_base, BN);
+}
+
+// ---- host side ----------------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn get_encode() {
+    static EncodeTiledFn fn = nullptr;
+    if (!fn) {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess && p)
+            fn = reinterpret_cast<EncodeTiledFn>(p);
+    }
+    return fn;
+}
+
+// 2-D bf16 tensor map: inner dim = K (contiguous), outer dim = rows, row pitch ld elements
+int make_tmap(CUtensorMap* tm, const void* base, int64_t rows, int64_t k, int64_t ld, int box_rows) {
+    EncodeTiledFn enc = get_encode();
+    if (!enc) { ewdml_set_error("cuTensorMapEncodeTiled not available"); return EWDML_ERR_CUDA; }
+    cuuint64_t dims[2] = {(cuuint64_t)k, (cuuint64_t)rows};
+    cuuint64_t strides[1] = {(cuuint64_t)ld * 2};
+    cuuint32_t box[2] = {(cuuint32_t)BK, (cuuint32_t)box_rows};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = enc(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        ewdml_set_error("cuTensorMapEncodeTiled failed (%d) base=%p rows=%lld k=%lld ld=%lld", (int)r, base, (long long)rows,
+                        (long long)k, (long long)ld);
+        return EWDML_ERR_CUDA;
+    }
+    return 0;
+}
+
+template <int BN, int STAGES>
+int launch(const CUtensorMap& tA, const CUtensorMap& tB, const GemmArgs& g, int split, cudaStream_t st) {
+    using S = Smem<BN, STAGES>;
+    static bool attr = false;
+    if (!attr) {
+        EWDML_CUDA(cudaFuncSetAttribute(k_gemm_tn_tcgen05<BN, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize, S::TOTAL));
+        attr = true;
+    }
+    dim3 grid((g.M + BM - 1) / BM, (g.N + BN - 1) / BN, split);
+    k_gemm_tn_tcgen05<BN, STAGES><<<grid, 192, S::TOTAL, st>>>(tA, tB, g);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) { ewdml_set_error("gemm launch failed: %s", cudaGetErrorString(e)); return (int)e; }
+    ewdml_counter_add(EWDML_CTR_COMPUTE_LAUNCHES, 1);
+    return 0;
+}
+
+}  // namespace
+
+// C[M,N] (op)= alpha * A[M,K] B[N,K]^T (+ bias[N]).  lda/ldb/ldc in elements; A,B bf16 with K % 8 == 0
+// and 16-byte aligned bases/pitches.  out_mode 0: bf16 store, 1: fp32 store, 2: fp32 atomic accumulate
+// (C must hold the running sum; bias is added once).  split_k <= 0 picks a split that fills the GPU.
+extern "C" int ewdml_gemm_bf16_tn(const void* A, const void* B, void* C, int M, int N, int K, int lda, int ldb, int ldc,
+                                  int out_mode, const float* bias, float alpha, int split_k, void* stream) {
+    EWDML_CHECK_ARG(A && B && C && M > 0 && N > 0 && K > 0);
+    EWDML_CHECK_ARG(lda % 8 == 0 && ldb % 8 == 0 && ((uintptr_t)A % 16) == 0 && ((uintptr_t)B % 16) == 0);
+    EWDML_CHECK_ARG(out_mode >= 0 && out_mode <= 2);
+    const int bn = N <= 64 ? 64 : 128;
+    GemmArgs g;
+    g.C = C; g.bias = bias; g.M = M; g.N = N; g.K = K; g.ldc = ldc; g.out_mode = out_mode; g.alpha = alpha;
+    g.kb_total = (K + BK - 1) / BK;
+    int tiles = ((M + BM - 1) / BM) * ((N + bn - 1) / bn);
+    int split = split_k;
+    if (split <= 0) {
+        split = 1;
+        if (out_mode == 2) {                       // only the accumulate mode may be split
+            int target = 2 * 148;
+            while (tiles * split * 2 <= target && split * 2 <= g.kb_total / 2) split *= 2;
+        }
+    }
+    if (split > 1 && out_mode != 2) { ewdml_set_error("split-K needs out_mode 2 (atomic accumulate)"); return EWDML_ERR_ARG; }
+    if (split > g.kb_total) split = g.kb_total;
+    g.kb_per_split = (g.kb_total + split - 1) / split;
+    split = (g.kb_total + g.kb_per_split - 1) / g.kb_per_split;     // no empty splits
+    CUtensorMap tA, tB;
+    int rc = make_tmap(&tA, A, M, K, lda, BM);
+    if (rc) return rc;
+    rc = make_tmap(&tB, B, N, K, ldb, bn);
+    if (rc) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (bn == 64) return launch<64, 4>(tA, tB, g, split, st);
+    return launch<128, 3>(tA, tB, g, split, st);
+}

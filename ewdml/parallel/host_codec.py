@@ -74,13 +74,16 @@ class HostCodec:
     """Encode/decode a flat gradient vector <-> one uint8 message."""
 
     def __init__(self, segments: List[Segment], compressor: str, qsgd_levels: int = 128,
-                 topk_ratio: float = 0.5, seed: int = 0, rank: int = 0):
+                 topk_ratio: float = 0.5, seed: int = 0, rank: int = 0, precise_norm: bool = False):
         self.segments = segments
         self.compressor = compressor
         self.s = int(qsgd_levels)
         self.ratio = float(topk_ratio)
         self.seed = seed
         self.rank = rank
+        # torch's fp32 norm over ~1e6 elements is only good to ~1e-4 relative; the CUDA kernels sum in
+        # fp64, so the oracle used by the GPU tests does too
+        self.precise_norm = precise_norm
         self.sizes = [self._seg_nbytes(seg) for seg in segments]
         self.offsets = np.concatenate([[0], np.cumsum(self.sizes)]).astype(np.int64)
         self.nbytes = int(self.offsets[-1])
@@ -103,6 +106,9 @@ class HostCodec:
             return 4 + _levels_nbytes(k, self.s) + 4 * k
         raise ValueError(c)
 
+    def _norm(self, t: torch.Tensor):
+        return t.double().norm().float() if self.precise_norm else None
+
     # stream id separates the draws of different senders (rank) so workers are independent
     def _uniform(self, idx: torch.Tensor, step: int) -> torch.Tensor:
         return uniform_for_indices(idx, self.seed, step, stream=self.rank)
@@ -118,7 +124,7 @@ class HostCodec:
                 dst.copy_(g.contiguous().view(torch.uint8))
             elif c == "qsgd":
                 idx = torch.arange(seg.offset, seg.offset + seg.numel)
-                q, norm = qsgd_quantize(g, self.s, self._uniform(idx, step))
+                q, norm = qsgd_quantize(g, self.s, self._uniform(idx, step), norm=self._norm(g))
                 dst[:4].copy_(norm.view(torch.uint8))
                 dst[4:].copy_(_pack_levels(q, self.s))
             elif c == "topk":
@@ -129,7 +135,7 @@ class HostCodec:
             else:  # topk-qsgd
                 vals, idx = sparsify(g, self.ratio)
                 k = vals.numel()
-                q, norm = qsgd_quantize(vals, self.s, self._uniform(idx + seg.offset, step))
+                q, norm = qsgd_quantize(vals, self.s, self._uniform(idx + seg.offset, step), norm=self._norm(vals))
                 lb = _levels_nbytes(k, self.s)
                 dst[:4].copy_(norm.view(torch.uint8))
                 dst[4:4 + lb].copy_(_pack_levels(q, self.s))

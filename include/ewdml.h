@@ -169,6 +169,19 @@ void ewdml_peer_matrix_add(int peer, int64_t bytes);             /* per-peer byt
 int ewdml_peer_matrix_get(int64_t out[EWDML_MAX_PEERS]);
 void ewdml_set_trace(int on);                                    /* libompitrace analogue        */
 
+/* ------------------------------------------------------------------------------------------
+ * Compute kernels (K5-K9).  Activations are NHWC bf16; weights are bf16 copies of the fp32 master
+ * parameters in [C_out][kh][kw][C_in] order; all entry points enqueue on `stream`.
+ * ------------------------------------------------------------------------------------------ */
+
+/* K6: C[M,N] (op)= alpha * A[M,K] * B[N,K]^T (+ bias[N]) on tcgen05/TMEM with TMA-fed operands.
+ * A, B bf16 with K contiguous, lda/ldb multiples of 8.  out_mode 0 = bf16 store, 1 = fp32 store,
+ * 2 = fp32 atomic accumulate (split-K; weight gradients accumulate straight into the flat gradient
+ * buffer).  split_k <= 0 chooses automatically.  Replaces nn.Linear / the GEMM inside nn.Conv2d
+ * (lenet.py:18-21, vgg.py:24-29,53, resnet.py:19-77), which the reference runs through ATen.      */
+int ewdml_gemm_bf16_tn(const void* A, const void* B, void* C, int M, int N, int K, int lda, int ldb,
+                       int ldc, int out_mode, const float* bias, float alpha, int split_k, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

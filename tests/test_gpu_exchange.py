@@ -76,14 +76,15 @@ class Emu:
                 self.plans[r].recv_apply(srcs, q, float(self.W), L.OUT_GRAD, out=out)
                 outs.append(out)
             else:
-                self.plans[r].recv_apply(srcs, q, float(self.W), out_mode, **kw[r])
+                self.plans[r].recv_apply(srcs, q, float(self.W), out_mode, **kw["kw"][r])
         torch.cuda.synchronize()
         return outs
 
     def oracle(self, grads, step=0):
         acc = torch.zeros(self.total)
         for r in range(self.W):
-            codec = HostCodec(self.segs, self.compressor, self.levels, self.ratio, seed=self.seed, rank=r)
+            codec = HostCodec(self.segs, self.compressor, self.levels, self.ratio, seed=self.seed, rank=r,
+                              precise_norm=True)
             codec.decode(codec.encode(grads[r].cpu(), step), out=acc, accumulate=True, total=self.total)
         return acc / self.W
 

@@ -1,0 +1,58 @@
+"""tcgen05/TMEM GEMM vs a plain PyTorch fp32 reference of the same bf16 operands."""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+SHAPES = [(128, 128, 64), (256, 128, 128), (128, 64, 512), (100, 72, 96), (2048, 512, 4608), (8192, 256, 1152),
+          (64, 10, 512), (131072, 64, 32), (333, 500, 808), (512, 512, 4608)]
+
+
+def _ref(a, b, bias=None, alpha=1.0):
+    r = alpha * (a.float() @ b.float().t())
+    return r + bias if bias is not None else r
+
+
+@pytest.mark.parametrize("M,N,K", SHAPES)
+def test_gemm_bf16_out(M, N, K):
+    from ewdml.ops import native
+    torch.manual_seed(M + N + K)
+    a = torch.randn(M, K, device="cuda").bfloat16()
+    b = torch.randn(N, K, device="cuda").bfloat16()
+    bias = torch.randn(N, device="cuda")
+    out = native.gemm_tn(a, b, bias=bias)
+    torch.cuda.synchronize()
+    ref = _ref(a, b, bias)
+    err = (out.float() - ref).abs().max().item()
+    assert err <= 2e-2 * ref.abs().max().item() + 1e-3, err
+
+
+@pytest.mark.parametrize("M,N,K", SHAPES[:7])
+def test_gemm_f32_and_accumulate_splitk(M, N, K):
+    from ewdml.ops import native
+    torch.manual_seed(1)
+    a = torch.randn(M, K, device="cuda").bfloat16()
+    b = torch.randn(N, K, device="cuda").bfloat16()
+    ref = _ref(a, b, alpha=0.5)
+    out = native.gemm_tn(a, b, out_mode=native.OUT_F32, alpha=0.5)
+    torch.cuda.synchronize()
+    tol = 1e-3 * ref.abs().max().item() + 1e-4
+    assert (out - ref).abs().max().item() <= tol
+    base = torch.randn(M, N, device="cuda")
+    acc = base.clone()
+    native.gemm_tn(a, b, out=acc, out_mode=native.OUT_ACCUM, alpha=0.5)           # auto split-K
+    native.gemm_tn(a, b, out=acc, out_mode=native.OUT_ACCUM, alpha=0.5, split_k=3)
+    torch.cuda.synchronize()
+    assert (acc - (base + 2 * ref)).abs().max().item() <= 4 * tol
+
+
+def test_gemm_strided_operands():
+    from ewdml.ops import native
+    torch.manual_seed(2)
+    big_a = torch.randn(300, 256, device="cuda").bfloat16()
+    big_b = torch.randn(200, 512, device="cuda").bfloat16()
+    a, b = big_a[:, :128], big_b[:, 64:192]
+    out = native.gemm_tn(a, b)
+    torch.cuda.synchronize()
+    ref = _ref(a, b)
+    assert (out.float() - ref).abs().max().item() <= 2e-2 * ref.abs().max().item()
