@@ -114,9 +114,23 @@ __device__ __forceinline__ uint64_t make_smem_desc(uint32_t smem_addr) {
     d |= (uint64_t)2 << 61;                               // layout: SWIZZLE_128B
     return d;
 }
-// kind::f16 instruction descriptor: D=f32, A=B=bf16, both K-major, M=128, N=BN
-__host__ __device__ constexpr uint32_t make_idesc(int n) {
-    return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+// MN-major, 128-byte swizzle: the tile is stored as [MN/64] slabs of [64 k-rows][64 mn] (128 B per k-row);
+// 8 k-rows x 128 B form one 1024-byte swizzle atom.  Canonical layout ((8,n),(8,k)):((1,LBO),(8,SBO)) in
+// 16-byte units: LBO = distance between 64-wide MN slabs (64 rows x 128 B), SBO = distance between atoms
+// along K (1024 B).
+__device__ __forceinline__ uint64_t make_smem_desc_mn(uint32_t smem_addr) {
+    uint64_t d = 0;
+    d |= (uint64_t)((smem_addr & 0x3FFFF) >> 4);
+    d |= (uint64_t)((BK * 128) >> 4) << 16;               // LBO: next 64-element MN slab
+    d |= (uint64_t)(1024 >> 4) << 32;                     // SBO: next group of 8 k-rows
+    d |= (uint64_t)1 << 46;
+    d |= (uint64_t)2 << 61;
+    return d;
+}
+// kind::f16 instruction descriptor: D=f32, A=B=bf16, M=128, N=BN; bit 15/16 = A/B is MN-major
+__host__ __device__ constexpr uint32_t make_idesc(int n, bool a_mn, bool b_mn) {
+    return (1u << 4) | (1u << 7) | (1u << 10) | ((a_mn ? 1u : 0u) << 15) | ((b_mn ? 1u : 0u) << 16) |
+           ((uint32_t)(n >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
 }
 
 template <int BN, int STAGES>
@@ -128,8 +142,8 @@ struct Smem {
     static constexpr int TOTAL = BAR_OFF + 8 * (2 * STAGES + 1) + 16 + 1024;   // + alignment slack
 };
 
-template <int BN, int STAGES>
-__global__ void __launch_bounds__(192) k_gemm_tn_tcgen05(const __grid_constant__ CUtensorMap tmA,
+template <int BN, int STAGES, bool A_MN, bool B_MN>
+__global__ void __launch_bounds__(192) k_gemm_tcgen05(const __grid_constant__ CUtensorMap tmA,
                                                          const __grid_constant__ CUtensorMap tmB, const GemmArgs g) {
     using S = Smem<BN, STAGES>;
     extern __shared__ uint8_t smem_raw[];
@@ -167,26 +181,39 @@ __global__ void __launch_bounds__(192) k_gemm_tn_tcgen05(const __grid_constant__
                 mbar_wait(empty_bar(s), ph ^ 1);
                 mbar_expect_tx(full_bar(s), S::STAGE_BYTES);
                 const uint32_t a_dst = smem_base + s * S::STAGE_BYTES;
-                tma_load_2d(a_dst, &tmA, full_bar(s), (kb0 + i) * BK, m_tile * BM);
-                tma_load_2d(a_dst + S::A_BYTES, &tmB, full_bar(s), (kb0 + i) * BK, n_tile * BN);
+                const int k0 = (kb0 + i) * BK;
+                if constexpr (A_MN) {            // box = [64 k-rows][64 mn]: one slab per 64 rows of the tile
+#pragma unroll
+                    for (int h = 0; h < BM / 64; ++h) tma_load_2d(a_dst + h * (BK * 128), &tmA, full_bar(s), m_tile * BM + h * 64, k0);
+                } else {
+                    tma_load_2d(a_dst, &tmA, full_bar(s), k0, m_tile * BM);
+                }
+                if constexpr (B_MN) {
+#pragma unroll
+                    for (int h = 0; h < BN / 64; ++h)
+                        tma_load_2d(a_dst + S::A_BYTES + h * (BK * 128), &tmB, full_bar(s), n_tile * BN + h * 64, k0);
+                } else {
+                    tma_load_2d(a_dst + S::A_BYTES, &tmB, full_bar(s), k0, n_tile * BN);
+                }
             }
         }
     } else if (warp == 1) {
         if (lane == 0 && nkb > 0) {
-            constexpr uint32_t idesc = make_idesc(BN);
+            constexpr uint32_t idesc = make_idesc(BN, A_MN, B_MN);
             for (int i = 0; i < nkb; ++i) {
                 const int s = i % STAGES;
                 const uint32_t ph = (i / STAGES) & 1;
                 mbar_wait(full_bar(s), ph);
                 tcgen05_fence_after();
                 const uint32_t a_addr = smem_base + s * S::STAGE_BYTES;
-                const uint64_t a_desc = make_smem_desc(a_addr);
-                const uint64_t b_desc = make_smem_desc(a_addr + S::A_BYTES);
+                const uint64_t a_desc = A_MN ? make_smem_desc_mn(a_addr) : make_smem_desc(a_addr);
+                const uint64_t b_desc = B_MN ? make_smem_desc_mn(a_addr + S::A_BYTES) : make_smem_desc(a_addr + S::A_BYTES);
+                // per UMMA_K = 16 step: K-major advances 32 B inside the swizzle row (+2 in addr>>4 units),
+                // MN-major advances 16 k-rows = two 1024-byte atoms (+128)
+                constexpr uint64_t a_step = A_MN ? 128 : 2, b_step = B_MN ? 128 : 2;
 #pragma unroll
                 for (int k = 0; k < BK / UMMA_K; ++k) {
-                    // advance 32 bytes (16 bf16) inside the 128-byte swizzle row: +2 in the (addr >> 4) field
-                    tcgen05_mma_f16(tmem_base, a_desc + (uint64_t)(2 * k), b_desc + (uint64_t)(2 * k), idesc,
-                                    (i > 0 || k > 0) ? 1u : 0u);
+                    tcgen05_mma_f16(tmem_base, a_desc + a_step * k, b_desc + b_step * k, idesc, (i > 0 || k > 0) ? 1u : 0u);
                 }
                 tcgen05_commit(empty_bar(s));          // frees the smem stage when these MMAs retire
             }
@@ -270,13 +297,15 @@ EncodeTiledFn get_encode() {
     return fn;
 }
 
-// 2-D bf16 tensor map: inner dim = K (contiguous), outer dim = rows, row pitch ld elements
+// 2-D bf16 tensor map over a row-major matrix [outer][inner] with row pitch ld elements.
+// K-major operand: inner = K, outer = rows (M or N), box {64, box_rows}.
+// MN-major operand: inner = MN, outer = K (reduction), box {64, 64}.
 int make_tmap(CUtensorMap* tm, const void* base, int64_t rows, int64_t k, int64_t ld, int box_rows) {
     EncodeTiledFn enc = get_encode();
     if (!enc) { ewdml_set_error("cuTensorMapEncodeTiled not available"); return EWDML_ERR_CUDA; }
     cuuint64_t dims[2] = {(cuuint64_t)k, (cuuint64_t)rows};
     cuuint64_t strides[1] = {(cuuint64_t)ld * 2};
-    cuuint32_t box[2] = {(cuuint32_t)BK, (cuuint32_t)box_rows};
+    cuuint32_t box[2] = {(cuuint32_t)64, (cuuint32_t)box_rows};
     cuuint32_t estr[2] = {1, 1};
     CUresult r = enc(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
                      CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
@@ -289,29 +318,25 @@ int make_tmap(CUtensorMap* tm, const void* base, int64_t rows, int64_t k, int64_
     return 0;
 }
 
-template <int BN, int STAGES>
+template <int BN, int STAGES, bool A_MN, bool B_MN>
 int launch(const CUtensorMap& tA, const CUtensorMap& tB, const GemmArgs& g, int split, cudaStream_t st) {
     using S = Smem<BN, STAGES>;
     static bool attr = false;
     if (!attr) {
-        EWDML_CUDA(cudaFuncSetAttribute(k_gemm_tn_tcgen05<BN, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize, S::TOTAL));
+        EWDML_CUDA(cudaFuncSetAttribute(k_gemm_tcgen05<BN, STAGES, A_MN, B_MN>, cudaFuncAttributeMaxDynamicSharedMemorySize, S::TOTAL));
         attr = true;
     }
     dim3 grid((g.M + BM - 1) / BM, (g.N + BN - 1) / BN, split);
-    k_gemm_tn_tcgen05<BN, STAGES><<<grid, 192, S::TOTAL, st>>>(tA, tB, g);
+    k_gemm_tcgen05<BN, STAGES, A_MN, B_MN><<<grid, 192, S::TOTAL, st>>>(tA, tB, g);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) { ewdml_set_error("gemm launch failed: %s", cudaGetErrorString(e)); return (int)e; }
     ewdml_counter_add(EWDML_CTR_COMPUTE_LAUNCHES, 1);
     return 0;
 }
 
-}  // namespace
-
-// C[M,N] (op)= alpha * A[M,K] B[N,K]^T (+ bias[N]).  lda/ldb/ldc in elements; A,B bf16 with K % 8 == 0
-// and 16-byte aligned bases/pitches.  out_mode 0: bf16 store, 1: fp32 store, 2: fp32 atomic accumulate
-// (C must hold the running sum; bias is added once).  split_k <= 0 picks a split that fills the GPU.
-extern "C" int ewdml_gemm_bf16_tn(const void* A, const void* B, void* C, int M, int N, int K, int lda, int ldb, int ldc,
-                                  int out_mode, const float* bias, float alpha, int split_k, void* stream) {
+template <bool A_MN, bool B_MN>
+int gemm_dispatch(const void* A, const void* B, void* C, int M, int N, int K, int lda, int ldb, int ldc, int out_mode,
+                  const float* bias, float alpha, int split_k, void* stream) {
     EWDML_CHECK_ARG(A && B && C && M > 0 && N > 0 && K > 0);
     EWDML_CHECK_ARG(lda % 8 == 0 && ldb % 8 == 0 && ((uintptr_t)A % 16) == 0 && ((uintptr_t)B % 16) == 0);
     EWDML_CHECK_ARG(out_mode >= 0 && out_mode <= 2);
@@ -333,11 +358,33 @@ extern "C" int ewdml_gemm_bf16_tn(const void* A, const void* B, void* C, int M, 
     g.kb_per_split = (g.kb_total + split - 1) / split;
     split = (g.kb_total + g.kb_per_split - 1) / g.kb_per_split;     // no empty splits
     CUtensorMap tA, tB;
-    int rc = make_tmap(&tA, A, M, K, lda, BM);
+    // K-major: matrix is [rows][K]; MN-major: matrix is [K][rows] (rows contiguous)
+    int rc = A_MN ? make_tmap(&tA, A, K, M, lda, 64) : make_tmap(&tA, A, M, K, lda, BM);
     if (rc) return rc;
-    rc = make_tmap(&tB, B, N, K, ldb, bn);
+    rc = B_MN ? make_tmap(&tB, B, K, N, ldb, 64) : make_tmap(&tB, B, N, K, ldb, bn);
     if (rc) return rc;
     cudaStream_t st = (cudaStream_t)stream;
-    if (bn == 64) return launch<64, 4>(tA, tB, g, split, st);
-    return launch<128, 3>(tA, tB, g, split, st);
+    if (bn == 64) return launch<64, 4, A_MN, B_MN>(tA, tB, g, split, st);
+    return launch<128, 3, A_MN, B_MN>(tA, tB, g, split, st);
+}
+
+}  // namespace
+
+// C[M,N] (op)= alpha * op(A) op(B) (+ bias[N]), bf16 operands, fp32 accumulation in TMEM.
+//   a_mn = 0: A is [M][K] (K contiguous);  a_mn = 1: A is [K][M] (M contiguous)
+//   b_mn = 0: B is [N][K] (K contiguous);  b_mn = 1: B is [K][N] (N contiguous)
+// so (0,0) = x W^T (forward), (0,1) = dy W (data gradient), (1,1) = dy^T x (weight gradient) without
+// any transposed copies.  Leading dimensions in elements (multiples of 8), bases 16-byte aligned.
+// out_mode 0: bf16 store, 1: fp32 store, 2: fp32 atomic accumulate (split-K).  split_k <= 0: automatic.
+extern "C" int ewdml_gemm_bf16(const void* A, const void* B, void* C, int M, int N, int K, int lda, int ldb, int ldc,
+                               int a_mn, int b_mn, int out_mode, const float* bias, float alpha, int split_k, void* stream) {
+    if (!a_mn && !b_mn) return gemm_dispatch<false, false>(A, B, C, M, N, K, lda, ldb, ldc, out_mode, bias, alpha, split_k, stream);
+    if (!a_mn && b_mn) return gemm_dispatch<false, true>(A, B, C, M, N, K, lda, ldb, ldc, out_mode, bias, alpha, split_k, stream);
+    if (a_mn && b_mn) return gemm_dispatch<true, true>(A, B, C, M, N, K, lda, ldb, ldc, out_mode, bias, alpha, split_k, stream);
+    return gemm_dispatch<true, false>(A, B, C, M, N, K, lda, ldb, ldc, out_mode, bias, alpha, split_k, stream);
+}
+
+extern "C" int ewdml_gemm_bf16_tn(const void* A, const void* B, void* C, int M, int N, int K, int lda, int ldb, int ldc,
+                                  int out_mode, const float* bias, float alpha, int split_k, void* stream) {
+    return ewdml_gemm_bf16(A, B, C, M, N, K, lda, ldb, ldc, 0, 0, out_mode, bias, alpha, split_k, stream);
 }

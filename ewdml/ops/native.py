@@ -21,8 +21,8 @@ def _l():
     if _lib is None:
         _lib = L.load()
         vp, i32, f32 = C.c_void_p, C.c_int, C.c_float
-        _lib.ewdml_gemm_bf16_tn.restype = i32
-        _lib.ewdml_gemm_bf16_tn.argtypes = [vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, vp, f32, i32, vp]
+        _lib.ewdml_gemm_bf16.restype = i32
+        _lib.ewdml_gemm_bf16.argtypes = [vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, i32, vp, f32, i32, vp]
     return _lib
 
 
@@ -37,18 +37,30 @@ def _p(t: Optional[torch.Tensor]):
 OUT_BF16, OUT_F32, OUT_ACCUM = 0, 1, 2
 
 
-def gemm_tn(a: torch.Tensor, b: torch.Tensor, out: Optional[torch.Tensor] = None, out_mode: int = OUT_BF16,
-            bias: Optional[torch.Tensor] = None, alpha: float = 1.0, split_k: int = 0) -> torch.Tensor:
-    """``out (op)= alpha * a @ b.T (+ bias)`` with a:[M,K], b:[N,K] bf16 (row pitch may exceed K)."""
+def gemm(a: torch.Tensor, b: torch.Tensor, a_mn: bool = False, b_mn: bool = False,
+         out: Optional[torch.Tensor] = None, out_mode: int = OUT_BF16, bias: Optional[torch.Tensor] = None,
+         alpha: float = 1.0, split_k: int = 0) -> torch.Tensor:
+    """tcgen05 GEMM ``out (op)= alpha * op(a) @ op(b) (+ bias)`` on bf16 row-major matrices.
+
+    ``a_mn=False``: a is [M, K];  ``a_mn=True``: a is [K, M] (used as its transpose).
+    ``b_mn=False``: b is [N, K];  ``b_mn=True``: b is [K, N].
+    Row pitches may exceed the logical width (views of wider matrices are fine).
+    """
     assert a.dtype == torch.bfloat16 and b.dtype == torch.bfloat16 and a.dim() == 2 and b.dim() == 2
-    assert a.stride(1) == 1 and b.stride(1) == 1 and a.shape[1] == b.shape[1]
-    M, K = a.shape
-    N = b.shape[0]
+    assert a.stride(1) == 1 and b.stride(1) == 1
+    (K, M) = a.shape if a_mn else (a.shape[1], a.shape[0])
+    (Kb, N) = b.shape if b_mn else (b.shape[1], b.shape[0])
+    assert K == Kb, (a.shape, b.shape, a_mn, b_mn)
     if out is None:
         out = torch.empty(M, N, dtype=torch.bfloat16 if out_mode == OUT_BF16 else torch.float32, device=a.device)
         if out_mode == OUT_ACCUM:
             out.zero_()
-    assert out.stride(1) == 1
-    L.check(_l().ewdml_gemm_bf16_tn(_p(a), _p(b), _p(out), M, N, K, a.stride(0), b.stride(0), out.stride(0), out_mode,
-                                    _p(bias), float(alpha), split_k, _stream()), "gemm_bf16_tn")
+    assert out.stride(-1) == 1
+    ldc = out.stride(0) if out.dim() == 2 else N
+    L.check(_l().ewdml_gemm_bf16(_p(a), _p(b), _p(out), M, N, K, a.stride(0), b.stride(0), ldc, int(a_mn), int(b_mn),
+                                 out_mode, _p(bias), float(alpha), split_k, _stream()), "gemm_bf16")
     return out
+
+
+def gemm_tn(a, b, **kw):
+    return gemm(a, b, False, False, **kw)

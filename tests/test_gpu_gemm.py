@@ -56,3 +56,29 @@ def test_gemm_strided_operands():
     torch.cuda.synchronize()
     ref = _ref(a, b)
     assert (out.float() - ref).abs().max().item() <= 2e-2 * ref.abs().max().item()
+
+
+@pytest.mark.parametrize("M,N,K", [(128, 128, 64), (256, 192, 128), (100, 72, 96), (512, 576, 32768), (64, 27, 131072),
+                                   (2048, 2304, 512), (333, 500, 808)])
+@pytest.mark.parametrize("a_mn,b_mn", [(False, True), (True, True), (True, False)])
+def test_gemm_mn_major_operands(M, N, K, a_mn, b_mn):
+    """dgrad (A K-major, B MN-major) and wgrad (both MN-major) forms: no transposed copies."""
+    from ewdml.ops import native
+    torch.manual_seed(3)
+    if max(M, N) * K > 4e8:
+        pytest.skip("too large")
+    # pitches must be multiples of 8 elements: pad the contiguous dimension of MN-major operands
+    def mk(rows, cols):
+        pitch = (cols + 7) // 8 * 8
+        return torch.randn(rows, pitch, device="cuda").bfloat16()[:, :cols]
+    a = mk(K, M) if a_mn else mk(M, K)
+    b = mk(K, N) if b_mn else mk(N, K)
+    if (not a_mn and K % 8) or (not b_mn and K % 8):
+        pytest.skip("K-major operands need K % 8 == 0")
+    A = a.float().t() if a_mn else a.float()
+    B = b.float() if b_mn else b.float().t()
+    ref = A @ B
+    out = native.gemm(a, b, a_mn, b_mn, out_mode=native.OUT_ACCUM)
+    torch.cuda.synchronize()
+    tol = 2e-3 * ref.abs().max().item() + 1e-3
+    assert (out - ref).abs().max().item() <= tol
