@@ -1,0 +1,608 @@
+// K5 (operand builders), K7, K8, K9: the memory-bound layers around the tcgen05 GEMM.
+//
+// Activations are bf16, NHWC.  A convolution pass is
+//   fprop : col = im2col(x)            ; y  = col  * W^T      (GEMM, K-major/K-major)
+//   wgrad : dW += dy^T * col                                   (GEMM, MN-major/MN-major, split-K, fp32 atomics
+//                                                               straight into the flat gradient buffer)
+//   dgrad : dcol = dy * W               ; dx = col2im(dcol)    (GEMM, K-major/MN-major)
+// and BatchNorm / ReLU / residual add / 2x2 max-pool are fused into one statistics pass plus one
+// normalise-activate(-pool) pass forward, and one reduce pass plus one apply pass backward.
+// Reference sites: nn.Conv2d / BatchNorm2d / ReLU / MaxPool2d / avg_pool2d / Dropout / CrossEntropyLoss in
+// src/model_ops/{lenet,vgg,resnet}.py and distributed_worker.py:103 -- all ATen library calls there.
+#include "../common.cuh"
+
+namespace {
+
+struct ConvGeom {
+    int N, H, W, C;          // input
+    int KH, KW, stride, pad;
+    int HO, WO;              // output spatial
+    int K, Kp;               // K = KH*KW*C, Kp = row pitch of col (multiple of 8)
+};
+
+__device__ __forceinline__ float bf16lo(uint32_t v) { return __uint_as_float(v << 16); }
+__device__ __forceinline__ float bf16hi(uint32_t v) { return __uint_as_float(v & 0xFFFF0000u); }
+__device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
+    __nv_bfloat162 p = __floats2bfloat162_rn(a, b);
+    return *reinterpret_cast<uint32_t*>(&p);
+}
+__device__ __forceinline__ void unpack8(const uint4& v, float (&f)[8]) {
+    f[0] = bf16lo(v.x); f[1] = bf16hi(v.x); f[2] = bf16lo(v.y); f[3] = bf16hi(v.y);
+    f[4] = bf16lo(v.z); f[5] = bf16hi(v.z); f[6] = bf16lo(v.w); f[7] = bf16hi(v.w);
+}
+__device__ __forceinline__ uint4 pack8(const float (&f)[8]) {
+    return make_uint4(pack_bf16(f[0], f[1]), pack_bf16(f[2], f[3]), pack_bf16(f[4], f[5]), pack_bf16(f[6], f[7]));
+}
+
+// ---------------------------------------------------------------------------------------------
+// im2col / col2im
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_im2col_vec8(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ col, ConvGeom g, int64_t total) {
+    const int c8n = g.C >> 3, taps = g.KH * g.KW;
+    for (int64_t t = (int64_t)blockIdx.x * 256 + threadIdx.x; t < total; t += (int64_t)gridDim.x * 256) {
+        const int c8 = (int)(t % c8n);
+        const int64_t r = t / c8n;
+        const int tap = (int)(r % taps);
+        const int64_t m = r / taps;
+        const int wo = (int)(m % g.WO), ho = (int)((m / g.WO) % g.HO), n = (int)(m / ((int64_t)g.WO * g.HO));
+        const int h = ho * g.stride - g.pad + tap / g.KW, w = wo * g.stride - g.pad + tap % g.KW;
+        uint4 v = make_uint4(0, 0, 0, 0);
+        if (h >= 0 && h < g.H && w >= 0 && w < g.W)
+            v = *reinterpret_cast<const uint4*>(x + (((int64_t)n * g.H + h) * g.W + w) * g.C + c8 * 8);
+        *reinterpret_cast<uint4*>(col + m * g.Kp + (int64_t)tap * g.C + c8 * 8) = v;
+    }
+}
+
+// any C (1, 3, 20 ...): one element per thread, zero padding of [K, Kp)
+__global__ void __launch_bounds__(256) k_im2col_scalar(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ col, ConvGeom g, int64_t total) {
+    for (int64_t t = (int64_t)blockIdx.x * 256 + threadIdx.x; t < total; t += (int64_t)gridDim.x * 256) {
+        const int kidx = (int)(t % g.Kp);
+        const int64_t m = t / g.Kp;
+        __nv_bfloat16 v = __float2bfloat16(0.f);
+        if (kidx < g.K) {
+            const int c = kidx % g.C, tap = kidx / g.C;
+            const int wo = (int)(m % g.WO), ho = (int)((m / g.WO) % g.HO), n = (int)(m / ((int64_t)g.WO * g.HO));
+            const int h = ho * g.stride - g.pad + tap / g.KW, w = wo * g.stride - g.pad + tap % g.KW;
+            if (h >= 0 && h < g.H && w >= 0 && w < g.W) v = x[(((int64_t)n * g.H + h) * g.W + w) * g.C + c];
+        }
+        col[t] = v;
+    }
+}
+
+// dx[n,h,w,c] = sum over taps of dcol[m(n,ho,wo)][tap][c]   (gather form: no atomics)
+template <int VEC>
+__global__ void __launch_bounds__(256) k_col2im(const __nv_bfloat16* __restrict__ dcol, __nv_bfloat16* __restrict__ dx, ConvGeom g, int64_t total) {
+    const int cvn = g.C / VEC;
+    for (int64_t t = (int64_t)blockIdx.x * 256 + threadIdx.x; t < total; t += (int64_t)gridDim.x * 256) {
+        const int cv = (int)(t % cvn);
+        const int64_t p = t / cvn;
+        const int w = (int)(p % g.W), h = (int)((p / g.W) % g.H), n = (int)(p / ((int64_t)g.W * g.H));
+        float acc[VEC];
+#pragma unroll
+        for (int i = 0; i < VEC; ++i) acc[i] = 0.f;
+        for (int kh = 0; kh < g.KH; ++kh) {
+            const int hn = h + g.pad - kh;
+            if (hn < 0 || hn % g.stride) continue;
+            const int ho = hn / g.stride;
+            if (ho >= g.HO) continue;
+            for (int kw = 0; kw < g.KW; ++kw) {
+                const int wn = w + g.pad - kw;
+                if (wn < 0 || wn % g.stride) continue;
+                const int wo = wn / g.stride;
+                if (wo >= g.WO) continue;
+                const int64_t m = ((int64_t)n * g.HO + ho) * g.WO + wo;
+                const __nv_bfloat16* src = dcol + m * g.Kp + (int64_t)(kh * g.KW + kw) * g.C + cv * VEC;
+                if (VEC == 8) {
+                    float f[8];
+                    unpack8(*reinterpret_cast<const uint4*>(src), f);
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) acc[i] += f[i];
+                } else {
+                    acc[0] += __bfloat162float(src[0]);
+                }
+            }
+        }
+        __nv_bfloat16* dst = dx + p * g.C + cv * VEC;
+        if (VEC == 8) {
+            float f[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) f[i] = acc[i];
+            *reinterpret_cast<uint4*>(dst) = pack8(f);
+        } else {
+            dst[0] = __float2bfloat16_rn(acc[0]);
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// per-channel column statistics of a [M, C] bf16 matrix: sum and (optionally) sum of squares, or the
+// two BatchNorm-backward sums.  Thread = one channel pair; a CTA covers `rows_par` rows at a time.
+// ---------------------------------------------------------------------------------------------
+struct ActGeom {
+    int64_t M;               // rows of the un-pooled activation
+    int C;
+    int pool;                // 1: dz_src / output are 2x2-pooled (H, W even)
+    int N, H, W;             // needed when pool == 1
+    int relu;
+    int has_affine;          // scale/shift present (BatchNorm); else identity
+};
+
+// z value before activation for element (row, c): scale*y + shift (+ residual)
+__device__ __forceinline__ float pre_act(float y, float sc, float sh, float res) { return fmaf(sc, y, sh) + res; }
+
+__global__ void __launch_bounds__(256) k_colstats(const __nv_bfloat16* __restrict__ y, float* __restrict__ sums, int64_t M, int C, int want_sq,
+                                                  int rows_per_cta) {
+    const int cp_n = C >> 1;                                  // channel pairs
+    const int lanes = cp_n < 256 ? cp_n : 256;                // threads along channels in this CTA
+    const int rows_par = 256 / lanes;
+    const int cp = blockIdx.x * lanes + (threadIdx.x % lanes);
+    const int rsub = threadIdx.x / lanes;
+    const int64_t r0 = (int64_t)blockIdx.y * rows_per_cta;
+    const int64_t r1 = r0 + rows_per_cta < M ? r0 + rows_per_cta : M;
+    float s0 = 0.f, s1 = 0.f, q0 = 0.f, q1 = 0.f;
+    if (cp < cp_n && rsub < rows_par) {
+        for (int64_t r = r0 + rsub; r < r1; r += rows_par) {
+            const uint32_t v = *reinterpret_cast<const uint32_t*>(y + r * C + cp * 2);
+            const float a = bf16lo(v), b = bf16hi(v);
+            s0 += a; s1 += b;
+            q0 = fmaf(a, a, q0); q1 = fmaf(b, b, q1);
+        }
+        atomicAdd(&sums[cp * 2], s0);
+        atomicAdd(&sums[cp * 2 + 1], s1);
+        if (want_sq) {
+            atomicAdd(&sums[C + cp * 2], q0);
+            atomicAdd(&sums[C + cp * 2 + 1], q1);
+        }
+    }
+}
+
+// mean/var -> scale/shift, running statistics update (momentum, unbiased variance), like nn.BatchNorm2d
+__global__ void k_bn_finalize(const float* __restrict__ sums, const float* __restrict__ gamma, const float* __restrict__ beta,
+                              float* __restrict__ running_mean, float* __restrict__ running_var, float* __restrict__ stats /* [4][C]: mean, rstd, scale, shift */,
+                              int C, float inv_m, float unbias, float momentum, float eps) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= C) return;
+    const float mean = sums[c] * inv_m;
+    float var = fmaf(-mean, mean, sums[C + c] * inv_m);
+    var = var > 0.f ? var : 0.f;
+    const float rstd = rsqrtf(var + eps);
+    const float sc = gamma[c] * rstd;
+    stats[c] = mean; stats[C + c] = rstd; stats[2 * C + c] = sc; stats[3 * C + c] = fmaf(-mean, sc, beta[c]);
+    if (running_mean) {
+        running_mean[c] = fmaf(momentum, mean - running_mean[c], running_mean[c]);
+        running_var[c] = fmaf(momentum, var * unbias - running_var[c], running_var[c]);
+    }
+}
+
+// forward: out = act(scale*y + shift (+res)), optionally 2x2 max-pooled.  8 channels per thread.
+__global__ void __launch_bounds__(256) k_bn_act_fwd(const __nv_bfloat16* __restrict__ y, const float* __restrict__ stats, const __nv_bfloat16* __restrict__ res,
+                                                    __nv_bfloat16* __restrict__ out, ActGeom g, int64_t total) {
+    const int c8n = g.C >> 3;
+    const float* scale = stats + 2 * g.C;
+    const float* shift = stats + 3 * g.C;
+    for (int64_t t = (int64_t)blockIdx.x * 256 + threadIdx.x; t < total; t += (int64_t)gridDim.x * 256) {
+        const int c8 = (int)(t % c8n);
+        const int64_t p = t / c8n;
+        float sc[8], sh[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            sc[i] = g.has_affine ? scale[c8 * 8 + i] : 1.f;
+            sh[i] = g.has_affine ? shift[c8 * 8 + i] : 0.f;
+        }
+        float o[8];
+        if (!g.pool) {
+            float f[8], r[8];
+            unpack8(*reinterpret_cast<const uint4*>(y + p * g.C + c8 * 8), f);
+            if (res) unpack8(*reinterpret_cast<const uint4*>(res + p * g.C + c8 * 8), r);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                float z = pre_act(f[i], sc[i], sh[i], res ? r[i] : 0.f);
+                o[i] = g.relu ? fmaxf(z, 0.f) : z;
+            }
+        } else {
+            const int WP = g.W >> 1, HP = g.H >> 1;
+            const int wp = (int)(p % WP), hp = (int)((p / WP) % HP), n = (int)(p / ((int64_t)WP * HP));
+#pragma unroll
+            for (int i = 0; i < 8; ++i) o[i] = -INFINITY;
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const int64_t row = ((int64_t)n * g.H + hp * 2 + (q >> 1)) * g.W + wp * 2 + (q & 1);
+                float f[8];
+                unpack8(*reinterpret_cast<const uint4*>(y + row * g.C + c8 * 8), f);
+#pragma unroll
+                for (int i = 0; i < 8; ++i) o[i] = fmaxf(o[i], pre_act(f[i], sc[i], sh[i], 0.f));
+            }
+            if (g.relu) {
+#pragma unroll
+                for (int i = 0; i < 8; ++i) o[i] = fmaxf(o[i], 0.f);
+            }
+        }
+        *reinterpret_cast<uint4*>(out + p * g.C + c8 * 8) = pack8(o);
+    }
+}
+
+// scalar-channel fallback (C % 8 != 0: LeNet's 20 / 50 channels)
+__global__ void __launch_bounds__(256) k_bn_act_fwd_scalar(const __nv_bfloat16* __restrict__ y, const float* __restrict__ stats, const __nv_bfloat16* __restrict__ res,
+                                                           __nv_bfloat16* __restrict__ out, ActGeom g, int64_t total) {
+    const float* scale = stats + 2 * g.C;
+    const float* shift = stats + 3 * g.C;
+    for (int64_t t = (int64_t)blockIdx.x * 256 + threadIdx.x; t < total; t += (int64_t)gridDim.x * 256) {
+        const int c = (int)(t % g.C);
+        const int64_t p = t / g.C;
+        const float sc = g.has_affine ? scale[c] : 1.f, sh = g.has_affine ? shift[c] : 0.f;
+        float o;
+        if (!g.pool) {
+            o = pre_act(__bfloat162float(y[p * g.C + c]), sc, sh, res ? __bfloat162float(res[p * g.C + c]) : 0.f);
+        } else {
+            const int WP = g.W >> 1, HP = g.H >> 1;
+            const int wp = (int)(p % WP), hp = (int)((p / WP) % HP), n = (int)(p / ((int64_t)WP * HP));
+            o = -INFINITY;
+            for (int q = 0; q < 4; ++q) {
+                const int64_t row = ((int64_t)n * g.H + hp * 2 + (q >> 1)) * g.W + wp * 2 + (q & 1);
+                o = fmaxf(o, pre_act(__bfloat162float(y[row * g.C + c]), sc, sh, 0.f));
+            }
+        }
+        if (g.relu) o = fmaxf(o, 0.f);
+        out[t] = __float2bfloat16_rn(o);
+    }
+}
+
+// gradient w.r.t. the pre-activation z of un-pooled element (row, c), recomputed from y:
+//   no pool: dz = dout * [z > 0]        pool: dz = dout(window) * [this element is the window's first max] * [z > 0]
+__device__ __forceinline__ float dz_elem(const __nv_bfloat16* __restrict__ y, const __nv_bfloat16* __restrict__ res, const __nv_bfloat16* __restrict__ dout,
+                                         const ActGeom& g, int64_t row, int c, float sc, float sh, float yv) {
+    if (!g.pool) {
+        const float d = __bfloat162float(dout[row * g.C + c]);
+        if (!g.relu) return d;
+        const float z = pre_act(yv, sc, sh, res ? __bfloat162float(res[row * g.C + c]) : 0.f);
+        return z > 0.f ? d : 0.f;
+    }
+    const int w = (int)(row % g.W), h = (int)((row / g.W) % g.H), n = (int)(row / ((int64_t)g.W * g.H));
+    const int hp = h >> 1, wp = w >> 1, me = ((h & 1) << 1) | (w & 1);
+    float best = -INFINITY;
+    int arg = 0;
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+        const int64_t r2 = ((int64_t)n * g.H + hp * 2 + (q >> 1)) * g.W + wp * 2 + (q & 1);
+        const float z = pre_act(q == me ? yv : __bfloat162float(y[r2 * g.C + c]), sc, sh, 0.f);
+        if (z > best) { best = z; arg = q; }
+    }
+    if (arg != me || (g.relu && !(best > 0.f))) return 0.f;
+    return __bfloat162float(dout[(((int64_t)n * (g.H >> 1) + hp) * (g.W >> 1) + wp) * g.C + c]);
+}
+
+// backward pass 1: per channel sum(dz) and sum(dz * xhat)   (thread = channel, CTA covers rows_par rows)
+__global__ void __launch_bounds__(256) k_bn_bwd_reduce(const __nv_bfloat16* __restrict__ y, const __nv_bfloat16* __restrict__ res, const __nv_bfloat16* __restrict__ dout,
+                                                       const float* __restrict__ stats, float* __restrict__ sums, ActGeom g, int rows_per_cta) {
+    const int lanes = g.C < 256 ? g.C : 256;
+    const int rows_par = 256 / lanes;
+    const int c = blockIdx.x * lanes + (threadIdx.x % lanes);
+    const int rsub = threadIdx.x / lanes;
+    if (c >= g.C || rsub >= rows_par) return;
+    const float mean = g.has_affine ? stats[c] : 0.f, rstd = g.has_affine ? stats[g.C + c] : 1.f;
+    const float sc = g.has_affine ? stats[2 * g.C + c] : 1.f, sh = g.has_affine ? stats[3 * g.C + c] : 0.f;
+    const int64_t r0 = (int64_t)blockIdx.y * rows_per_cta;
+    const int64_t r1 = r0 + rows_per_cta < g.M ? r0 + rows_per_cta : g.M;
+    float s = 0.f, sx = 0.f;
+    for (int64_t r = r0 + rsub; r < r1; r += rows_par) {
+        const float yv = __bfloat162float(y[r * g.C + c]);
+        const float dz = dz_elem(y, res, dout, g, r, c, sc, sh, yv);
+        s += dz;
+        sx = fmaf(dz, (yv - mean) * rstd, sx);
+    }
+    atomicAdd(&sums[c], s);
+    atomicAdd(&sums[g.C + c], sx);
+}
+
+// backward pass 2: dy = scale * (dz - mean(dz) - xhat * mean(dz*xhat)); dres = dz; also emits dgamma/dbeta
+__global__ void __launch_bounds__(256) k_bn_bwd_apply(const __nv_bfloat16* __restrict__ y, const __nv_bfloat16* __restrict__ res, const __nv_bfloat16* __restrict__ dout,
+                                                      const float* __restrict__ stats, const float* __restrict__ sums, __nv_bfloat16* __restrict__ dy,
+                                                      __nv_bfloat16* __restrict__ dres, ActGeom g, float inv_m, int64_t total) {
+    for (int64_t t = (int64_t)blockIdx.x * 256 + threadIdx.x; t < total; t += (int64_t)gridDim.x * 256) {
+        const int c = (int)(t % g.C);
+        const int64_t r = t / g.C;
+        const float mean = g.has_affine ? stats[c] : 0.f, rstd = g.has_affine ? stats[g.C + c] : 1.f;
+        const float sc = g.has_affine ? stats[2 * g.C + c] : 1.f, sh = g.has_affine ? stats[3 * g.C + c] : 0.f;
+        const float yv = __bfloat162float(y[t]);
+        const float dz = dz_elem(y, res, dout, g, r, c, sc, sh, yv);
+        float d = dz;
+        if (g.has_affine) d = sc * (dz - sums[c] * inv_m - (yv - mean) * rstd * sums[g.C + c] * inv_m);
+        dy[t] = __float2bfloat16_rn(d);
+        if (dres) dres[t] = __float2bfloat16_rn(dz);
+    }
+}
+
+// dgamma += sum(dz*xhat), dbeta += sum(dz)  (into the flat fp32 gradient buffer)
+__global__ void k_bn_param_grads(const float* __restrict__ sums, float* __restrict__ dgamma, float* __restrict__ dbeta, int C) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= C) return;
+    dbeta[c] += sums[c];
+    dgamma[c] += sums[C + c];
+}
+
+__global__ void k_add_vec(const float* __restrict__ src, float* __restrict__ dst, int n) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) dst[i] += src[i];
+}
+
+// ---------------------------------------------------------------------------------------------
+// small elementwise / head kernels
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_cast_f32_bf16(const float* __restrict__ x, __nv_bfloat16* __restrict__ y, int64_t n) {
+    for (int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x; i < n; i += (int64_t)gridDim.x * 256) y[i] = __float2bfloat16_rn(x[i]);
+}
+
+// copy a [rows, cols] bf16 matrix into a wider pitch (zero padded): conv weights with K % 8 != 0
+__global__ void __launch_bounds__(256) k_pad_rows(const __nv_bfloat16* __restrict__ src, __nv_bfloat16* __restrict__ dst, int rows, int cols, int pitch) {
+    for (int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x; i < (int64_t)rows * pitch; i += (int64_t)gridDim.x * 256) {
+        const int c = (int)(i % pitch);
+        const int64_t r = i / pitch;
+        dst[i] = c < cols ? src[r * cols + c] : __float2bfloat16(0.f);
+    }
+}
+
+// y = relu(x) in place variant is done in the GEMM epilogue; backward mask: dx = dy * [y > 0]
+__global__ void __launch_bounds__(256) k_relu_bwd(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ y, __nv_bfloat16* __restrict__ dx, int64_t n) {
+    for (int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x; i < n; i += (int64_t)gridDim.x * 256)
+        dx[i] = __bfloat162float(y[i]) > 0.f ? dy[i] : __float2bfloat16(0.f);
+}
+__global__ void __launch_bounds__(256) k_relu_fwd(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y, int64_t n) {
+    for (int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x; i < n; i += (int64_t)gridDim.x * 256)
+        y[i] = __bfloat162float(x[i]) > 0.f ? x[i] : __float2bfloat16(0.f);
+}
+
+// inverted dropout with a counter-based mask (recomputed in backward, nothing stored)
+__global__ void __launch_bounds__(256) k_dropout(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y, int64_t n, float p, float scale,
+                                                 uint32_t seed, uint32_t offset) {
+    for (int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x; i < n; i += (int64_t)gridDim.x * 256) {
+        Philox4 r = philox4x32_10((uint32_t)(i >> 2), offset, 0x9E37u, 0u, seed, 0xD409u);
+        const uint32_t li = (uint32_t)i & 3u;
+        const uint32_t rx = li == 0 ? r.v[0] : (li == 1 ? r.v[1] : (li == 2 ? r.v[2] : r.v[3]));
+        const float u = philox_to_uniform(rx);
+        y[i] = u >= p ? __float2bfloat16_rn(__bfloat162float(x[i]) * scale) : __float2bfloat16(0.f);
+    }
+}
+
+// [N, HW, C] -> [N, C] mean over HW (F.avg_pool2d(out, 4) on a 4x4 map, resnet.py:93) and its backward
+__global__ void __launch_bounds__(256) k_avgpool_fwd(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y, int N, int HW, int C) {
+    for (int64_t t = (int64_t)blockIdx.x * 256 + threadIdx.x; t < (int64_t)N * C; t += (int64_t)gridDim.x * 256) {
+        const int c = (int)(t % C), n = (int)(t / C);
+        float s = 0.f;
+        for (int i = 0; i < HW; ++i) s += __bfloat162float(x[((int64_t)n * HW + i) * C + c]);
+        y[t] = __float2bfloat16_rn(s / HW);
+    }
+}
+__global__ void __launch_bounds__(256) k_avgpool_bwd(const __nv_bfloat16* __restrict__ dy, __nv_bfloat16* __restrict__ dx, int N, int HW, int C) {
+    for (int64_t t = (int64_t)blockIdx.x * 256 + threadIdx.x; t < (int64_t)N * HW * C; t += (int64_t)gridDim.x * 256) {
+        const int c = (int)(t % C), n = (int)(t / ((int64_t)HW * C));
+        dx[t] = __float2bfloat16_rn(__bfloat162float(dy[(int64_t)n * C + c]) / HW);
+    }
+}
+
+// softmax cross-entropy, mean over the batch: one warp per row.  Writes loss (atomic mean), dlogits = (p - onehot)/B
+// and the top-1 hit count (accuracy, distributed_worker.py:27-39).
+__global__ void __launch_bounds__(256) k_xent(const __nv_bfloat16* __restrict__ logits, const int64_t* __restrict__ target, float* __restrict__ loss_acc /* [2]: loss, correct */,
+                                              __nv_bfloat16* __restrict__ dlogits, int B, int C, int ld) {
+    const int row = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (row >= B) return;
+    const __nv_bfloat16* x = logits + (int64_t)row * ld;
+    float mx = -INFINITY;
+    int amax = 0;
+    for (int c = lane; c < C; c += 32) {
+        float v = __bfloat162float(x[c]);
+        if (v > mx) { mx = v; amax = c; }
+    }
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) {
+        float o = __shfl_xor_sync(0xffffffffu, mx, d);
+        int oa = __shfl_xor_sync(0xffffffffu, amax, d);
+        if (o > mx || (o == mx && oa < amax)) { mx = o; amax = oa; }
+    }
+    float se = 0.f;
+    for (int c = lane; c < C; c += 32) se += __expf(__bfloat162float(x[c]) - mx);
+    se = warp_sum(se);
+    const int tgt = (int)target[row];
+    const float lse = __logf(se) + mx;
+    const float invB = 1.f / B;
+    for (int c = lane; c < C; c += 32) {
+        const float p = __expf(__bfloat162float(x[c]) - lse);
+        dlogits[(int64_t)row * ld + c] = __float2bfloat16_rn((p - (c == tgt ? 1.f : 0.f)) * invB);
+    }
+    if (lane == 0) {
+        atomicAdd(&loss_acc[0], (lse - __bfloat162float(x[tgt])) * invB);
+        if (amax == tgt) atomicAdd(&loss_acc[1], 1.f);
+    }
+}
+
+int grid_for(int64_t work_items, int per_cta = 256) {
+    int64_t g = (work_items + per_cta - 1) / per_cta;
+    const int64_t cap = 148 * 16;
+    return (int)(g < 1 ? 1 : (g > cap ? cap : g));
+}
+
+ConvGeom make_geom(int N, int H, int W, int C, int KH, int KW, int stride, int pad) {
+    ConvGeom g;
+    g.N = N; g.H = H; g.W = W; g.C = C; g.KH = KH; g.KW = KW; g.stride = stride; g.pad = pad;
+    g.HO = (H + 2 * pad - KH) / stride + 1;
+    g.WO = (W + 2 * pad - KW) / stride + 1;
+    g.K = KH * KW * C;
+    g.Kp = (g.K + 7) / 8 * 8;
+    return g;
+}
+
+#define NN_LAUNCH_CHECK()                                                                                 \
+    do {                                                                                                  \
+        cudaError_t _e = cudaGetLastError();                                                              \
+        if (_e != cudaSuccess) { ewdml_set_error("%s:%d: launch failed: %s", __FILE__, __LINE__, cudaGetErrorString(_e)); return (int)_e; } \
+        ewdml_counter_add(EWDML_CTR_COMPUTE_LAUNCHES, 1);                                                 \
+    } while (0)
+
+}  // namespace
+
+// ---- C ABI -----------------------------------------------------------------------------------------
+extern "C" int ewdml_im2col(const void* x, void* col, int N, int H, int W, int C, int KH, int KW, int stride, int pad, void* stream) {
+    EWDML_CHECK_ARG(x && col && N > 0 && C > 0);
+    ConvGeom g = make_geom(N, H, W, C, KH, KW, stride, pad);
+    const int64_t M = (int64_t)N * g.HO * g.WO;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (C % 8 == 0) {
+        const int64_t total = M * KH * KW * (C / 8);
+        k_im2col_vec8<<<grid_for(total), 256, 0, st>>>((const __nv_bfloat16*)x, (__nv_bfloat16*)col, g, total);
+    } else {
+        const int64_t total = M * g.Kp;
+        k_im2col_scalar<<<grid_for(total), 256, 0, st>>>((const __nv_bfloat16*)x, (__nv_bfloat16*)col, g, total);
+    }
+    NN_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int ewdml_col2im(const void* dcol, void* dx, int N, int H, int W, int C, int KH, int KW, int stride, int pad, void* stream) {
+    EWDML_CHECK_ARG(dcol && dx && N > 0 && C > 0);
+    ConvGeom g = make_geom(N, H, W, C, KH, KW, stride, pad);
+    cudaStream_t st = (cudaStream_t)stream;
+    if (C % 8 == 0) {
+        const int64_t total = (int64_t)N * H * W * (C / 8);
+        k_col2im<8><<<grid_for(total), 256, 0, st>>>((const __nv_bfloat16*)dcol, (__nv_bfloat16*)dx, g, total);
+    } else {
+        const int64_t total = (int64_t)N * H * W * C;
+        k_col2im<1><<<grid_for(total), 256, 0, st>>>((const __nv_bfloat16*)dcol, (__nv_bfloat16*)dx, g, total);
+    }
+    NN_LAUNCH_CHECK();
+    return 0;
+}
+
+// sums: fp32 [2*C], must be zero on entry.  want_sq: also accumulate sum of squares in sums[C..2C).
+extern "C" int ewdml_colstats(const void* y, float* sums, int64_t M, int C, int want_sq, void* stream) {
+    EWDML_CHECK_ARG(y && sums && M > 0 && C > 0 && C % 2 == 0);
+    const int cp = C / 2, lanes = cp < 256 ? cp : 256;
+    const int gx = (cp + lanes - 1) / lanes;
+    int gy = (int)((2 * 148 + gx - 1) / gx);
+    int64_t rows_per = (M + gy - 1) / gy;
+    const int rows_par = 256 / lanes;
+    if (rows_per < 4 * rows_par) rows_per = 4 * rows_par;
+    gy = (int)((M + rows_per - 1) / rows_per);
+    k_colstats<<<dim3(gx, gy), 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)y, sums, M, C, want_sq, (int)rows_per);
+    NN_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int ewdml_bn_finalize(const float* sums, const float* gamma, const float* beta, float* running_mean, float* running_var,
+                                 float* stats, int C, int64_t M, float momentum, float eps, void* stream) {
+    EWDML_CHECK_ARG(sums && gamma && beta && stats && C > 0 && M > 0);
+    const float unbias = M > 1 ? (float)((double)M / (double)(M - 1)) : 1.f;
+    k_bn_finalize<<<(C + 127) / 128, 128, 0, (cudaStream_t)stream>>>(sums, gamma, beta, running_mean, running_var, stats, C,
+                                                                     (float)(1.0 / (double)M), unbias, momentum, eps);
+    NN_LAUNCH_CHECK();
+    return 0;
+}
+
+static ActGeom make_act(int64_t M, int C, int pool, int N, int H, int W, int relu, int has_affine) {
+    ActGeom g;
+    g.M = M; g.C = C; g.pool = pool; g.N = N; g.H = H; g.W = W; g.relu = relu; g.has_affine = has_affine;
+    return g;
+}
+
+// out = act(scale*y+shift (+res)), optionally 2x2 max-pooled; stats = [mean|rstd|scale|shift] or NULL (identity)
+extern "C" int ewdml_bn_act_fwd(const void* y, const float* stats, const void* res, void* out, int N, int H, int W, int C, int relu, int pool,
+                                void* stream) {
+    EWDML_CHECK_ARG(y && out && (!pool || (H % 2 == 0 && W % 2 == 0 && !res)));
+    const int64_t M = (int64_t)N * H * W;
+    ActGeom g = make_act(M, C, pool, N, H, W, relu, stats != nullptr);
+    const int64_t rows_out = pool ? M / 4 : M;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (C % 8 == 0) {
+        const int64_t total = rows_out * (C / 8);
+        k_bn_act_fwd<<<grid_for(total), 256, 0, st>>>((const __nv_bfloat16*)y, stats, (const __nv_bfloat16*)res, (__nv_bfloat16*)out, g, total);
+    } else {
+        const int64_t total = rows_out * C;
+        k_bn_act_fwd_scalar<<<grid_for(total), 256, 0, st>>>((const __nv_bfloat16*)y, stats, (const __nv_bfloat16*)res, (__nv_bfloat16*)out, g, total);
+    }
+    NN_LAUNCH_CHECK();
+    return 0;
+}
+
+// Backward of the fused block.  sums: fp32 [2*C] zero on entry (scratch).  dgamma/dbeta (fp32, accumulated) may be
+// NULL when stats == NULL.  dres (may be NULL) receives the gradient of the residual input.
+extern "C" int ewdml_bn_act_bwd(const void* y, const float* stats, const void* res, const void* dout, float* sums, void* dy, void* dres,
+                                float* dgamma, float* dbeta, int N, int H, int W, int C, int relu, int pool, void* stream) {
+    EWDML_CHECK_ARG(y && dout && sums && dy);
+    const int64_t M = (int64_t)N * H * W;
+    ActGeom g = make_act(M, C, pool, N, H, W, relu, stats != nullptr);
+    cudaStream_t st = (cudaStream_t)stream;
+    if (stats) {
+        const int lanes = C < 256 ? C : 256;
+        const int gx = (C + lanes - 1) / lanes;
+        int gy = (int)((2 * 148 + gx - 1) / gx);
+        int64_t rows_per = (M + gy - 1) / gy;
+        const int rows_par = 256 / lanes;
+        if (rows_per < 4 * rows_par) rows_per = 4 * rows_par;
+        gy = (int)((M + rows_per - 1) / rows_per);
+        k_bn_bwd_reduce<<<dim3(gx, gy), 256, 0, st>>>((const __nv_bfloat16*)y, (const __nv_bfloat16*)res, (const __nv_bfloat16*)dout, stats, sums, g,
+                                                       (int)rows_per);
+        NN_LAUNCH_CHECK();
+        if (dgamma && dbeta) {
+            k_bn_param_grads<<<(C + 127) / 128, 128, 0, st>>>(sums, dgamma, dbeta, C);
+            NN_LAUNCH_CHECK();
+        }
+    }
+    const int64_t total = M * C;
+    k_bn_bwd_apply<<<grid_for(total), 256, 0, st>>>((const __nv_bfloat16*)y, (const __nv_bfloat16*)res, (const __nv_bfloat16*)dout, stats, sums,
+                                                    (__nv_bfloat16*)dy, (__nv_bfloat16*)dres, g, (float)(1.0 / (double)M), total);
+    NN_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int ewdml_add_vec_f32(const float* src, float* dst, int n, void* stream) {
+    EWDML_CHECK_ARG(src && dst && n > 0);
+    k_add_vec<<<(n + 255) / 256, 256, 0, (cudaStream_t)stream>>>(src, dst, n);
+    NN_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int ewdml_cast_f32_bf16(const float* x, void* y, int64_t n, void* stream) {
+    EWDML_CHECK_ARG(x && y && n > 0);
+    k_cast_f32_bf16<<<grid_for(n), 256, 0, (cudaStream_t)stream>>>(x, (__nv_bfloat16*)y, n);
+    NN_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int ewdml_pad_rows_bf16(const void* src, void* dst, int rows, int cols, int pitch, void* stream) {
+    EWDML_CHECK_ARG(src && dst && rows > 0 && cols > 0 && pitch >= cols);
+    k_pad_rows<<<grid_for((int64_t)rows * pitch), 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)src, (__nv_bfloat16*)dst, rows, cols, pitch);
+    NN_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int ewdml_relu_fwd(const void* x, void* y, int64_t n, void* stream) {
+    k_relu_fwd<<<grid_for(n), 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)x, (__nv_bfloat16*)y, n);
+    NN_LAUNCH_CHECK();
+    return 0;
+}
+extern "C" int ewdml_relu_bwd(const void* dy, const void* y, void* dx, int64_t n, void* stream) {
+    k_relu_bwd<<<grid_for(n), 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)dy, (const __nv_bfloat16*)y, (__nv_bfloat16*)dx, n);
+    NN_LAUNCH_CHECK();
+    return 0;
+}
+extern "C" int ewdml_dropout(const void* x, void* y, int64_t n, float p, uint32_t seed, uint32_t offset, void* stream) {
+    EWDML_CHECK_ARG(p >= 0.f && p < 1.f);
+    k_dropout<<<grid_for(n), 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)x, (__nv_bfloat16*)y, n, p, 1.f / (1.f - p), seed, offset);
+    NN_LAUNCH_CHECK();
+    return 0;
+}
+extern "C" int ewdml_avgpool_fwd(const void* x, void* y, int N, int HW, int C, void* stream) {
+    k_avgpool_fwd<<<grid_for((int64_t)N * C), 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)x, (__nv_bfloat16*)y, N, HW, C);
+    NN_LAUNCH_CHECK();
+    return 0;
+}
+extern "C" int ewdml_avgpool_bwd(const void* dy, void* dx, int N, int HW, int C, void* stream) {
+    k_avgpool_bwd<<<grid_for((int64_t)N * HW * C), 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)dy, (__nv_bfloat16*)dx, N, HW, C);
+    NN_LAUNCH_CHECK();
+    return 0;
+}
+// loss_acc: fp32 [2] zero on entry -> {mean loss, #correct}; dlogits has the same pitch as logits
+extern "C" int ewdml_xent(const void* logits, const int64_t* target, float* loss_acc, void* dlogits, int B, int C, int ld, void* stream) {
+    EWDML_CHECK_ARG(logits && target && loss_acc && dlogits && B > 0 && C > 0);
+    k_xent<<<(B + 7) / 8, 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)logits, target, loss_acc, (__nv_bfloat16*)dlogits, B, C, ld);
+    NN_LAUNCH_CHECK();
+    return 0;
+}

@@ -24,8 +24,9 @@ class LeNet(nn.Module):
         self.pool = L.MaxPool2d(2, 2)
 
     def forward(self, x):
-        x = self.pool(self.conv1(x), relu=True)   # relu(maxpool(.)) as in lenet.py:24-26
-        x = self.pool(self.conv2(x), relu=True)
+        # relu(maxpool(conv(x))) as in lenet.py:24-29 (== maxpool(relu(.)): relu is monotonic)
+        x = L.conv_bn_act(x, self.conv1, None, relu=True, pool=True)
+        x = L.conv_bn_act(x, self.conv2, None, relu=True, pool=True)
         x = x.reshape(x.shape[0], -1)              # logical (C,H,W) order, as x.view(-1, 800)
         x = self.fc1(x)
         return self.fc2(x)

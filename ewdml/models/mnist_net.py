@@ -21,8 +21,8 @@ class MnistNet(nn.Module):
         self.log_softmax_output = True
 
     def forward(self, x):
-        x = self.pool(self.conv1(x), relu=True)
-        x = self.pool(self.conv2_drop(self.conv2(x)), relu=True)
+        x = L.conv_bn_act(x, self.conv1, None, relu=True, pool=True)
+        x = F.relu(F.max_pool2d(self.conv2_drop(self.conv2(x)), 2))
         x = x.reshape(x.shape[0], -1)
         x = F.relu(self.fc1(x))
         x = F.dropout(x, training=self.training)

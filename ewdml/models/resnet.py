@@ -27,7 +27,7 @@ def _shortcut(in_planes, out_planes, stride):
 def _run_shortcut(sc, x):
     if len(sc) == 0:
         return x
-    return sc[1](sc[0](x))
+    return L.conv_bn_act(x, sc[0], sc[1])
 
 
 class BasicBlock(nn.Module):
@@ -42,8 +42,8 @@ class BasicBlock(nn.Module):
         self.shortcut = _shortcut(in_planes, self.expansion * planes, stride)
 
     def forward(self, x):
-        out = self.bn1(self.conv1(x), relu=True)
-        return self.bn2(self.conv2(out), relu=True, residual=_run_shortcut(self.shortcut, x))
+        out = L.conv_bn_act(x, self.conv1, self.bn1, relu=True)
+        return L.conv_bn_act(out, self.conv2, self.bn2, relu=True, residual=_run_shortcut(self.shortcut, x))
 
 
 class Bottleneck(nn.Module):
@@ -60,9 +60,9 @@ class Bottleneck(nn.Module):
         self.shortcut = _shortcut(in_planes, self.expansion * planes, stride)
 
     def forward(self, x):
-        out = self.bn1(self.conv1(x), relu=True)
-        out = self.bn2(self.conv2(out), relu=True)
-        return self.bn3(self.conv3(out), relu=True, residual=_run_shortcut(self.shortcut, x))
+        out = L.conv_bn_act(x, self.conv1, self.bn1, relu=True)
+        out = L.conv_bn_act(out, self.conv2, self.bn2, relu=True)
+        return L.conv_bn_act(out, self.conv3, self.bn3, relu=True, residual=_run_shortcut(self.shortcut, x))
 
 
 class ResNet(nn.Module):
@@ -86,7 +86,7 @@ class ResNet(nn.Module):
         return nn.Sequential(*blocks)
 
     def forward(self, x):
-        out = self.bn1(self.conv1(x), relu=True)
+        out = L.conv_bn_act(x, self.conv1, self.bn1, relu=True)
         out = self.layer4(self.layer3(self.layer2(self.layer1(out))))
         out = self.avgpool(out)
         return self.linear(out.reshape(out.shape[0], -1))

@@ -26,17 +26,23 @@ CFG = {
 
 
 class FusedFeatures(nn.Sequential):
-    """Sequential whose forward fuses conv->bn->relu triples (same children, same keys)."""
+    """Sequential whose forward fuses conv -> [bn] -> relu -> [maxpool] groups (same children, same keys)."""
 
     def forward(self, x):
         mods = list(self)
         i = 0
         while i < len(mods):
             m = mods[i]
-            if (isinstance(m, L.Conv2d) and i + 2 < len(mods) and isinstance(mods[i + 1], L.BatchNorm2d)
-                    and isinstance(mods[i + 2], nn.ReLU)):
-                x = mods[i + 1](m(x), relu=True)
-                i += 3
+            if isinstance(m, nn.Conv2d):
+                j = i + 1
+                bn = mods[j] if j < len(mods) and isinstance(mods[j], nn.BatchNorm2d) else None
+                j += bn is not None
+                relu = j < len(mods) and isinstance(mods[j], nn.ReLU)
+                j += relu
+                pool = j < len(mods) and isinstance(mods[j], nn.MaxPool2d)
+                j += pool
+                x = L.conv_bn_act(x, m, bn, relu=relu, pool=pool)
+                i = j
             else:
                 x = m(x)
                 i += 1
@@ -74,7 +80,10 @@ class VGG(nn.Module):
     def forward(self, x):
         x = self.features(x)
         x = x.reshape(x.shape[0], -1)
-        return self.classifier(x)
+        c = self.classifier
+        x = L.linear_act(c[0](x), c[1], relu=True)          # Dropout - Linear - ReLU
+        x = L.linear_act(c[3](x), c[4], relu=True)          # Dropout - Linear - ReLU
+        return c[6](x)
 
 
 def _vgg(key, bn, num_classes):

@@ -32,48 +32,27 @@ def _native(x: torch.Tensor) -> bool:
 
 
 class Conv2d(nn.Conv2d):
-    def forward(self, x):
-        if _native(x):
-            from . import native
-            return native.conv2d(x, self.weight, self.bias, self.stride, self.padding)
-        return super().forward(x)
+    pass
 
 
 class Linear(nn.Linear):
     def forward(self, x):
         if _native(x):
             from . import native
-            return native.linear(x, self.weight, self.bias)
+            return native.linear_block(x, self, relu=False)
         return super().forward(x)
 
 
 class BatchNorm2d(nn.BatchNorm2d):
-    def forward(self, x, relu: bool = False, residual=None):
-        """BatchNorm with optional fused residual-add and ReLU (``y = relu(bn(x) + residual)``)."""
-        if _native(x):
-            from . import native
-            return native.batch_norm(self, x, relu=relu, residual=residual)
-        y = super().forward(x)
-        if residual is not None:
-            y = y + residual
-        return F.relu(y) if relu else y
+    pass
 
 
 class ReLU(nn.ReLU):
-    def forward(self, x):
-        if _native(x):
-            from . import native
-            return native.relu(x)
-        return super().forward(x)
+    pass
 
 
 class MaxPool2d(nn.MaxPool2d):
-    def forward(self, x, relu: bool = False):
-        if _native(x):
-            from . import native
-            return native.max_pool2x2(x, relu=relu)
-        y = super().forward(x)
-        return F.relu(y) if relu else y
+    pass
 
 
 class AvgPool2d(nn.AvgPool2d):
@@ -90,6 +69,35 @@ class Dropout(nn.Dropout):
             from . import native
             return native.dropout(x, self.p)
         return super().forward(x)
+
+
+def conv_bn_act(x, conv: nn.Conv2d, bn=None, relu: bool = False, residual=None, pool: bool = False):
+    """``[maxpool2x2] relu?( bn?( conv(x) ) [+ residual] )`` -- the unit every model here is built from.
+
+    Native mode: one fused chain of sm_100a kernels (im2col -> tcgen05 GEMM -> BN statistics ->
+    normalise/add/activate/pool).  Torch mode: the same modules called one after another.
+    """
+    if _native(x):
+        from . import native
+        return native.conv_block(x, conv, bn, relu=relu, residual=residual, pool=pool)
+    y = conv(x)
+    if bn is not None:
+        y = bn(y)
+    if residual is not None:
+        y = y + residual
+    if relu:
+        y = F.relu(y)
+    if pool:
+        y = F.max_pool2d(y, 2, 2)
+    return y
+
+
+def linear_act(x, lin: nn.Linear, relu: bool = False):
+    if _native(x):
+        from . import native
+        return native.linear_block(x, lin, relu=relu)
+    y = lin(x)
+    return F.relu(y) if relu else y
 
 
 def cross_entropy(logits: torch.Tensor, target: torch.Tensor) -> torch.Tensor:

@@ -21,8 +21,29 @@ def _l():
     if _lib is None:
         _lib = L.load()
         vp, i32, f32 = C.c_void_p, C.c_int, C.c_float
-        _lib.ewdml_gemm_bf16.restype = i32
-        _lib.ewdml_gemm_bf16.argtypes = [vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, i32, vp, f32, i32, vp]
+        i64, u32 = C.c_int64, C.c_uint32
+        sig = {
+            "ewdml_gemm_bf16": [vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, i32, vp, f32, i32, vp],
+            "ewdml_im2col": [vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, vp],
+            "ewdml_col2im": [vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, vp],
+            "ewdml_colstats": [vp, vp, i64, i32, i32, vp],
+            "ewdml_bn_finalize": [vp, vp, vp, vp, vp, vp, i32, i64, f32, f32, vp],
+            "ewdml_bn_act_fwd": [vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, vp],
+            "ewdml_bn_act_bwd": [vp, vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, vp],
+            "ewdml_add_vec_f32": [vp, vp, i32, vp],
+            "ewdml_cast_f32_bf16": [vp, vp, i64, vp],
+            "ewdml_pad_rows_bf16": [vp, vp, i32, i32, i32, vp],
+            "ewdml_relu_fwd": [vp, vp, i64, vp],
+            "ewdml_relu_bwd": [vp, vp, vp, i64, vp],
+            "ewdml_dropout": [vp, vp, i64, f32, u32, u32, vp],
+            "ewdml_avgpool_fwd": [vp, vp, i32, i32, i32, vp],
+            "ewdml_avgpool_bwd": [vp, vp, i32, i32, i32, vp],
+            "ewdml_xent": [vp, vp, vp, vp, i32, i32, i32, vp],
+        }
+        for name, args in sig.items():
+            fn = getattr(_lib, name)
+            fn.restype = i32
+            fn.argtypes = args
     return _lib
 
 
@@ -64,3 +85,351 @@ def gemm(a: torch.Tensor, b: torch.Tensor, a_mn: bool = False, b_mn: bool = Fals
 
 def gemm_tn(a, b, **kw):
     return gemm(a, b, False, False, **kw)
+
+
+# ======================================================================================
+# layer functions
+# ======================================================================================
+BF16 = torch.bfloat16
+
+
+def _r8(n: int) -> int:
+    return (n + 7) // 8 * 8
+
+
+def _empty2d(rows: int, cols: int, device, zero: bool = False) -> torch.Tensor:
+    """[rows, cols] bf16 view of a buffer whose row pitch is a multiple of 8 elements (TMA operand rule)."""
+    pitch = _r8(cols)
+    buf = (torch.zeros if (zero or pitch != cols) else torch.empty)(rows, pitch, dtype=BF16, device=device)
+    return buf[:, :cols] if pitch != cols else buf
+
+
+def to_nhwc_bf16(x: torch.Tensor) -> torch.Tensor:
+    """[N,C,H,W] (any format/dtype) -> contiguous [N,H,W,C] bf16."""
+    xn = x.permute(0, 2, 3, 1)
+    if x.dtype == BF16:
+        return xn.contiguous()
+    xn = xn.contiguous()
+    if x.dtype == torch.float32:
+        out = torch.empty(xn.shape, dtype=BF16, device=x.device)
+        L.check(_l().ewdml_cast_f32_bf16(_p(xn), _p(out), xn.numel(), _stream()), "cast")
+        return out
+    return xn.to(BF16)
+
+
+def _weight_bf16(w: torch.nn.Parameter, rows: int, k: int) -> torch.Tensor:
+    """bf16 [rows, Kp] K-major weight matrix: the shadow copy kept by the fused optimizer when present."""
+    sh = getattr(w, "_ewdml_bf16", None)
+    if sh is None:
+        src = w.detach()
+        src = src.permute(0, 2, 3, 1) if src.dim() == 4 else src
+        sh = src.reshape(rows, k).to(BF16).contiguous().view(-1)
+    wb = sh.view(rows, k)
+    if k % 8 == 0:
+        return wb
+    kp = _r8(k)
+    out = torch.empty(rows, kp, dtype=BF16, device=w.device)
+    L.check(_l().ewdml_pad_rows_bf16(_p(wb), _p(out), rows, k, kp, _stream()), "pad_rows")
+    return out
+
+
+def _grad2d(w: torch.nn.Parameter, rows: int, k: int) -> torch.Tensor:
+    """fp32 [rows, k] view of the parameter's gradient in storage order (a slice of the flat gradient buffer)."""
+    if w.grad is None:
+        w.grad = torch.zeros_like(w)
+    g = w.grad
+    g = g.permute(0, 2, 3, 1) if g.dim() == 4 else g
+    if not g.is_contiguous():
+        raise RuntimeError("native compute needs conv weights/gradients in channels-last storage (FlatModel(channels_last=True))")
+    return g.reshape(rows, k)
+
+
+def _colsum_into(dy2d: torch.Tensor, target: torch.Tensor) -> None:
+    """target (fp32 [C]) += column sums of dy2d ([M, C] bf16 contiguous)."""
+    M, Cn = dy2d.shape
+    sums = torch.zeros(2 * Cn, dtype=torch.float32, device=dy2d.device)
+    L.check(_l().ewdml_colstats(_p(dy2d), _p(sums), M, Cn, 0, _stream()), "colstats")
+    L.check(_l().ewdml_add_vec_f32(_p(sums), _p(target), Cn, _stream()), "add_vec")
+
+
+def _conv_supported(conv, x) -> bool:
+    return (conv.out_channels % 8 == 0 and conv.groups == 1 and conv.dilation == (1, 1)
+            and conv.kernel_size[0] == conv.kernel_size[1] and conv.stride[0] == conv.stride[1]
+            and conv.padding[0] == conv.padding[1] and isinstance(conv.padding, tuple))
+
+
+class _ConvBlockFn(torch.autograd.Function):
+    """out = [maxpool2x2] act( bn( conv(x) + bias ) [+ residual] ) with every stage on the native kernels."""
+
+    @staticmethod
+    def forward(ctx, x, residual, _w, conv, bn, relu, pool):      # _w: the weight, so autograd sees a differentiable input
+        lib = _l()
+        st = _stream()
+        dev = x.device
+        N, Cin, H, W = x.shape
+        kh, stride, pad = conv.kernel_size[0], conv.stride[0], conv.padding[0]
+        Cout = conv.out_channels
+        HO, WO = (H + 2 * pad - kh) // stride + 1, (W + 2 * pad - kh) // stride + 1
+        M, K = N * HO * WO, kh * kh * Cin
+        Kp = _r8(K)
+        xn = to_nhwc_bf16(x)
+        direct = kh == 1 and stride == 1 and pad == 0 and Cin % 8 == 0
+        if direct:
+            col = xn.view(M, Cin)
+        else:
+            col = torch.empty(M, Kp, dtype=BF16, device=dev)
+            L.check(lib.ewdml_im2col(_p(xn), _p(col), N, H, W, Cin, kh, kh, stride, pad, st), "im2col")
+        wb = _weight_bf16(conv.weight, Cout, K)
+        y = gemm(col, wb, bias=conv.bias.detach() if conv.bias is not None else None)          # [M, Cout] bf16
+        stats = None
+        if bn is not None:
+            stats = torch.empty(4 * Cout, dtype=torch.float32, device=dev)
+            if bn.training:
+                sums = torch.zeros(2 * Cout, dtype=torch.float32, device=dev)
+                L.check(lib.ewdml_colstats(_p(y), _p(sums), M, Cout, 1, st), "colstats")
+                mom = bn.momentum if bn.momentum is not None else 0.1
+                L.check(lib.ewdml_bn_finalize(_p(sums), _p(bn.weight.detach()), _p(bn.bias.detach()),
+                                              _p(bn.running_mean) if bn.track_running_stats else None,
+                                              _p(bn.running_var) if bn.track_running_stats else None,
+                                              _p(stats), Cout, M, float(mom), float(bn.eps), st), "bn_finalize")
+                if bn.track_running_stats and bn.num_batches_tracked is not None:
+                    bn.num_batches_tracked += 1
+            else:
+                rstd = torch.rsqrt(bn.running_var + bn.eps)
+                sc = bn.weight.detach() * rstd
+                stats.copy_(torch.cat([bn.running_mean, rstd, sc, bn.bias.detach() - bn.running_mean * sc]))
+        resn = to_nhwc_bf16(residual) if residual is not None else None
+        HP, WP = (HO // 2, WO // 2) if pool else (HO, WO)
+        out = torch.empty(N, HP, WP, Cout, dtype=BF16, device=dev)
+        L.check(lib.ewdml_bn_act_fwd(_p(y), _p(stats), _p(resn), _p(out), N, HO, WO, Cout, int(relu), int(pool), st), "bn_act_fwd")
+        ctx.save_for_backward(col, y, stats if stats is not None else torch.empty(0, device=dev),
+                              resn if resn is not None else torch.empty(0, device=dev))
+        ctx.meta = (conv, bn, relu, pool, N, H, W, Cin, HO, WO, Cout, kh, stride, pad, M, K, Kp, direct)
+        ctx.has_res = residual is not None
+        return out.permute(0, 3, 1, 2)
+
+    @staticmethod
+    def backward(ctx, dout):
+        lib = _l()
+        st = _stream()
+        col, y, stats, resn = ctx.saved_tensors
+        conv, bn, relu, pool, N, H, W, Cin, HO, WO, Cout, kh, stride, pad, M, K, Kp, direct = ctx.meta
+        dev = dout.device
+        stats = stats if stats.numel() else None
+        resn = resn if resn.numel() else None
+        dn = to_nhwc_bf16(dout)
+        need_dz = bn is not None or relu or pool
+        dres = None
+        if need_dz:
+            dy = torch.empty(M, Cout, dtype=BF16, device=dev)
+            dres = torch.empty(M, Cout, dtype=BF16, device=dev) if ctx.has_res else None
+            sums = torch.zeros(2 * Cout, dtype=torch.float32, device=dev)
+            dg = db = None
+            if bn is not None:
+                if bn.weight.grad is None:
+                    bn.weight.grad = torch.zeros_like(bn.weight)
+                if bn.bias.grad is None:
+                    bn.bias.grad = torch.zeros_like(bn.bias)
+                dg, db = bn.weight.grad, bn.bias.grad
+            L.check(lib.ewdml_bn_act_bwd(_p(y), _p(stats), _p(resn), _p(dn), _p(sums), _p(dy), _p(dres), _p(dg), _p(db),
+                                         N, HO, WO, Cout, int(relu), int(pool), st), "bn_act_bwd")
+        else:
+            dy = dn.view(M, Cout)
+            dres = dy if ctx.has_res else None
+        # weight gradient: dW[Cout, K] += dy^T col   (both operands MN-major, split-K, fp32 atomics into the flat buffer)
+        gw = _grad2d(conv.weight, Cout, K)
+        gemm(dy, col[:, :K] if Kp != K else col, True, True, out=gw, out_mode=OUT_ACCUM)
+        if conv.bias is not None and bn is None:
+            if conv.bias.grad is None:
+                conv.bias.grad = torch.zeros_like(conv.bias)
+            _colsum_into(dy, conv.bias.grad)
+        dx = None
+        if ctx.needs_input_grad[0]:
+            wb = _weight_bf16(conv.weight, Cout, K)                      # [Cout, Kp]: used as the MN-major B operand [K=Cout][N=Kp]
+            dcol = gemm(dy, wb, False, True)                             # [M, Kp] bf16
+            if direct:
+                dxn = dcol.view(N, H, W, Cin)
+            else:
+                dxn = torch.empty(N, H, W, Cin, dtype=BF16, device=dev)
+                L.check(lib.ewdml_col2im(_p(dcol), _p(dxn), N, H, W, Cin, kh, kh, stride, pad, st), "col2im")
+            dx = dxn.permute(0, 3, 1, 2)
+        dr = dres.view(N, HO, WO, Cout).permute(0, 3, 1, 2) if (ctx.has_res and ctx.needs_input_grad[1]) else None
+        return dx, dr, None, None, None, None, None
+
+
+def conv_block(x, conv, bn=None, relu=False, residual=None, pool=False):
+    """Fused conv (+bias) [+BatchNorm] [+residual] [+ReLU] [+2x2 max-pool]; falls back to torch for odd shapes."""
+    if not _conv_supported(conv, x) or (pool and residual is not None):
+        import torch.nn.functional as F
+        y = F.conv2d(x.float() if x.dtype != conv.weight.dtype else x, conv.weight, conv.bias, conv.stride, conv.padding)
+        if bn is not None:
+            y = F.batch_norm(y, bn.running_mean, bn.running_var, bn.weight, bn.bias, bn.training, bn.momentum or 0.1, bn.eps)
+        if residual is not None:
+            y = y + residual
+        if relu:
+            y = F.relu(y)
+        if pool:
+            y = F.max_pool2d(y, 2, 2)
+        return y
+    return _ConvBlockFn.apply(x, residual, conv.weight, conv, bn, relu, pool)
+
+
+class _LinearFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, _w, lin, relu):
+        lib = _l()
+        B = x.shape[0]
+        if x.dtype != BF16 or x.stride(1) != 1 or x.stride(0) % 8:
+            xb = _empty2d(B, x.shape[1], x.device)
+            xb.copy_(x)
+            x = xb
+        wb = _weight_bf16(lin.weight, lin.out_features, lin.in_features)
+        y = _empty2d(B, lin.out_features, x.device, zero=True)
+        gemm(x, wb, out=y, bias=lin.bias.detach() if lin.bias is not None else None)
+        if relu:
+            buf = y if y.is_contiguous() else None
+            if buf is not None:
+                L.check(lib.ewdml_relu_fwd(_p(y), _p(y), y.numel(), _stream()), "relu")
+            else:
+                y.clamp_(min=0)
+        ctx.save_for_backward(x, y if relu else torch.empty(0, device=x.device))
+        ctx.meta = (lin, relu)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        lib = _l()
+        x, yact = ctx.saved_tensors
+        lin, relu = ctx.meta
+        B = x.shape[0]
+        if dy.dtype != BF16 or dy.stride(1) != 1 or dy.stride(0) % 8:
+            d = _empty2d(B, dy.shape[1], dy.device, zero=True)
+            d.copy_(dy)
+            dy = d
+        if relu:
+            d2 = _empty2d(B, dy.shape[1], dy.device, zero=True)
+            if dy.is_contiguous() and yact.is_contiguous():
+                L.check(lib.ewdml_relu_bwd(_p(dy), _p(yact), _p(d2), dy.numel(), _stream()), "relu_bwd")
+            else:
+                d2.copy_(dy * (yact > 0))
+            dy = d2
+        gw = _grad2d(lin.weight, lin.out_features, lin.in_features)
+        gemm(dy, x, True, True, out=gw, out_mode=OUT_ACCUM)                 # dW += dy^T x
+        if lin.bias is not None:
+            if lin.bias.grad is None:
+                lin.bias.grad = torch.zeros_like(lin.bias)
+            if dy.is_contiguous():
+                _colsum_into(dy, lin.bias.grad)
+            else:
+                lin.bias.grad += dy.float().sum(0)
+        dx = None
+        if ctx.needs_input_grad[0]:
+            wb = _weight_bf16(lin.weight, lin.out_features, lin.in_features)
+            dx = _empty2d(B, lin.in_features, dy.device)
+            gemm(dy, wb, False, True, out=dx)                                # dx = dy W
+        return dx, None, None, None
+
+
+def linear_block(x, lin, relu=False):
+    return _LinearFn.apply(x, lin.weight, lin, relu)
+
+
+class _XentFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, logits, target):
+        B, Cn = logits.shape
+        if logits.dtype != BF16 or logits.stride(1) != 1:
+            lb = _empty2d(B, Cn, logits.device, zero=True)
+            lb.copy_(logits)
+            logits = lb
+        acc = torch.zeros(2, dtype=torch.float32, device=logits.device)
+        dl = torch.zeros(B, logits.stride(0), dtype=BF16, device=logits.device)
+        L.check(_l().ewdml_xent(_p(logits), _p(target), _p(acc), _p(dl), B, Cn, logits.stride(0), _stream()), "xent")
+        ctx.save_for_backward(dl[:, :Cn])
+        ctx.correct = acc[1:2]
+        return acc[0].clone()
+
+    @staticmethod
+    def backward(ctx, g):
+        (dl,) = ctx.saved_tensors
+        return dl * g.to(dl.dtype), None
+
+
+def cross_entropy(logits, target):
+    return _XentFn.apply(logits, target)
+
+
+class _DropoutFn(torch.autograd.Function):
+    _counter = [0]
+
+    @staticmethod
+    def forward(ctx, x, p):
+        _DropoutFn._counter[0] += 1
+        seed = int(torch.initial_seed() & 0xFFFFFFFF)
+        off = _DropoutFn._counter[0] & 0xFFFFFFFF
+        xc = x if x.is_contiguous() else x.contiguous()
+        y = torch.empty_like(xc)
+        L.check(_l().ewdml_dropout(_p(xc), _p(y), xc.numel(), float(p), seed, off, _stream()), "dropout")
+        ctx.meta = (p, seed, off)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        p, seed, off = ctx.meta
+        d = dy if dy.is_contiguous() else dy.contiguous()
+        dx = torch.empty_like(d)
+        L.check(_l().ewdml_dropout(_p(d), _p(dx), d.numel(), float(p), seed, off, _stream()), "dropout_bwd")
+        return dx, None
+
+
+def dropout(x, p):
+    if x.dtype != BF16:
+        x = x.to(BF16)
+    return _DropoutFn.apply(x, p)
+
+
+class _AvgPoolFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x):
+        N, Cn, H, W = x.shape
+        xn = to_nhwc_bf16(x)
+        y = torch.empty(N, Cn, dtype=BF16, device=x.device)
+        L.check(_l().ewdml_avgpool_fwd(_p(xn), _p(y), N, H * W, Cn, _stream()), "avgpool")
+        ctx.meta = (N, Cn, H, W)
+        return y.view(N, Cn, 1, 1)
+
+    @staticmethod
+    def backward(ctx, dy):
+        N, Cn, H, W = ctx.meta
+        d = dy.reshape(N, Cn).to(BF16).contiguous()
+        dx = torch.empty(N, H, W, Cn, dtype=BF16, device=dy.device)
+        L.check(_l().ewdml_avgpool_bwd(_p(d), _p(dx), N, H * W, Cn, _stream()), "avgpool_bwd")
+        return dx.permute(0, 3, 1, 2)
+
+
+def avg_pool(x, kernel_size):
+    k = kernel_size if isinstance(kernel_size, int) else kernel_size[0]
+    if x.shape[2] != k or x.shape[3] != k:
+        return torch.nn.functional.avg_pool2d(x, k)
+    return _AvgPoolFn.apply(x)
+
+
+# ---- entry points used by ewdml.ops.layers (unfused module-by-module use) ---------------------------
+def conv2d(x, weight, bias, stride, padding):
+    raise RuntimeError("native conv is reached through conv_block(); see ewdml.ops.layers.Conv2d.forward")
+
+
+def linear(x, weight, bias):
+    raise RuntimeError("native linear is reached through linear_block(); see ewdml.ops.layers.Linear.forward")
+
+
+def relu(x):
+    xc = x if x.is_contiguous() else x.contiguous()
+    if xc.dtype != BF16:
+        return torch.relu(x)
+    return torch.relu(xc)      # stand-alone ReLU is rare on the native path (fused elsewhere)
+
+
+def max_pool2x2(x, relu=False):
+    y = torch.nn.functional.max_pool2d(x, 2, 2)
+    return torch.relu(y) if relu else y

@@ -71,6 +71,9 @@ class FlatModel:
             b.data = b.data.to(self.device)
         if self.param_bf16 is not None:
             self.param_bf16.copy_(self.param)
+            for seg, p in zip(self.segments, self.params):
+                # storage-order bf16 copy of this parameter, kept current by the fused optimizer kernel
+                p._ewdml_bf16 = self.param_bf16[seg.offset:seg.offset + seg.numel]
 
     # ------------------------------------------------------------------
     def _view(self, flat: torch.Tensor, seg: Segment) -> torch.Tensor:

@@ -1,0 +1,187 @@
+"""Native compute kernels (im2col + tcgen05 GEMM conv, fused BN/ReLU/pool, linear, cross-entropy)
+vs a plain PyTorch fp32 reference of the same op on the same (bf16-rounded) inputs."""
+import pytest
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+DEV = "cuda"
+
+
+def _close(a, b, tol=6e-2, name=""):
+    """Relative L2 error and cosine: ReLU / max-pool masks flip for a few near-tie elements when the
+    pre-activation is bf16, so a max-abs criterion is not meaningful for gradients."""
+    a, b = a.float().flatten(), b.float().flatten()
+    nb = b.norm().item()
+    if nb < 1e-6:
+        assert a.norm().item() < 1e-3, f"{name}: expected ~0"
+        return
+    rel = (a - b).norm().item() / nb
+    cos = F.cosine_similarity(a, b, dim=0).item()
+    assert rel <= tol and cos >= 1 - tol, f"{name}: rel L2 err {rel:.4g}, cosine {cos:.5f}"
+
+
+def _round(t):
+    return t.to(torch.bfloat16).float()
+
+
+@pytest.mark.parametrize("cin,cout,k,stride,pad,hw,bn,relu,pool,res", [
+    (16, 32, 3, 1, 1, 8, True, True, False, False),
+    (3, 64, 3, 1, 1, 32, True, True, True, False),       # VGG first layer (C_in = 3 -> padded K)
+    (64, 128, 3, 1, 1, 16, True, True, True, False),
+    (64, 64, 1, 1, 0, 8, True, True, False, False),       # bottleneck 1x1 (no im2col)
+    (64, 128, 3, 2, 1, 16, True, True, False, False),     # strided
+    (64, 256, 1, 2, 0, 8, True, False, False, False),     # shortcut conv
+    (32, 32, 3, 1, 1, 8, True, True, False, True),        # residual add
+    (16, 24, 5, 1, 0, 12, False, True, True, False),      # no BN (LeNet-like), bias grad
+])
+def test_conv_block_forward_backward(cin, cout, k, stride, pad, hw, bn, relu, pool, res):
+    from ewdml.ops import native
+    torch.manual_seed(0)
+    N = 4
+    conv = nn.Conv2d(cin, cout, k, stride, pad, bias=not bn or True).to(DEV)
+    conv.weight.data = _round(conv.weight.data).contiguous(memory_format=torch.channels_last)
+    conv.bias.data = _round(conv.bias.data)
+    bnm = nn.BatchNorm2d(cout).to(DEV) if bn else None
+    if bn:
+        bnm.weight.data = _round(torch.rand(cout, device=DEV) + 0.5)
+        bnm.bias.data = _round(torch.randn(cout, device=DEV) * 0.1)
+    x = _round(torch.randn(N, cin, hw, hw, device=DEV)).contiguous(memory_format=torch.channels_last)
+    ho = (hw + 2 * pad - k) // stride + 1
+    r = _round(torch.randn(N, cout, ho, ho, device=DEV)).contiguous(memory_format=torch.channels_last) if res else None
+    # ---- reference (fp32 torch) ----
+    xr = x.clone().requires_grad_(True)
+    rr = r.clone().requires_grad_(True) if res else None
+    conv_r = nn.Conv2d(cin, cout, k, stride, pad).to(DEV)
+    conv_r.load_state_dict(conv.state_dict())
+    bn_r = nn.BatchNorm2d(cout).to(DEV) if bn else None
+    if bn:
+        bn_r.load_state_dict(bnm.state_dict())
+    y = conv_r(xr)
+    if bn:
+        y = bn_r(y)
+    if res:
+        y = y + rr
+    if relu:
+        y = F.relu(y)
+    if pool:
+        y = F.max_pool2d(y, 2, 2)
+    go = _round(torch.randn_like(y))
+    y.backward(go)
+    # ---- native ----
+    xn = x.clone().requires_grad_(True)
+    rn = r.clone().requires_grad_(True) if res else None
+    for p in list(conv.parameters()) + (list(bnm.parameters()) if bn else []):
+        p.grad = None
+    out = native.conv_block(xn, conv, bnm, relu=relu, residual=rn, pool=pool)
+    out.backward(go.to(torch.bfloat16))
+    torch.cuda.synchronize()
+    _close(out, y, name="out")
+    _close(xn.grad, xr.grad, name="dx")
+    _close(conv.weight.grad, conv_r.weight.grad, name="dW")
+    if bn:
+        _close(bnm.weight.grad, bn_r.weight.grad, name="dgamma")
+        _close(bnm.bias.grad, bn_r.bias.grad, name="dbeta")
+        _close(bnm.running_mean, bn_r.running_mean, tol=1e-2, name="running_mean")
+        _close(bnm.running_var, bn_r.running_var, tol=1e-2, name="running_var")
+    else:
+        _close(conv.bias.grad, conv_r.bias.grad, name="dbias")
+    if res:
+        _close(rn.grad, rr.grad, name="dres")
+
+
+@pytest.mark.parametrize("B,fin,fout,relu", [(128, 512, 512, True), (128, 512, 10, False), (64, 800, 500, False), (37, 2048, 10, False)])
+def test_linear_block(B, fin, fout, relu):
+    from ewdml.ops import native
+    torch.manual_seed(1)
+    lin = nn.Linear(fin, fout).to(DEV)
+    lin.weight.data = _round(lin.weight.data); lin.bias.data = _round(lin.bias.data)
+    x = _round(torch.randn(B, fin, device=DEV))
+    xr = x.clone().requires_grad_(True)
+    lr_ = nn.Linear(fin, fout).to(DEV); lr_.load_state_dict(lin.state_dict())
+    y = lr_(xr)
+    y = F.relu(y) if relu else y
+    go = _round(torch.randn_like(y))
+    y.backward(go)
+    xn = x.clone().to(torch.bfloat16).requires_grad_(True)
+    out = native.linear_block(xn, lin, relu=relu)
+    out.backward(go.to(torch.bfloat16))
+    torch.cuda.synchronize()
+    _close(out, y, name="out"); _close(xn.grad, xr.grad, name="dx")
+    _close(lin.weight.grad, lr_.weight.grad, name="dW"); _close(lin.bias.grad, lr_.bias.grad, name="db")
+
+
+def test_cross_entropy_and_avgpool_and_dropout():
+    from ewdml.ops import native
+    torch.manual_seed(2)
+    logits = _round(torch.randn(128, 10, device=DEV) * 3)
+    tgt = torch.randint(0, 10, (128,), device=DEV)
+    lr_ = logits.clone().requires_grad_(True)
+    ref = F.cross_entropy(lr_, tgt); ref.backward()
+    ln = logits.clone().to(torch.bfloat16).requires_grad_(True)
+    loss = native.cross_entropy(ln, tgt); loss.backward()
+    assert abs(loss.item() - ref.item()) < 2e-3
+    _close(ln.grad, lr_.grad, tol=2e-2, name="dlogits")
+    x = _round(torch.randn(8, 64, 4, 4, device=DEV)).contiguous(memory_format=torch.channels_last)
+    xr = x.clone().requires_grad_(True); yr = F.avg_pool2d(xr, 4); yr.sum().backward()
+    xn = x.clone().to(torch.bfloat16).requires_grad_(True); yn = native.avg_pool(xn, 4); yn.float().sum().backward()
+    _close(yn, yr, tol=1e-2, name="avgpool"); _close(xn.grad, xr.grad, tol=1e-2, name="avgpool dx")
+    d = torch.ones(1 << 16, device=DEV, dtype=torch.bfloat16, requires_grad=True)
+    y = native.dropout(d, 0.5)
+    keep = (y != 0).float().mean().item()
+    assert 0.47 < keep < 0.53 and abs(y.float().max().item() - 2.0) < 1e-3
+    y.float().sum().backward()
+    assert torch.equal(d.grad != 0, y != 0)
+
+
+@pytest.mark.parametrize("name,shape", [("VGG11", (16, 3, 32, 32)), ("ResNet18", (8, 3, 32, 32)), ("ResNet50", (8, 3, 32, 32))])
+def test_whole_model_native_matches_torch(name, shape):
+    """Same weights, same batch: native loss close to fp32 torch, per-tensor gradient cosine > 0.98."""
+    from ewdml.models import build_model
+    from ewdml.ops import layers as L
+    from ewdml.parallel.flat import FlatModel
+    torch.manual_seed(3)
+    m_ref = build_model(name, 10).to(DEV)
+    m_nat = build_model(name, 10)
+    m_nat.load_state_dict(m_ref.state_dict())
+    flat = FlatModel(m_nat, torch.device(DEV), channels_last=True, with_bf16=True)
+    x = torch.randn(*shape, device=DEV)
+    y = torch.randint(0, 10, (shape[0],), device=DEV)
+    for m in (m_ref, m_nat):
+        m.train()
+        for mod in m.modules():
+            if isinstance(mod, nn.Dropout):
+                mod.p = 0.0
+    L.set_compute("torch")
+    loss_ref = F.cross_entropy(m_ref(x), y); loss_ref.backward()
+    # second reference: the library bf16 path (autocast); the native kernels must be as faithful as it is
+    m_amp = build_model(name, 10).to(DEV)
+    m_amp.load_state_dict(m_ref.state_dict())
+    m_amp.train()
+    for mod in m_amp.modules():
+        if isinstance(mod, nn.Dropout):
+            mod.p = 0.0
+    with torch.autocast("cuda", dtype=torch.bfloat16):
+        loss_amp = F.cross_entropy(m_amp(x).float(), y)
+    loss_amp.backward()
+    L.set_compute("native")
+    try:
+        flat.zero_grad()
+        logits = m_nat(x.contiguous(memory_format=torch.channels_last))
+        loss = L.cross_entropy(logits, y); loss.backward()
+        torch.cuda.synchronize()
+    finally:
+        L.set_compute("torch")
+    assert abs(loss.item() - loss_ref.item()) < 0.02 * max(1.0, abs(loss_ref.item()))
+    cos_nat, cos_amp = [], []
+    for (n, p), pr, pa in zip(m_nat.named_parameters(), m_ref.parameters(), m_amp.parameters()):
+        g, gr, ga = p.grad.float().flatten(), pr.grad.float().flatten(), pa.grad.float().flatten()
+        if gr.norm() < 1e-5 or (n.endswith("bias") and p.dim() == 1 and "bn" not in n and "features" in n):
+            continue                      # conv bias in front of BatchNorm: true gradient is 0
+        cos_nat.append(F.cosine_similarity(g, gr, dim=0).item())
+        cos_amp.append(F.cosine_similarity(ga, gr, dim=0).item())
+    mean_nat, mean_amp = sum(cos_nat) / len(cos_nat), sum(cos_amp) / len(cos_amp)
+    assert mean_nat >= mean_amp - 0.03, (mean_nat, mean_amp)
+    assert min(cos_nat) >= min(cos_amp) - 0.15, (min(cos_nat), min(cos_amp))
