@@ -50,6 +50,7 @@ def parse():
     p.add_argument("--dtype", type=str, default="bf16")
     p.add_argument("--no-e2e", action="store_true")
     p.add_argument("--no-flush", action="store_true")
+    p.add_argument("--no-graph", action="store_true", help="do not capture the step in a CUDA graph")
     return p.parse_args()
 
 
@@ -180,10 +181,15 @@ def run_ewdml(a):
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t[0]), float(t[1]), last
 
-    # ---- warm-up -----------------------------------------------------------------------------
+    # ---- warm-up (eager), then optional CUDA-graph capture of the whole step, then graph warm-up -----
     for _ in range(max(3, a.warmup)):
         one_step(x0, y0)
     barrier()
+    if not a.no_graph and role == "worker":
+        tr.capture(x0, y0)
+        for _ in range(max(3, a.warmup)):
+            one_step(x0, y0)
+        barrier()
     err = tr.check_device_error()
     if err:
         raise SystemExit(f"device error word {err:#x} after warm-up")
@@ -191,9 +197,9 @@ def run_ewdml(a):
     sampler = ClockSampler(local_rank) if rank == 0 else None
     if sampler:
         sampler.start()
-    l0 = L.launches()
+    l0 = tr.own_launches()
     ms, wall_ms, _ = timed(a.steps, e2e=False)
-    launches = L.launches() - l0
+    launches = tr.own_launches() - l0
     clocks = sampler.stop() if sampler else None
     stats = tr.exchange.step  # noqa: F841 (keep reference alive)
     e2e = None
@@ -225,7 +231,7 @@ def run_ewdml(a):
                    "seq_len": None, "image": list(tr.input_spec()[1:]),
                    "parallelism": f"dp{world}" + ("(1 server)" if a.exchange == "ps" else ""),
                    "compressor": a.compressor, "topk_ratio": a.topk_ratio, "qsgd_levels": a.qsgd_levels,
-                   "exchange": a.exchange, "compute": a.compute,
+                   "exchange": a.exchange, "compute": a.compute, "cuda_graph": tr.graph is not None,
                    "l2": "none" if a.no_flush else "256 MiB buffer overwritten every step inside the timed region"},
         "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "device_ms_total": ms, "wall_ms_total": wall_ms,
         "exchange": None if st is None else {"bytes_sent_per_step": st.bytes_sent, "bytes_recv_per_step": st.bytes_recv,

@@ -24,12 +24,14 @@
 #define FLAG_ENTRY(p) (p)
 #define FLAG_EXIT(p) (EWDML_MAX_PEERS + (p))
 #define FLAG_BAR(p) (2 * EWDML_MAX_PEERS + (p))
+#define SEQ(a) ((a).state ? (a).state[0] : (a).seq)
 
 struct ArArgs {
     ewdml_comm comm;
     int64_t n4;             // number of float4 vectors
     float scale;
     uint32_t seq;
+    const uint32_t* state;  // optional device step state (seq at [0])
     uint32_t* work_counter; // device counter used to elect the last CTA (self-resetting)
     uint32_t* err_word;
     unsigned long long spin_limit;
@@ -43,12 +45,12 @@ __device__ __forceinline__ void entry_barrier(const ArArgs& a, int* s_ok) {
     const int tid = threadIdx.x, W = a.comm.world, me = a.comm.rank;
     if (blockIdx.x == 0 && tid < W) {
         __threadfence_system();
-        st_release_sys(a.comm.peer_flags[tid] + FLAG_ENTRY(me), a.seq);
+        st_release_sys(a.comm.peer_flags[tid] + FLAG_ENTRY(me), SEQ(a));
     }
     if (tid == 0) *s_ok = 1;
     __syncthreads();
     if (tid < W)
-        if (!wait_flag_ge(a.comm.flags + FLAG_ENTRY(tid), a.seq, a.spin_limit, a.err_word, (uint32_t)EWDML_ERR_TIMEOUT))
+        if (!wait_flag_ge(a.comm.flags + FLAG_ENTRY(tid), SEQ(a), a.spin_limit, a.err_word, (uint32_t)EWDML_ERR_TIMEOUT))
             *s_ok = 0;
     __syncthreads();
 }
@@ -65,8 +67,8 @@ __device__ __forceinline__ void exit_barrier(const ArArgs& a) {
     if (!s_last) return;
     if (tid < W) {
         __threadfence_system();
-        st_release_sys(a.comm.peer_flags[tid] + FLAG_EXIT(me), a.seq);
-        wait_flag_ge(a.comm.flags + FLAG_EXIT(tid), a.seq, a.spin_limit, a.err_word, (uint32_t)EWDML_ERR_TIMEOUT);
+        st_release_sys(a.comm.peer_flags[tid] + FLAG_EXIT(me), SEQ(a));
+        wait_flag_ge(a.comm.flags + FLAG_EXIT(tid), SEQ(a), a.spin_limit, a.err_word, (uint32_t)EWDML_ERR_TIMEOUT);
     }
     if (tid == 0) *a.work_counter = 0;
 }
@@ -131,8 +133,8 @@ __global__ void k_barrier(const ArArgs a) {
     const int tid = threadIdx.x, W = a.comm.world, me = a.comm.rank;
     if (tid < W) {
         __threadfence_system();
-        st_release_sys(a.comm.peer_flags[tid] + FLAG_BAR(me), a.seq);
-        wait_flag_ge(a.comm.flags + FLAG_BAR(tid), a.seq, a.spin_limit, a.err_word, (uint32_t)EWDML_ERR_TIMEOUT);
+        st_release_sys(a.comm.peer_flags[tid] + FLAG_BAR(me), SEQ(a));
+        wait_flag_ge(a.comm.flags + FLAG_BAR(tid), SEQ(a), a.spin_limit, a.err_word, (uint32_t)EWDML_ERR_TIMEOUT);
     }
 }
 
@@ -151,12 +153,19 @@ static int fill_args(ArArgs& a, const ewdml_comm* comm, int64_t n, float scale, 
     return a.err_word ? 0 : EWDML_ERR_CUDA;
 }
 
+extern "C" int ewdml_allreduce_state(const ewdml_comm* comm, int64_t n, float scale, int algo, uint32_t seq, const uint32_t* state,
+                                     uint32_t* work_counter, void* stream);
 extern "C" int ewdml_allreduce(const ewdml_comm* comm, int64_t n, float scale, int algo, uint32_t seq,
                                uint32_t* work_counter, void* stream) {
+    return ewdml_allreduce_state(comm, n, scale, algo, seq, nullptr, work_counter, stream);
+}
+extern "C" int ewdml_allreduce_state(const ewdml_comm* comm, int64_t n, float scale, int algo, uint32_t seq, const uint32_t* state,
+                                     uint32_t* work_counter, void* stream) {
     EWDML_CHECK_ARG(comm && comm->world >= 1 && comm->world <= EWDML_MAX_PEERS && comm->rank >= 0 &&
                     comm->rank < comm->world && n > 0 && n % 4 == 0 && work_counter);
     ArArgs a;
     if (fill_args(a, comm, n, scale, seq, work_counter)) return EWDML_ERR_CUDA;
+    a.state = state;
     cudaStream_t st = (cudaStream_t)stream;
     if (algo == EWDML_AR_AUTO) algo = (n * 4 <= (1 << 18)) ? EWDML_AR_ONESHOT : EWDML_AR_TWOSHOT;
     const int sms = sm_count();

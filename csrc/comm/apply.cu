@@ -12,7 +12,8 @@
 struct ApplyArgs {
     const TileDesc* tiles;
     SlotLayout layout;
-    ewdml_sources srcs;
+    ewdml_sources srcs[2];             // [parity]
+    const uint32_t* state;             // optional device step state {seq, step, first}
     int mode, val, code_bits, levels, ntiles, out_mode;
     uint32_t seq;
     float divisor;
@@ -39,13 +40,13 @@ __device__ __forceinline__ float decode_value(uint32_t code, int cw, int val, fl
     return __fmul_rn(dq, sign ? -lvl : lvl);
 }
 
-__device__ __forceinline__ void sgd_update4(const ApplyArgs& a, size_t idx, float4 g) {
+__device__ __forceinline__ void sgd_update4(const ApplyArgs& a, size_t idx, float4 g, const bool first_step) {
     float4 p = *reinterpret_cast<const float4*>(a.param + idx);
     float gg[4] = {g.x, g.y, g.z, g.w};
     float pp[4] = {p.x, p.y, p.z, p.w};
     float mm[4] = {0.f, 0.f, 0.f, 0.f};
     const bool use_m = a.sgd.momentum != 0.f && a.momentum != nullptr;
-    if (use_m && !a.sgd.first_step) {
+    if (use_m && !first_step) {
         float4 m = *reinterpret_cast<const float4*>(a.momentum + idx);
         mm[0] = m.x; mm[1] = m.y; mm[2] = m.z; mm[3] = m.w;
     }
@@ -54,7 +55,7 @@ __device__ __forceinline__ void sgd_update4(const ApplyArgs& a, size_t idx, floa
         float d = gg[q];
         if (a.sgd.weight_decay != 0.f) d = __fmaf_rn(a.sgd.weight_decay, pp[q], d);
         if (use_m) {
-            float buf = a.sgd.first_step ? d : __fadd_rn(__fmul_rn(a.sgd.momentum, mm[q]),
+            float buf = first_step ? d : __fadd_rn(__fmul_rn(a.sgd.momentum, mm[q]),
                                                          __fmul_rn(1.f - a.sgd.dampening, d));
             mm[q] = buf;
             d = a.sgd.nesterov ? __fmaf_rn(a.sgd.momentum, buf, d) : buf;
@@ -77,23 +78,26 @@ __global__ void __launch_bounds__(256) k_recv_apply(const ApplyArgs a) {
     __shared__ uint32_t scan_smem[40];
     __shared__ int s_ok;
     const int tid = threadIdx.x;
+    const uint32_t seq = a.state ? a.state[0] : a.seq;
+    const ewdml_sources& S = a.srcs[a.state ? (seq & 1u) : 0u];
     // ---- acquire: every CTA waits until all sources have published this sequence number -------
     if (tid == 0) s_ok = 1;
     __syncthreads();
-    if (tid < a.srcs.n && a.srcs.flag[tid] != nullptr) {
-        if (!wait_flag_ge(a.srcs.flag[tid], a.seq, a.spin_limit, a.err_word, (uint32_t)EWDML_ERR_TIMEOUT)) s_ok = 0;
+    if (tid < S.n && S.flag[tid] != nullptr) {
+        if (!wait_flag_ge(S.flag[tid], seq, a.spin_limit, a.err_word, (uint32_t)EWDML_ERR_TIMEOUT)) s_ok = 0;
     }
     __syncthreads();
     if (!s_ok) return;
     const float inv_scale = a.divisor;
+    const bool first_step = a.state ? (a.state[2] != 0) : (a.sgd.first_step != 0);
     for (int t = blockIdx.x; t < a.ntiles; t += gridDim.x) {
         const TileDesc td = a.tiles[t];
         const uint32_t n4 = (td.len + 3) >> 2;
         if (a.mode != EWDML_MODE_DENSE) {
             for (uint32_t i = tid; i < n4; i += 256) reinterpret_cast<float4*>(acc)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
             __syncthreads();
-            for (int s = 0; s < a.srcs.n; ++s) {
-                const char* slot = (const char*)a.srcs.slot[s];
+            for (int s = 0; s < S.n; ++s) {
+                const char* slot = (const char*)S.slot[s];
                 const uint2 de = *reinterpret_cast<const uint2*>(slot + a.layout.dir + (size_t)t * 8);
                 const uint32_t cnt = de.y;
                 const float norm = reinterpret_cast<const float*>(slot + a.layout.norms)[td.seg];
@@ -131,9 +135,9 @@ __global__ void __launch_bounds__(256) k_recv_apply(const ApplyArgs a) {
             float4 g;
             if (a.mode == EWDML_MODE_DENSE) {
                 g = make_float4(0.f, 0.f, 0.f, 0.f);
-                for (int s = 0; s < a.srcs.n; ++s) {
+                for (int s = 0; s < S.n; ++s) {
                     const float4 v = *reinterpret_cast<const float4*>(
-                        (const char*)a.srcs.slot[s] + a.layout.data + ((size_t)td.start + i * 4) * 4);
+                        (const char*)S.slot[s] + a.layout.data + ((size_t)td.start + i * 4) * 4);
                     g.x += v.x; g.y += v.y; g.z += v.z; g.w += v.w;
                 }
             } else {
@@ -143,7 +147,7 @@ __global__ void __launch_bounds__(256) k_recv_apply(const ApplyArgs a) {
             g.z = __fdiv_rn(g.z, inv_scale); g.w = __fdiv_rn(g.w, inv_scale);
             const size_t idx = (size_t)td.start + i * 4;
             if (a.out_mode == EWDML_OUT_SGD) {
-                sgd_update4(a, idx, g);
+                sgd_update4(a, idx, g, first_step);
             } else if (a.out_mode == EWDML_OUT_GRAD) {
                 *reinterpret_cast<float4*>(a.out + idx) = g;
             } else {  // ASSIGN: weights pulled from the server
@@ -166,7 +170,7 @@ __global__ void __launch_bounds__(256) k_sgd_apply(const float* __restrict__ gra
     for (int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x; i < n4; i += (int64_t)gridDim.x * 256) {
         float4 g = *reinterpret_cast<const float4*>(grad + i * 4);
         g.x *= gscale; g.y *= gscale; g.z *= gscale; g.w *= gscale;
-        sgd_update4(a, (size_t)i * 4, g);
+        sgd_update4(a, (size_t)i * 4, g, a.state ? (a.state[2] != 0) : (a.sgd.first_step != 0));
     }
 }
 
@@ -181,16 +185,17 @@ static int num_sms() {
     return sms;
 }
 
-extern "C" int ewdml_recv_apply(ewdml_plan* p, const ewdml_sources* srcs, uint32_t seq, float divisor, int out_mode,
-                                const ewdml_sgd* sgd, float* param, float* momentum, void* param_bf16, float* out,
-                                void* stream) {
+static int recv_impl(ewdml_plan* p, const ewdml_sources* srcs, const ewdml_sources* srcs_odd, const uint32_t* state, uint32_t seq,
+                     float divisor, int out_mode, const ewdml_sgd* sgd, float* param, float* momentum, void* param_bf16, float* out,
+                     void* stream) {
     EWDML_CHECK_ARG(p && srcs && srcs->n >= 1 && srcs->n <= EWDML_MAX_PEERS && divisor != 0.f);
     EWDML_CHECK_ARG(out_mode != EWDML_OUT_SGD || (sgd && param));
     EWDML_CHECK_ARG(out_mode != EWDML_OUT_GRAD || out);
     EWDML_CHECK_ARG(out_mode != EWDML_OUT_ASSIGN || param);
     ApplyArgs a;
     memset(&a, 0, sizeof(a));
-    a.tiles = p->d_tile; a.layout = p->layout; a.srcs = *srcs;
+    a.tiles = p->d_tile; a.layout = p->layout; a.srcs[0] = *srcs; a.srcs[1] = srcs_odd ? *srcs_odd : *srcs;
+    a.state = state;
     a.mode = p->codec.mode; a.val = p->codec.val; a.code_bits = p->codec.code_bits; a.levels = p->codec.levels;
     a.ntiles = p->ntiles; a.out_mode = out_mode; a.seq = seq; a.divisor = divisor;
     if (sgd) a.sgd = *sgd;
@@ -205,12 +210,48 @@ extern "C" int ewdml_recv_apply(ewdml_plan* p, const ewdml_sources* srcs, uint32
     return 0;
 }
 
+extern "C" int ewdml_recv_apply(ewdml_plan* p, const ewdml_sources* srcs, uint32_t seq, float divisor, int out_mode,
+                                const ewdml_sgd* sgd, float* param, float* momentum, void* param_bf16, float* out,
+                                void* stream) {
+    return recv_impl(p, srcs, nullptr, nullptr, seq, divisor, out_mode, sgd, param, momentum, param_bf16, out, stream);
+}
+
+extern "C" int ewdml_recv_apply_state(ewdml_plan* p, const ewdml_sources* srcs_even, const ewdml_sources* srcs_odd,
+                                      const uint32_t* state, float divisor, int out_mode, const ewdml_sgd* sgd, float* param,
+                                      float* momentum, void* param_bf16, float* out, void* stream) {
+    EWDML_CHECK_ARG(state && srcs_odd);
+    return recv_impl(p, srcs_even, srcs_odd, state, 0, divisor, out_mode, sgd, param, momentum, param_bf16, out, stream);
+}
+
+// Device step state {seq, step, first, applies}.  Called once at the start of every optimizer application:
+// step += 1 (RNG stream position), first = (no update applied yet), applies += 1, and for exchanges seq += 1
+// (flag sequence number / slot parity).  Everything downstream reads the state from memory, so a captured
+// CUDA graph replays correctly.
+__global__ void k_state_advance(uint32_t* st, int bump_seq) {
+    if (bump_seq) st[0] = st[0] + 1;
+    st[1] = st[1] + 1;
+    st[2] = st[3] == 0 ? 1u : 0u;
+    st[3] = st[3] + 1;
+}
+extern "C" int ewdml_state_advance(uint32_t* state, int bump_seq, void* stream) {
+    EWDML_CHECK_ARG(state);
+    k_state_advance<<<1, 1, 0, (cudaStream_t)stream>>>(state, bump_seq);
+    EWDML_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int ewdml_sgd_apply_state(const float* grad, float* param, float* momentum, void* param_bf16, int64_t n,
+                                     const ewdml_sgd* sgd, float grad_scale, const uint32_t* state, void* stream);
 extern "C" int ewdml_sgd_apply(const float* grad, float* param, float* momentum, void* param_bf16, int64_t n,
                                const ewdml_sgd* sgd, float grad_scale, void* stream) {
+    return ewdml_sgd_apply_state(grad, param, momentum, param_bf16, n, sgd, grad_scale, nullptr, stream);
+}
+extern "C" int ewdml_sgd_apply_state(const float* grad, float* param, float* momentum, void* param_bf16, int64_t n,
+                                     const ewdml_sgd* sgd, float grad_scale, const uint32_t* state, void* stream) {
     EWDML_CHECK_ARG(grad && param && sgd && n > 0 && n % 4 == 0);
     ApplyArgs a;
     memset(&a, 0, sizeof(a));
-    a.sgd = *sgd; a.param = param; a.momentum = momentum; a.param_bf16 = (__nv_bfloat16*)param_bf16;
+    a.sgd = *sgd; a.param = param; a.momentum = momentum; a.param_bf16 = (__nv_bfloat16*)param_bf16; a.state = state;
     int64_t n4 = n / 4;
     int64_t want = (n4 + 255) / 256;
     int grid = (int)(want < 8 * num_sms() ? want : 8 * num_sms());

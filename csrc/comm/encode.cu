@@ -25,7 +25,8 @@ struct EncodeArgs {
     Counters* ctr;
     uint32_t* stats;
     SlotLayout layout;
-    ewdml_dests dests;
+    ewdml_dests dests[2];              // [parity]; both equal when no device step state is used
+    const uint32_t* state;             // optional device step state {seq, step, first}: makes the launch graph-replayable
     int mode, sel, val, code_bits, levels, nseg, ntiles;
     uint32_t seq, seed_lo, seed_hi, step, rng_stream;
     uint32_t* err_word;
@@ -49,13 +50,16 @@ __global__ void __launch_bounds__(256) k_encode_push(const EncodeArgs a) {
 
     const TileDesc td = a.tiles[blockIdx.x];
     const int tid = threadIdx.x;
+    const uint32_t seq = a.state ? a.state[0] : a.seq;
+    const uint32_t step = a.state ? a.state[1] : a.step;
+    const ewdml_dests& D = a.dests[a.state ? (seq & 1u) : 0u];
 
     if constexpr (MODE == EWDML_MODE_DENSE) {
         // plain tile copy into every destination (uncompressed push / allgather)
         const float* src = a.grad + td.start;
         const uint32_t n4 = (td.len + 3) >> 2;
-        for (int d = 0; d < a.dests.n; ++d) {
-            char* dst = (char*)a.dests.slot[d] + a.layout.data + (size_t)td.start * 4;
+        for (int d = 0; d < D.n; ++d) {
+            char* dst = (char*)D.slot[d] + a.layout.data + (size_t)td.start * 4;
             for (uint32_t i = tid; i < n4; i += 256)
                 st_na_v4(dst + (size_t)i * 16, *reinterpret_cast<const uint4*>(src + i * 4));
         }
@@ -103,7 +107,7 @@ __global__ void __launch_bounds__(256) k_encode_push(const EncodeArgs a) {
                     const uint32_t gidx = td.start + e;     // global element index -> RNG counter
                     const uint32_t group = gidx >> 2;
                     if (group != cached_group) {
-                        rnd = philox4x32_10(group, a.rng_stream, 0u, 0u, a.seed_lo, a.step);
+                        rnd = philox4x32_10(group, a.rng_stream, 0u, 0u, a.seed_lo, step);
                         cached_group = group;
                     }
                     const uint32_t ln = gidx & 3;
@@ -153,8 +157,8 @@ __global__ void __launch_bounds__(256) k_encode_push(const EncodeArgs a) {
         const uint32_t off = s_off;
         const bool overflow = a.ctr->overflow != 0;
         // ---- push to every destination ------------------------------------------------------
-        for (int d = 0; d < a.dests.n; ++d) {
-            char* slot = (char*)a.dests.slot[d];
+        for (int d = 0; d < D.n; ++d) {
+            char* slot = (char*)D.slot[d];
             if (tid == 0) {
                 uint2 de = make_uint2(off, overflow ? 0u : total);
                 *reinterpret_cast<uint2*>(slot + a.layout.dir + (size_t)blockIdx.x * 8) = de;
@@ -183,8 +187,8 @@ __global__ void __launch_bounds__(256) k_encode_push(const EncodeArgs a) {
         const uint32_t entries = a.ctr->entries;
         const uint32_t data_bytes = (uint32_t)a.ctr->data_used;
         const uint32_t overflow = a.ctr->overflow;
-        for (int d = 0; d < a.dests.n; ++d) {
-            char* slot = (char*)a.dests.slot[d];
+        for (int d = 0; d < D.n; ++d) {
+            char* slot = (char*)D.slot[d];
             float* norms = reinterpret_cast<float*>(slot + a.layout.norms);
             if (MODE != EWDML_MODE_DENSE)
                 for (int s = tid; s < a.nseg; s += 256) norms[s] = a.info[s].norm;
@@ -193,14 +197,14 @@ __global__ void __launch_bounds__(256) k_encode_push(const EncodeArgs a) {
                 hdr[HDR_ENTRIES] = entries;
                 hdr[HDR_DATA_BYTES] = data_bytes;
                 hdr[HDR_MODE] = (uint32_t)MODE | ((uint32_t)a.code_bits << 8) | (overflow << 31);
-                hdr[HDR_SEQ] = a.seq;
+                hdr[HDR_SEQ] = seq;
             }
         }
         __syncthreads();
         if (tid == 0) {
             __threadfence_system();
-            for (int d = 0; d < a.dests.n; ++d)
-                if (a.dests.flag[d]) st_release_sys(a.dests.flag[d], a.seq);
+            for (int d = 0; d < D.n; ++d)
+                if (D.flag[d]) st_release_sys(D.flag[d], seq);
             a.stats[0] = entries;
             a.stats[1] = data_bytes;
             a.stats[3] = overflow ? (uint32_t)EWDML_ERR_OVERFLOW : 0u;
@@ -220,8 +224,8 @@ static size_t encode_smem_bytes(const ewdml_codec& c) {
     return (size_t)(8448 + 4096 + c.code_bits * 256 + 4) * 4;
 }
 
-extern "C" int ewdml_send(ewdml_plan* p, const float* grad, const ewdml_dests* dests, uint32_t seq, uint64_t seed,
-                          uint32_t step, uint32_t rng_stream, void* stream) {
+static int send_impl(ewdml_plan* p, const float* grad, const ewdml_dests* dests, const ewdml_dests* dests_odd,
+                     const uint32_t* state, uint32_t seq, uint64_t seed, uint32_t step, uint32_t rng_stream, void* stream) {
     EWDML_CHECK_ARG(p && grad && dests && dests->n >= 1 && dests->n <= EWDML_MAX_PEERS);
     cudaStream_t st = (cudaStream_t)stream;
     int rc = ewdml_launch_select(p, grad, st);
@@ -229,7 +233,8 @@ extern "C" int ewdml_send(ewdml_plan* p, const float* grad, const ewdml_dests* d
     EncodeArgs a;
     memset(&a, 0, sizeof(a));
     a.grad = grad; a.tiles = p->d_tile; a.segs = p->d_seg; a.info = p->d_seginfo; a.ctr = p->d_ctr;
-    a.stats = p->d_stats; a.layout = p->layout; a.dests = *dests;
+    a.stats = p->d_stats; a.layout = p->layout; a.dests[0] = *dests; a.dests[1] = dests_odd ? *dests_odd : *dests;
+    a.state = state;
     a.mode = p->codec.mode; a.sel = p->codec.sel; a.val = p->codec.val; a.code_bits = p->codec.code_bits;
     a.levels = p->codec.levels; a.nseg = p->nseg; a.ntiles = p->ntiles;
     a.seq = seq; a.seed_lo = (uint32_t)seed; a.seed_hi = (uint32_t)(seed >> 32); a.step = step;
@@ -262,4 +267,17 @@ extern "C" int ewdml_send(ewdml_plan* p, const float* grad, const ewdml_dests* d
     EWDML_LAUNCH_CHECK();
     ewdml_counter_add(EWDML_CTR_SEND_CALLS, 1);
     return 0;
+}
+
+extern "C" int ewdml_send(ewdml_plan* p, const float* grad, const ewdml_dests* dests, uint32_t seq, uint64_t seed,
+                          uint32_t step, uint32_t rng_stream, void* stream) {
+    return send_impl(p, grad, dests, nullptr, nullptr, seq, seed, step, rng_stream, stream);
+}
+
+// Graph-replayable form: sequence number, RNG step and slot parity come from the device step state
+// (ewdml_state_advance), dests_even/dests_odd are the destination sets for even/odd sequence numbers.
+extern "C" int ewdml_send_state(ewdml_plan* p, const float* grad, const ewdml_dests* dests_even, const ewdml_dests* dests_odd,
+                                const uint32_t* state, uint64_t seed, uint32_t rng_stream, void* stream) {
+    EWDML_CHECK_ARG(state && dests_odd);
+    return send_impl(p, grad, dests_even, dests_odd, state, 0, seed, 0, rng_stream, stream);
 }

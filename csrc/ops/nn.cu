@@ -353,7 +353,8 @@ __global__ void __launch_bounds__(256) k_relu_fwd(const __nv_bfloat16* __restric
 
 // inverted dropout with a counter-based mask (recomputed in backward, nothing stored)
 __global__ void __launch_bounds__(256) k_dropout(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y, int64_t n, float p, float scale,
-                                                 uint32_t seed, uint32_t offset) {
+                                                 uint32_t seed, uint32_t offset, const uint32_t* __restrict__ step_ptr) {
+    if (step_ptr) offset += step_ptr[1] * 0x9E3779B1u;      // device step counter: fresh mask on every graph replay
     for (int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x; i < n; i += (int64_t)gridDim.x * 256) {
         Philox4 r = philox4x32_10((uint32_t)(i >> 2), offset, 0x9E37u, 0u, seed, 0xD409u);
         const uint32_t li = (uint32_t)i & 3u;
@@ -583,9 +584,9 @@ extern "C" int ewdml_relu_bwd(const void* dy, const void* y, void* dx, int64_t n
     NN_LAUNCH_CHECK();
     return 0;
 }
-extern "C" int ewdml_dropout(const void* x, void* y, int64_t n, float p, uint32_t seed, uint32_t offset, void* stream) {
+extern "C" int ewdml_dropout(const void* x, void* y, int64_t n, float p, uint32_t seed, uint32_t offset, const uint32_t* step_state, void* stream) {
     EWDML_CHECK_ARG(p >= 0.f && p < 1.f);
-    k_dropout<<<grid_for(n), 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)x, (__nv_bfloat16*)y, n, p, 1.f / (1.f - p), seed, offset);
+    k_dropout<<<grid_for(n), 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)x, (__nv_bfloat16*)y, n, p, 1.f / (1.f - p), seed, offset, step_state);
     NN_LAUNCH_CHECK();
     return 0;
 }

@@ -35,7 +35,7 @@ def _l():
             "ewdml_pad_rows_bf16": [vp, vp, i32, i32, i32, vp],
             "ewdml_relu_fwd": [vp, vp, i64, vp],
             "ewdml_relu_bwd": [vp, vp, vp, i64, vp],
-            "ewdml_dropout": [vp, vp, i64, f32, u32, u32, vp],
+            "ewdml_dropout": [vp, vp, i64, f32, u32, u32, vp, vp],
             "ewdml_avgpool_fwd": [vp, vp, i32, i32, i32, vp],
             "ewdml_avgpool_bwd": [vp, vp, i32, i32, i32, vp],
             "ewdml_xent": [vp, vp, vp, vp, i32, i32, i32, vp],
@@ -56,6 +56,9 @@ def _p(t: Optional[torch.Tensor]):
 
 
 OUT_BF16, OUT_F32, OUT_ACCUM = 0, 1, 2
+
+# device step state of the active trainer (uint32[4] tensor) -- lets dropout masks change on graph replays
+STEP_STATE = {"tensor": None}
 
 
 def gemm(a: torch.Tensor, b: torch.Tensor, a_mn: bool = False, b_mn: bool = False,
@@ -369,7 +372,7 @@ class _DropoutFn(torch.autograd.Function):
         off = _DropoutFn._counter[0] & 0xFFFFFFFF
         xc = x if x.is_contiguous() else x.contiguous()
         y = torch.empty_like(xc)
-        L.check(_l().ewdml_dropout(_p(xc), _p(y), xc.numel(), float(p), seed, off, _stream()), "dropout")
+        L.check(_l().ewdml_dropout(_p(xc), _p(y), xc.numel(), float(p), seed, off, _p(STEP_STATE["tensor"]), _stream()), "dropout")
         ctx.meta = (p, seed, off)
         return y
 
@@ -378,7 +381,7 @@ class _DropoutFn(torch.autograd.Function):
         p, seed, off = ctx.meta
         d = dy if dy.is_contiguous() else dy.contiguous()
         dx = torch.empty_like(d)
-        L.check(_l().ewdml_dropout(_p(d), _p(dx), d.numel(), float(p), seed, off, _stream()), "dropout_bwd")
+        L.check(_l().ewdml_dropout(_p(d), _p(dx), d.numel(), float(p), seed, off, _p(STEP_STATE["tensor"]), _stream()), "dropout_bwd")
         return dx, None
 
 

@@ -104,6 +104,36 @@ class ExchangePlan:
                                           C.byref(sgd) if sgd is not None else None, ptr(param), ptr(momentum),
                                           ptr(param_bf16), ptr(out), self._stream()), "ewdml_recv_apply")
 
+    @staticmethod
+    def _dests(pairs) -> L.Dests:
+        d = L.Dests()
+        d.n = len(pairs)
+        for i, (slot, flag) in enumerate(pairs):
+            d.slot[i], d.flag[i] = slot, flag
+        return d
+
+    @staticmethod
+    def _sources(pairs) -> L.Sources:
+        s = L.Sources()
+        s.n = len(pairs)
+        for i, (slot, flag) in enumerate(pairs):
+            s.slot[i], s.flag[i] = slot, flag
+        return s
+
+    def send_state(self, grad: torch.Tensor, dests_even, dests_odd, state: torch.Tensor, seed: int, rng_stream: int) -> None:
+        """Graph-replayable send: sequence number / RNG step / parity come from the device ``state``."""
+        L.check(self.lib.ewdml_send_state(self._h, C.c_void_p(grad.data_ptr()), C.byref(self._dests(dests_even)),
+                                          C.byref(self._dests(dests_odd)), C.c_void_p(state.data_ptr()),
+                                          seed & 0xFFFFFFFFFFFFFFFF, rng_stream, self._stream()), "ewdml_send_state")
+
+    def recv_apply_state(self, srcs_even, srcs_odd, state: torch.Tensor, divisor: float, out_mode: int,
+                         sgd: Optional[L.Sgd] = None, param=None, momentum=None, param_bf16=None, out=None) -> None:
+        ptr = lambda t: C.c_void_p(t.data_ptr()) if t is not None else C.c_void_p(0)
+        L.check(self.lib.ewdml_recv_apply_state(self._h, C.byref(self._sources(srcs_even)), C.byref(self._sources(srcs_odd)),
+                                                C.c_void_p(state.data_ptr()), float(divisor), out_mode,
+                                                C.byref(sgd) if sgd is not None else None, ptr(param), ptr(momentum),
+                                                ptr(param_bf16), ptr(out), self._stream()), "ewdml_recv_apply_state")
+
     def stats(self) -> dict:
         out = (C.c_int64 * 4)()
         L.check(self.lib.ewdml_plan_read_stats(self._h, out, self._stream()), "read_stats")
@@ -165,8 +195,9 @@ class _NativeBase(Exchange):
         self.flat, self.cfg, self.optimizer, self.pg = flat, cfg, optimizer, pg
         self.rank, self.world = pg.rank, pg.world
         self.lib = L.load()
-        self.q = 0                      # exchange counter (flag sequence number)
-        self.first = True               # momentum buffer not initialised yet
+        # device step state {seq, step, first, applies}: no per-step value is baked into a launch, so the whole
+        # step (including these kernels) can be captured in a CUDA graph and replayed
+        self.state = torch.zeros(4, dtype=torch.int32, device=pg.device)
         self._ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
         self._last_payload = 0
 
@@ -188,14 +219,26 @@ class _NativeBase(Exchange):
         # BN running statistics start equal as well (they are never exchanged afterwards)
         # -- every rank builds the model from the same seed, so they already are.
 
-    def local_step(self) -> ExchangeStats:
-        sgd = make_sgd(self.cfg, self.first)
-        self.first = False
+    def _rec(self, i: int, stream) -> None:
+        if not torch.cuda.is_current_stream_capturing():      # timing events are not recorded into CUDA graphs
+            self._ev[i].record(stream)
+
+    def _advance(self, bump_seq: bool) -> None:
+        L.check(self.lib.ewdml_state_advance(C.c_void_p(self.state.data_ptr()), int(bump_seq), ExchangePlan._stream()),
+                "state_advance")
+
+    def _sgd_apply(self) -> None:
+        sgd = make_sgd(self.cfg, False)
         f = self.flat
-        L.check(self.lib.ewdml_sgd_apply(C.c_void_p(f.grad.data_ptr()), C.c_void_p(f.param.data_ptr()),
-                                         C.c_void_p(f.momentum.data_ptr()) if f.momentum is not None else None,
-                                         C.c_void_p(f.param_bf16.data_ptr()) if f.param_bf16 is not None else None,
-                                         f.total, C.byref(sgd), 1.0, ExchangePlan._stream()), "sgd_apply")
+        L.check(self.lib.ewdml_sgd_apply_state(C.c_void_p(f.grad.data_ptr()), C.c_void_p(f.param.data_ptr()),
+                                               C.c_void_p(f.momentum.data_ptr()) if f.momentum is not None else None,
+                                               C.c_void_p(f.param_bf16.data_ptr()) if f.param_bf16 is not None else None,
+                                               f.total, C.byref(sgd), 1.0, C.c_void_p(self.state.data_ptr()),
+                                               ExchangePlan._stream()), "sgd_apply")
+
+    def local_step(self) -> ExchangeStats:
+        self._advance(False)
+        self._sgd_apply()
         return ExchangeStats()
 
     def _finish_stats(self, st: ExchangeStats, plan: Optional[ExchangePlan], n_remote_out: int, n_remote_in: int,
@@ -221,20 +264,19 @@ class NativeAllgather(_NativeBase):
     def step(self, step_idx: int, is_sync_step: bool = True, want_stats: bool = False) -> ExchangeStats:
         if not is_sync_step:
             return self.local_step()
-        self.q += 1
-        q, par, me = self.q, self.q & 1, self.rank
+        me, W, mb = self.rank, self.world, self.mb
         cur = torch.cuda.current_stream()
-        self._ev[0].record(cur)
-        self.plan.send(self.flat.grad, [(self.mb.slot(r, par, me), self.mb.flag(r, par, me)) for r in range(self.world)],
-                       q, self.cfg.seed, step_idx, me)
-        self._ev[1].record(cur)
-        sgd = make_sgd(self.cfg, self.first)
-        self.first = False
-        self.plan.recv_apply([(self.mb.slot(me, par, r), self.mb.flag(me, par, r)) for r in range(self.world)],
-                             q, float(self.world), L.OUT_SGD, sgd, self.flat.param, self.flat.momentum,
-                             self.flat.param_bf16)
-        self._ev[2].record(cur)
-        return self._finish_stats(ExchangeStats(), self.plan, self.world - 1, self.world - 1, want_stats)
+        self._advance(True)
+        self._rec(0, cur)
+        self.plan.send_state(self.flat.grad, [(mb.slot(r, 0, me), mb.flag(r, 0, me)) for r in range(W)],
+                             [(mb.slot(r, 1, me), mb.flag(r, 1, me)) for r in range(W)], self.state, self.cfg.seed, me)
+        self._rec(1, cur)
+        self.plan.recv_apply_state([(mb.slot(me, 0, r), mb.flag(me, 0, r)) for r in range(W)],
+                                   [(mb.slot(me, 1, r), mb.flag(me, 1, r)) for r in range(W)], self.state, float(W),
+                                   L.OUT_SGD, make_sgd(self.cfg, False), self.flat.param, self.flat.momentum,
+                                   self.flat.param_bf16)
+        self._rec(2, cur)
+        return self._finish_stats(ExchangeStats(), self.plan, W - 1, W - 1, want_stats)
 
 
 class NativePSWorker(_NativeBase):
@@ -256,40 +298,39 @@ class NativePSWorker(_NativeBase):
     def step(self, step_idx: int, is_sync_step: bool = True, want_stats: bool = False) -> ExchangeStats:
         if not is_sync_step:
             return self.local_step() if self.role == "worker" else ExchangeStats()
-        self.q += 1
-        q, par, me = self.q, self.q & 1, self.rank
+        me, W = self.rank, self.world
+        push, pull = self.push_mb, self.pull_mb
         cur = torch.cuda.current_stream()
         st = ExchangeStats()
-        self._ev[0].record(cur)
+        self._advance(True)
+        self._rec(0, cur)
+        sgd = make_sgd(self.cfg, False)
         if self.role == "worker":
-            self.push.send(self.flat.grad, [(self.push_mb.slot(0, par, me), self.push_mb.flag(0, par, me))], q,
-                           self.cfg.seed, step_idx, me)
-            self._ev[1].record(cur)
-            src = [(self.pull_mb.slot(me, par, 0), self.pull_mb.flag(me, par, 0))]
+            self.push.send_state(self.flat.grad, [(push.slot(0, 0, me), push.flag(0, 0, me))],
+                                 [(push.slot(0, 1, me), push.flag(0, 1, me))], self.state, self.cfg.seed, me)
+            self._rec(1, cur)
+            src = [[(pull.slot(me, par, 0), pull.flag(me, par, 0))] for par in (0, 1)]
             if self.pull_mode == "weights":
-                self.pull.recv_apply(src, q, 1.0, L.OUT_ASSIGN, param=self.flat.param, param_bf16=self.flat.param_bf16)
+                self.pull.recv_apply_state(src[0], src[1], self.state, 1.0, L.OUT_ASSIGN, param=self.flat.param,
+                                           param_bf16=self.flat.param_bf16)
             else:
-                sgd = make_sgd(self.cfg, self.first)
-                self.first = False
-                self.pull.recv_apply(src, q, 1.0, L.OUT_SGD, sgd, self.flat.param, self.flat.momentum,
-                                     self.flat.param_bf16)
-            self._ev[2].record(cur)
+                self.pull.recv_apply_state(src[0], src[1], self.state, 1.0, L.OUT_SGD, sgd, self.flat.param,
+                                           self.flat.momentum, self.flat.param_bf16)
+            self._rec(2, cur)
             return self._finish_stats(st, self.push, 1, 1, want_stats)
         # ---- server ------------------------------------------------------------------------
-        srcs = [(self.push_mb.slot(0, par, r), self.push_mb.flag(0, par, r)) for r in range(1, self.world)]
-        dests = [(self.pull_mb.slot(r, par, 0), self.pull_mb.flag(r, par, 0)) for r in range(1, self.world)]
+        srcs = [[(push.slot(0, par, r), push.flag(0, par, r)) for r in range(1, W)] for par in (0, 1)]
+        dests = [[(pull.slot(r, par, 0), pull.flag(r, par, 0)) for r in range(1, W)] for par in (0, 1)]
         if self.pull_mode == "weights":
-            sgd = make_sgd(self.cfg, self.first)
-            self.first = False
-            self.push.recv_apply(srcs, q, float(self.num_workers), L.OUT_SGD, sgd, self.flat.param, self.flat.momentum,
-                                 self.flat.param_bf16)
-            self._ev[1].record(cur)
-            self.pull.send(self.flat.param, dests, q, self.cfg.seed, step_idx, 0)
+            self.push.recv_apply_state(srcs[0], srcs[1], self.state, float(self.num_workers), L.OUT_SGD, sgd,
+                                       self.flat.param, self.flat.momentum, self.flat.param_bf16)
+            self._rec(1, cur)
+            self.pull.send_state(self.flat.param, dests[0], dests[1], self.state, self.cfg.seed, 0)
         else:
-            self.push.recv_apply(srcs, q, float(self.num_workers), L.OUT_GRAD, out=self.avg)
-            self._ev[1].record(cur)
-            self.pull.send(self.avg, dests, q, self.cfg.seed, step_idx, 0)
-        self._ev[2].record(cur)
+            self.push.recv_apply_state(srcs[0], srcs[1], self.state, float(self.num_workers), L.OUT_GRAD, out=self.avg)
+            self._rec(1, cur)
+            self.pull.send_state(self.avg, dests[0], dests[1], self.state, self.cfg.seed, 0)
+        self._rec(2, cur)
         return self._finish_stats(st, self.pull, self.num_workers, self.num_workers, want_stats)
 
 
@@ -316,19 +357,20 @@ class NativeAllreduce(_NativeBase):
         self.algo = {"auto": L.AR_AUTO, "oneshot": L.AR_ONESHOT, "twoshot": L.AR_TWOSHOT}[registry.get("allreduce_algo")]
 
     def allreduce_(self, n: int, scale: float) -> None:
-        self.q += 1
-        L.check(self.lib.ewdml_allreduce(C.byref(self.comm), n, scale, self.algo, self.q,
-                                         C.c_void_p(self.work_counter), ExchangePlan._stream()), "allreduce")
+        L.check(self.lib.ewdml_allreduce_state(C.byref(self.comm), n, scale, self.algo, 0, C.c_void_p(self.state.data_ptr()),
+                                               C.c_void_p(self.work_counter), ExchangePlan._stream()), "allreduce")
 
     def step(self, step_idx: int, is_sync_step: bool = True, want_stats: bool = False) -> ExchangeStats:
         if not is_sync_step:
             return self.local_step()
         cur = torch.cuda.current_stream()
-        self._ev[0].record(cur)
+        self._advance(True)
+        self._rec(0, cur)
         self.allreduce_(self.flat.total, 1.0 / self.world)
-        self._ev[1].record(cur)
-        st = self.local_step()
-        self._ev[2].record(cur)
+        self._rec(1, cur)
+        self._sgd_apply()
+        st = ExchangeStats()
+        self._rec(2, cur)
         n = self.flat.dense_nbytes()
         st.bytes_sent = st.bytes_recv = int((self.world - 1) / self.world * n)
         if want_stats:

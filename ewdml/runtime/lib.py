@@ -81,6 +81,11 @@ def load() -> C.CDLL:
         "ewdml_send": (i32, [vp, vp, P(Dests), u32, u64, u32, u32, vp]),
         "ewdml_recv_apply": (i32, [vp, P(Sources), u32, f32, i32, P(Sgd), vp, vp, vp, vp, vp]),
         "ewdml_sgd_apply": (i32, [vp, vp, vp, vp, i64, P(Sgd), f32, vp]),
+        "ewdml_state_advance": (i32, [vp, i32, vp]),
+        "ewdml_send_state": (i32, [vp, vp, P(Dests), P(Dests), vp, u64, u32, vp]),
+        "ewdml_recv_apply_state": (i32, [vp, P(Sources), P(Sources), vp, f32, i32, P(Sgd), vp, vp, vp, vp, vp]),
+        "ewdml_sgd_apply_state": (i32, [vp, vp, vp, vp, i64, P(Sgd), f32, vp, vp]),
+        "ewdml_allreduce_state": (i32, [P(Comm), i64, f32, i32, u32, vp, vp, vp]),
         "ewdml_plan_read_stats": (i32, [vp, P(i64), vp]),
         "ewdml_plan_read_seginfo": (i32, [vp, P(u32), vp]),
         "ewdml_allreduce": (i32, [P(Comm), i64, f32, i32, u32, vp, vp]),

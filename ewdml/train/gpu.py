@@ -57,9 +57,65 @@ class GpuTrainer:
         self.last_logits = None
         # seeds differ per rank for dropout etc. after the common initialisation
         torch.manual_seed(cfg.seed + 1000 * (self.rank + 1))
+        if cfg.compute == "native":
+            from ..ops import native
+            native.STEP_STATE["tensor"] = self.exchange.state
+        self.graph = None
+        self.graph_launches = 0          # launches of this repo's kernels inside one captured step
+        self.replays = 0
+
+    # -- CUDA-graph capture of the whole step (forward, backward, exchange, optimizer) ----------
+    def capture(self, x: torch.Tensor, y: torch.Tensor, warmup: int = 3) -> None:
+        """Capture one full training step in a CUDA graph; later ``step()`` calls copy the batch into the
+        static input buffers and replay it.  Every per-step quantity the kernels need (flag sequence
+        number, slot parity, RNG position, first-step flag) lives in device memory, so replays are exact.
+        Only valid for sync_period == 1 (method 6 alternates two different step bodies)."""
+        if self.period != 1:
+            raise RuntimeError("graph capture needs sync_period == 1")
+        self.static_x, self.static_y = x.clone(), y.clone()
+        side = torch.cuda.Stream(device=self.device)
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            for _ in range(warmup):
+                self._step_body(self.static_x, self.static_y)
+        torch.cuda.current_stream().wait_stream(side)
+        torch.cuda.synchronize()
+        g = torch.cuda.CUDAGraph()
+        before = L.launches()
+        with torch.cuda.graph(g):
+            loss, logits = self._step_body(self.static_x, self.static_y)
+        self.graph_launches = L.launches() - before
+        self.graph, self.static_loss, self.static_logits = g, loss, logits
+
+    def _step_body(self, x, y):
+        f = self.flat
+        f.grad.zero_()
+        if self.autocast:
+            with torch.autocast("cuda", dtype=torch.bfloat16):
+                logits = self.model(x)
+            loss = torch.nn.functional.cross_entropy(logits.float(), y)
+        else:
+            logits = self.model(x)
+            loss = Lyr.cross_entropy(logits, y)
+        loss.backward()
+        self.exchange.step(self.step_idx, is_sync_step=True, want_stats=False)
+        return loss.detach(), logits.detach()
+
+    def own_launches(self) -> int:
+        """Launches of this repo's kernels so far (eager launches + replays x launches per captured step)."""
+        return L.launches() + self.replays * self.graph_launches
 
     # -- one optimisation step on a device-resident batch ------------------------------------
     def step(self, x: torch.Tensor, y: torch.Tensor, want_stats: bool = False):
+        if self.graph is not None and not want_stats:
+            self.static_x.copy_(x, non_blocking=True)
+            self.static_y.copy_(y, non_blocking=True)
+            self.graph.replay()
+            self.replays += 1
+            self.step_idx += 1
+            self.last_loss, self.last_logits = self.static_loss, self.static_logits
+            from ..parallel.host_exchange import ExchangeStats
+            return self.static_loss, ExchangeStats()
         f = self.flat
         f.grad.zero_()
         if self.autocast:

@@ -109,6 +109,21 @@ int ewdml_plan_read_stats(ewdml_plan* plan, int64_t out[4], void* stream);
  * out[4*i+0]=threshold key, +1=ties taken, +2=norm bits, +3=candidate count                     */
 int ewdml_plan_read_seginfo(ewdml_plan* plan, uint32_t* out, void* stream);
 
+/* Graph-replayable forms.  `state` is a device array of 4 uint32 {seq, step, first, applies} advanced by
+ * ewdml_state_advance (one tiny launch at the start of every optimizer application; bump_seq = 1 for
+ * exchanges).  Sequence number, RNG step, slot parity and the first-step flag are read from it on the
+ * device, so a CUDA graph that captured these launches can be replayed every step.  *_even / *_odd are the
+ * slot sets used when seq is even / odd.                                                               */
+int ewdml_state_advance(uint32_t* state, int bump_seq, void* stream);
+int ewdml_send_state(ewdml_plan* plan, const float* grad, const ewdml_dests* dests_even,
+                     const ewdml_dests* dests_odd, const uint32_t* state, uint64_t seed, uint32_t rng_stream,
+                     void* stream);
+int ewdml_recv_apply_state(ewdml_plan* plan, const ewdml_sources* srcs_even, const ewdml_sources* srcs_odd,
+                           const uint32_t* state, float divisor, int out_mode, const ewdml_sgd* sgd,
+                           float* param, float* momentum, void* param_bf16, float* out, void* stream);
+int ewdml_sgd_apply_state(const float* grad, float* param, float* momentum, void* param_bf16, int64_t n,
+                          const ewdml_sgd* sgd, float grad_scale, const uint32_t* state, void* stream);
+
 /* ------------------------------------------------------------------------------------------
  * K4: dense fused-scale allreduce over peer memory (replaces hvd.allreduce(Average) and
  * ompi:ompi/mca/coll/base/coll_base_allreduce.c:341 + ompi:ompi/mca/op/avx/op_avx_functions.c).
@@ -127,6 +142,8 @@ enum { EWDML_AR_AUTO = 0, EWDML_AR_ONESHOT = 1, EWDML_AR_TWOSHOT = 2 };
 int ewdml_allreduce(const ewdml_comm* comm, int64_t n, float scale, int algo, uint32_t seq,
                     uint32_t* work_counter, void* stream);
 /* device-side barrier across ranks (flag exchange)                                              */
+int ewdml_allreduce_state(const ewdml_comm* comm, int64_t n, float scale, int algo, uint32_t seq,
+                          const uint32_t* state, uint32_t* work_counter, void* stream);
 int ewdml_barrier(const ewdml_comm* comm, uint32_t seq, void* stream);
 /* device error word (0 = ok) set by kernels whose flag spin exceeded the limit                  */
 int ewdml_get_device_error(uint32_t* out, void* stream);
@@ -181,6 +198,43 @@ void ewdml_set_trace(int on);                                    /* libompitrace
  * (lenet.py:18-21, vgg.py:24-29,53, resnet.py:19-77), which the reference runs through ATen.      */
 int ewdml_gemm_bf16_tn(const void* A, const void* B, void* C, int M, int N, int K, int lda, int ldb,
                        int ldc, int out_mode, const float* bias, float alpha, int split_k, void* stream);
+
+/* General form: a_mn / b_mn = 1 means the operand is stored with its M / N dimension contiguous
+ * ([K][M] / [K][N]), so dgrad (dy W) and wgrad (dy^T x) need no transposed copies.                     */
+int ewdml_gemm_bf16(const void* A, const void* B, void* C, int M, int N, int K, int lda, int ldb, int ldc,
+                    int a_mn, int b_mn, int out_mode, const float* bias, float alpha, int split_k, void* stream);
+
+/* K5 operand builders (nn.Conv2d, vgg.py:53, resnet.py:19-55): NHWC bf16 x -> col[M][Kp], Kp = round_up(KH*KW*C, 8);
+ * and the data-gradient gather dcol -> dx.                                                              */
+int ewdml_im2col(const void* x, void* col, int N, int H, int W, int C, int KH, int KW, int stride, int pad, void* stream);
+int ewdml_col2im(const void* dcol, void* dx, int N, int H, int W, int C, int KH, int KW, int stride, int pad, void* stream);
+
+/* K7/K8 (nn.BatchNorm2d train mode, ReLU, residual add, MaxPool2d(2,2); vgg.py:51-55, resnet.py:20-63):
+ * colstats: per-channel sum (and sum of squares) of a [M][C] bf16 matrix into zeroed fp32 sums[2C];
+ * bn_finalize: stats = [mean | rstd | scale | shift] + running-stat update; bn_act_fwd: out = [pool2x2]
+ * relu?(scale*y + shift (+res)); bn_act_bwd: dy (and dres), dgamma/dbeta accumulated in fp32.             */
+int ewdml_colstats(const void* y, float* sums, int64_t M, int C, int want_sq, void* stream);
+int ewdml_bn_finalize(const float* sums, const float* gamma, const float* beta, float* running_mean,
+                      float* running_var, float* stats, int C, int64_t M, float momentum, float eps, void* stream);
+int ewdml_bn_act_fwd(const void* y, const float* stats, const void* res, void* out, int N, int H, int W, int C,
+                     int relu, int pool, void* stream);
+int ewdml_bn_act_bwd(const void* y, const float* stats, const void* res, const void* dout, float* sums, void* dy,
+                     void* dres, float* dgamma, float* dbeta, int N, int H, int W, int C, int relu, int pool,
+                     void* stream);
+int ewdml_add_vec_f32(const float* src, float* dst, int n, void* stream);
+int ewdml_cast_f32_bf16(const float* x, void* y, int64_t n, void* stream);
+int ewdml_pad_rows_bf16(const void* src, void* dst, int rows, int cols, int pitch, void* stream);
+int ewdml_relu_fwd(const void* x, void* y, int64_t n, void* stream);
+int ewdml_relu_bwd(const void* dy, const void* y, void* dx, int64_t n, void* stream);
+/* nn.Dropout (vgg.py:23-26): inverted dropout, counter-based mask; step_state (optional) = device step state */
+int ewdml_dropout(const void* x, void* y, int64_t n, float p, uint32_t seed, uint32_t offset,
+                  const uint32_t* step_state, void* stream);
+/* F.avg_pool2d(out, 4) on the final 4x4 map (resnet.py:93)                                               */
+int ewdml_avgpool_fwd(const void* x, void* y, int N, int HW, int C, void* stream);
+int ewdml_avgpool_bwd(const void* dy, void* dx, int N, int HW, int C, void* stream);
+/* K9: softmax cross-entropy, mean over batch (distributed_worker.py:103): loss_acc[2] = {loss, #top-1 hits} */
+int ewdml_xent(const void* logits, const int64_t* target, float* loss_acc, void* dlogits, int B, int C, int ld,
+               void* stream);
 
 #ifdef __cplusplus
 }
