@@ -174,7 +174,7 @@ def test_whole_model_native_matches_torch(name, shape):
         torch.cuda.synchronize()
     finally:
         L.set_compute("torch")
-    assert abs(loss.item() - loss_ref.item()) < 0.02 * max(1.0, abs(loss_ref.item()))
+    assert abs(loss.item() - loss_ref.item()) < 0.05 * max(1.0, abs(loss_ref.item()))
     cos_nat, cos_amp = [], []
     for (n, p), pr, pa in zip(m_nat.named_parameters(), m_ref.parameters(), m_amp.parameters()):
         g, gr, ga = p.grad.float().flatten(), pr.grad.float().flatten(), pa.grad.float().flatten()
