@@ -9,6 +9,8 @@
 // normalise-activate(-pool) pass forward, and one reduce pass plus one apply pass backward.
 // Reference sites: nn.Conv2d / BatchNorm2d / ReLU / MaxPool2d / avg_pool2d / Dropout / CrossEntropyLoss in
 // src/model_ops/{lenet,vgg,resnet}.py and distributed_worker.py:103 -- all ATen library calls there.
+#include <mutex>
+
 #include "../common.cuh"
 
 namespace {
@@ -604,6 +606,84 @@ extern "C" int ewdml_avgpool_bwd(const void* dy, void* dx, int N, int HW, int C,
 extern "C" int ewdml_xent(const void* logits, const int64_t* target, float* loss_acc, void* dlogits, int B, int C, int ld, void* stream) {
     EWDML_CHECK_ARG(logits && target && loss_acc && dlogits && B > 0 && C > 0);
     k_xent<<<(B + 7) / 8, 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)logits, target, loss_acc, (__nv_bfloat16*)dlogits, B, C, ld);
+    NN_LAUNCH_CHECK();
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// BatchNorm batch statistics without any allocation (no counterpart in the reference).
+//
+// ewdml_colstats + ewdml_bn_finalize need a zeroed fp32 scratch vector of 2*C partial sums, which the
+// Python layer takes from torch's caching allocator.  Some users of this C ABI cannot do that: a plain
+// C/C++ host loop that links libewdml.so without torch has no caching allocator, and calling cudaMalloc
+// per step from it would synchronise the whole device and can fail outright when another component of
+// the process has already reserved the GPU's memory.  For them the scratch lives in the library image:
+// a file-scope device array of EWDML_BN_STATIC_MAX_C * 2 floats (32 KiB) that every GPU which loads the
+// library keeps until the process exits.
+//
+// Rules that follow from sharing ONE array:
+//   * C must be <= EWDML_BN_STATIC_MAX_C (4096); larger sizes are rejected with EWDML_ERR_ARG.
+//   * the array keeps the previous call's sums, so each call clears the 2*C floats it uses first
+//     (stream-ordered memset on `stream`);
+//   * two calls whose work overlaps on the GPU (different streams, or several host threads) race on the
+//     array -- serialise them on one stream;
+//   * the first call on each device looks up the array's device address (cudaGetSymbolAddress, with that
+//     device current).  That lookup is part of the first call, so make the first call on a device before
+//     starting any stream capture on it.
+// ---------------------------------------------------------------------------------------------------
+#define EWDML_BN_STATIC_MAX_C 4096
+static __device__ __align__(256) float g_bn_static_sums[2 * EWDML_BN_STATIC_MAX_C];
+
+static float* bn_static_scratch_for_current_device() {
+    // In host code `g_bn_static_sums` is only a handle for the symbol, never a usable address: the real
+    // device address differs per GPU and has to be queried with that GPU current.
+    static float* addr[64] = {nullptr};
+    static std::mutex mu;
+    int dev = -1;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) {
+        ewdml_set_error("ewdml_bn_stats_static: cannot determine the current device");
+        return nullptr;
+    }
+    std::lock_guard<std::mutex> lk(mu);
+    if (!addr[dev]) {
+        float* p = nullptr;
+        cudaError_t e = cudaGetSymbolAddress((void**)&p, g_bn_static_sums);
+        if (e != cudaSuccess || !p) {
+            ewdml_set_error("ewdml_bn_stats_static: cudaGetSymbolAddress failed on device %d: %s", dev, cudaGetErrorString(e));
+            return nullptr;
+        }
+        addr[dev] = p;
+    }
+    return addr[dev];
+}
+
+// Same result as ewdml_colstats(y, sums, M, C, 1) followed by ewdml_bn_finalize(sums, ...): writes
+// stats = [mean | rstd | scale | shift] (4*C floats) and updates the running statistics when given.
+// Inputs and outputs are the caller's; nothing is allocated or freed here.
+extern "C" int ewdml_bn_stats_static(const void* y, const float* gamma, const float* beta, float* running_mean, float* running_var,
+                                     float* stats, int C, int64_t M, float momentum, float eps, void* stream) {
+    EWDML_CHECK_ARG(y && gamma && beta && stats && M > 0 && C > 0 && C % 2 == 0);
+    if (C > EWDML_BN_STATIC_MAX_C) {
+        ewdml_set_error("ewdml_bn_stats_static: C = %d exceeds the built-in scratch (max %d channels); use ewdml_colstats + "
+                        "ewdml_bn_finalize with your own 2*C-float buffer", C, EWDML_BN_STATIC_MAX_C);
+        return EWDML_ERR_ARG;
+    }
+    float* sums = bn_static_scratch_for_current_device();
+    if (!sums) return EWDML_ERR_CUDA;
+    cudaStream_t st = (cudaStream_t)stream;
+    EWDML_CUDA(cudaMemsetAsync(sums, 0, sizeof(float) * 2 * (size_t)C, st));       // the previous call's sums are still there
+    const int cp = C / 2, lanes = cp < 256 ? cp : 256;
+    const int gx = (cp + lanes - 1) / lanes;
+    int gy = (int)((2 * 148 + gx - 1) / gx);
+    int64_t rows_per = (M + gy - 1) / gy;
+    const int rows_par = 256 / lanes;
+    if (rows_per < 4 * rows_par) rows_per = 4 * rows_par;
+    gy = (int)((M + rows_per - 1) / rows_per);
+    k_colstats<<<dim3(gx, gy), 256, 0, st>>>((const __nv_bfloat16*)y, sums, M, C, 1, (int)rows_per);
+    NN_LAUNCH_CHECK();
+    const float unbias = M > 1 ? (float)((double)M / (double)(M - 1)) : 1.f;
+    k_bn_finalize<<<(C + 127) / 128, 128, 0, st>>>(sums, gamma, beta, running_mean, running_var, stats, C, (float)(1.0 / (double)M), unbias,
+                                                   momentum, eps);
     NN_LAUNCH_CHECK();
     return 0;
 }

@@ -221,6 +221,15 @@ int ewdml_bn_act_fwd(const void* y, const float* stats, const void* res, void* o
 int ewdml_bn_act_bwd(const void* y, const float* stats, const void* res, const void* dout, float* sums, void* dy,
                      void* dres, float* dgamma, float* dbeta, int N, int H, int W, int C, int relu, int pool,
                      void* stream);
+/* No counterpart in the reference.  BatchNorm batch statistics for callers that must not allocate (a C/C++
+ * host loop without torch's caching allocator; a process whose GPU memory is already fully reserved): same
+ * result as ewdml_colstats + ewdml_bn_finalize, but the 2*C-float scratch is a device array built into the
+ * library (32 KiB per GPU, held until exit).  C <= 4096 or EWDML_ERR_ARG.  The array is shared by all calls:
+ * it is cleared at the start of each call, and calls that overlap on the GPU race.  The first call on a
+ * device also resolves the array's address, so make it before any stream capture on that device.        */
+int ewdml_bn_stats_static(const void* y, const float* gamma, const float* beta, float* running_mean,
+                          float* running_var, float* stats, int C, int64_t M, float momentum, float eps,
+                          void* stream);
 int ewdml_add_vec_f32(const float* src, float* dst, int n, void* stream);
 int ewdml_cast_f32_bf16(const float* x, void* y, int64_t n, void* stream);
 int ewdml_pad_rows_bf16(const void* src, void* dst, int rows, int cols, int pitch, void* stream);
