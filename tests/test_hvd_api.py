@@ -1,0 +1,37 @@
+"""Horovod-style API over gloo, the native launcher and the info tool."""
+import json
+import os
+import subprocess
+import sys
+
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_allreduce_mnist_under_native_launcher(tmp_path):
+    ck = str(tmp_path / "checkpoint-{epoch}.pt")
+    cmd = [sys.executable, "-m", "ewdml.cli.launch", "-np", "2", "--master-port", "29741", "--",
+           sys.executable, "-m", "ewdml.cli.allreduce_mnist", "--epochs", "1", "--max-steps", "6", "--no-cuda",
+           "--synthetic-size", "256", "--batch-size", "16", "--test-batch-size", "64", "--compression", "qsgd",
+           "--warmup-epochs", "0.5", "--checkpoint-format", ck]
+    out = subprocess.run(cmd, capture_output=True, text=True, timeout=300, cwd=ROOT)
+    assert out.returncode == 0, out.stderr[-1500:]
+    assert "Test set: Average loss" in out.stdout and os.path.isfile(ck.format(epoch=1))
+
+
+def test_launcher_tears_job_down_on_failure():
+    code = "import os,sys,time; r=int(os.environ['RANK']); time.sleep(0.3 if r==1 else 60); sys.exit(5 if r==1 else 0)"
+    out = subprocess.run([sys.executable, "-m", "ewdml.cli.launch", "-np", "3", "--grace-seconds", "1", "--",
+                          sys.executable, "-c", code], capture_output=True, text=True, timeout=60, cwd=ROOT)
+    assert out.returncode == 5 and "rank 1 exited with status 5" in out.stderr
+
+
+def test_info_tool_and_adasum_pair():
+    out = subprocess.run([sys.executable, "-m", "ewdml.cli.info"], capture_output=True, text=True, timeout=120, cwd=ROOT)
+    info = json.loads(out.stdout)
+    assert "select_tile" in info["tunables"] and info["flags"]["network"] == "LeNet"
+    from ewdml.parallel.hvd import _adasum_pair
+    a = torch.tensor([1.0, 0.0]); b = torch.tensor([0.0, 1.0])
+    assert torch.allclose(_adasum_pair(a, b), a + b)                 # orthogonal -> sum
+    assert torch.allclose(_adasum_pair(a, a), a)                     # parallel   -> average
