@@ -272,7 +272,15 @@ __global__ void __launch_bounds__(192) k_gemm_tcgen05(const __grid_constant__ CU
                 }
             } else {
                 float* out = reinterpret_cast<float*>(g.C) + (size_t)row * g.ldc + col0;
-                for (int j = 0; j < 32 && col0 + j < g.N; ++j) atomicAdd(out + j, f[j]);
+                if (full && (g.ldc % 4 == 0) && ((reinterpret_cast<uintptr_t>(g.C) & 15) == 0)) {
+#pragma unroll
+                    for (int j = 0; j < 32; j += 4)       // 16-byte vector reduction: 4x fewer L2 atomic operations
+                        asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(out + j), "f"(f[j]), "f"(f[j + 1]), "f"(f[j + 2]),
+                                     "f"(f[j + 3])
+                                     : "memory");
+                } else {
+                    for (int j = 0; j < 32 && col0 + j < g.N; ++j) atomicAdd(out + j, f[j]);
+                }
             }
         }
     }

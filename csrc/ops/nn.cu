@@ -132,6 +132,43 @@ struct ActGeom {
 // z value before activation for element (row, c): scale*y + shift (+ residual)
 __device__ __forceinline__ float pre_act(float y, float sc, float sh, float res) { return fmaf(sc, y, sh) + res; }
 
+// 8 channels per thread (one 16-byte load per row), `lanes` threads along channels, 256/lanes rows in flight
+// per CTA; per-CTA reduction in shared memory, then one global atomic per channel per CTA.
+__global__ void __launch_bounds__(256) k_colstats_v8(const __nv_bfloat16* __restrict__ y, float* __restrict__ sums, int64_t M, int C, int want_sq,
+                                                     int rows_per_cta) {
+    __shared__ float red[256 * 16];
+    const int c8n = C >> 3;
+    const int lanes = c8n < 256 ? c8n : 256;
+    const int rows_par = 256 / lanes;
+    const int lane = threadIdx.x % lanes, rsub = threadIdx.x / lanes;
+    const int c8 = blockIdx.x * lanes + lane;
+    const int64_t r0 = (int64_t)blockIdx.y * rows_per_cta;
+    const int64_t r1 = r0 + rows_per_cta < M ? r0 + rows_per_cta : M;
+    for (int i = threadIdx.x; i < lanes * 16; i += 256) red[i] = 0.f;
+    __syncthreads();
+    if (c8 < c8n && rsub < rows_par) {
+        float s[8], q[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) { s[i] = 0.f; q[i] = 0.f; }
+        for (int64_t r = r0 + rsub; r < r1; r += rows_par) {
+            float f[8];
+            unpack8(*reinterpret_cast<const uint4*>(y + r * C + c8 * 8), f);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) { s[i] += f[i]; q[i] = fmaf(f[i], f[i], q[i]); }
+        }
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            atomicAdd(&red[lane * 16 + i], s[i]);
+            if (want_sq) atomicAdd(&red[lane * 16 + 8 + i], q[i]);
+        }
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < lanes * 16; i += 256) {
+        const int l = i >> 4, j = i & 15, c = (blockIdx.x * lanes + l) * 8 + (j & 7);
+        if (c < C && (j < 8 || want_sq)) atomicAdd(&sums[(j < 8 ? 0 : C) + c], red[i]);
+    }
+}
+
 __global__ void __launch_bounds__(256) k_colstats(const __nv_bfloat16* __restrict__ y, float* __restrict__ sums, int64_t M, int C, int want_sq,
                                                   int rows_per_cta) {
     const int cp_n = C >> 1;                                  // channel pairs
@@ -158,11 +195,59 @@ __global__ void __launch_bounds__(256) k_colstats(const __nv_bfloat16* __restric
     }
 }
 
+// split-K epilogue: fp32 accumulator [M][C] (+bias) -> bf16 [M][C], optionally accumulating the BatchNorm column
+// statistics of the ROUNDED values in the same pass (so the separate statistics read disappears)
+__global__ void __launch_bounds__(256) k_f32_to_bf16_stats(const float* __restrict__ src, const float* __restrict__ bias, __nv_bfloat16* __restrict__ dst,
+                                                           float* __restrict__ sums, int64_t M, int C, int rows_per_cta) {
+    __shared__ float red[256 * 16];
+    const int c8n = C >> 3;
+    const int lanes = c8n < 256 ? c8n : 256;
+    const int rows_par = 256 / lanes;
+    const int lane = threadIdx.x % lanes, rsub = threadIdx.x / lanes;
+    const int c8 = blockIdx.x * lanes + lane;
+    const int64_t r0 = (int64_t)blockIdx.y * rows_per_cta;
+    const int64_t r1 = r0 + rows_per_cta < M ? r0 + rows_per_cta : M;
+    if (sums) {
+        for (int i = threadIdx.x; i < lanes * 16; i += 256) red[i] = 0.f;
+        __syncthreads();
+    }
+    if (c8 < c8n && rsub < rows_par) {
+        float b[8], s[8], q[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) { b[i] = bias ? bias[c8 * 8 + i] : 0.f; s[i] = 0.f; q[i] = 0.f; }
+        for (int64_t r = r0 + rsub; r < r1; r += rows_par) {
+            const float4 a0 = *reinterpret_cast<const float4*>(src + r * C + c8 * 8);
+            const float4 a1 = *reinterpret_cast<const float4*>(src + r * C + c8 * 8 + 4);
+            float f[8] = {a0.x + b[0], a0.y + b[1], a0.z + b[2], a0.w + b[3], a1.x + b[4], a1.y + b[5], a1.z + b[6], a1.w + b[7]};
+            const uint4 pk = pack8(f);
+            *reinterpret_cast<uint4*>(dst + r * C + c8 * 8) = pk;
+            if (sums) {
+                float fr[8];
+                unpack8(pk, fr);
+#pragma unroll
+                for (int i = 0; i < 8; ++i) { s[i] += fr[i]; q[i] = fmaf(fr[i], fr[i], q[i]); }
+            }
+        }
+        if (sums) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) { atomicAdd(&red[lane * 16 + i], s[i]); atomicAdd(&red[lane * 16 + 8 + i], q[i]); }
+        }
+    }
+    if (sums) {
+        __syncthreads();
+        for (int i = threadIdx.x; i < lanes * 16; i += 256) {
+            const int l = i >> 4, j = i & 15, c = (blockIdx.x * lanes + l) * 8 + (j & 7);
+            if (c < C) atomicAdd(&sums[(j < 8 ? 0 : C) + c], red[i]);
+        }
+    }
+}
+
 // mean/var -> scale/shift, running statistics update (momentum, unbiased variance), like nn.BatchNorm2d
 __global__ void k_bn_finalize(const float* __restrict__ sums, const float* __restrict__ gamma, const float* __restrict__ beta,
                               float* __restrict__ running_mean, float* __restrict__ running_var, float* __restrict__ stats /* [4][C]: mean, rstd, scale, shift */,
-                              int C, float inv_m, float unbias, float momentum, float eps) {
+                              int C, float inv_m, float unbias, float momentum, float eps, long long* __restrict__ num_batches) {
     const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c == 0 && num_batches) *num_batches += 1;
     if (c >= C) return;
     const float mean = sums[c] * inv_m;
     float var = fmaf(-mean, mean, sums[C + c] * inv_m);
@@ -311,6 +396,130 @@ __global__ void __launch_bounds__(256) k_bn_bwd_apply(const __nv_bfloat16* __res
         if (g.has_affine) d = sc * (dz - sums[c] * inv_m - (yv - mean) * rstd * sums[g.C + c] * inv_m);
         dy[t] = __float2bfloat16_rn(d);
         if (dres) dres[t] = __float2bfloat16_rn(dz);
+    }
+}
+
+// ---- vectorised backward (C % 8 == 0): a work unit is one row (no pool) or one 2x2 window (pool) x 8 channels ----
+// dz for the unit, recomputed from the saved pre-BN output y: every y value is read exactly once per pass.
+template <bool POOL>
+__device__ __forceinline__ void unit_dz(const __nv_bfloat16* __restrict__ y, const __nv_bfloat16* __restrict__ res, const __nv_bfloat16* __restrict__ dout,
+                                        const ActGeom& g, int64_t unit, int c8, const float (&sc)[8], const float (&sh)[8],
+                                        float (&yv)[POOL ? 4 : 1][8], float (&dz)[POOL ? 4 : 1][8], int64_t (&rows)[POOL ? 4 : 1]) {
+    if (!POOL) {
+        rows[0] = unit;
+        float d[8], r[8];
+        unpack8(*reinterpret_cast<const uint4*>(y + unit * g.C + c8 * 8), yv[0]);
+        unpack8(*reinterpret_cast<const uint4*>(dout + unit * g.C + c8 * 8), d);
+        if (res) unpack8(*reinterpret_cast<const uint4*>(res + unit * g.C + c8 * 8), r);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const float z = pre_act(yv[0][i], sc[i], sh[i], res ? r[i] : 0.f);
+            dz[0][i] = (!g.relu || z > 0.f) ? d[i] : 0.f;
+        }
+    } else {
+        const int WP = g.W >> 1, HP = g.H >> 1;
+        const int wp = (int)(unit % WP), hp = (int)((unit / WP) % HP), n = (int)(unit / ((int64_t)WP * HP));
+        float d[8], best[8];
+        int arg[8];
+        unpack8(*reinterpret_cast<const uint4*>(dout + unit * g.C + c8 * 8), d);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) { best[i] = -INFINITY; arg[i] = 0; }
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            rows[q] = ((int64_t)n * g.H + hp * 2 + (q >> 1)) * g.W + wp * 2 + (q & 1);
+            unpack8(*reinterpret_cast<const uint4*>(y + rows[q] * g.C + c8 * 8), yv[q]);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const float z = pre_act(yv[q][i], sc[i], sh[i], 0.f);
+                if (z > best[i]) { best[i] = z; arg[i] = q; }
+            }
+        }
+#pragma unroll
+        for (int q = 0; q < 4; ++q)
+#pragma unroll
+            for (int i = 0; i < 8; ++i) dz[q][i] = (arg[i] == q && (!g.relu || best[i] > 0.f)) ? d[i] : 0.f;
+    }
+}
+
+template <bool POOL>
+__global__ void __launch_bounds__(256) k_bn_bwd_reduce_v8(const __nv_bfloat16* __restrict__ y, const __nv_bfloat16* __restrict__ res, const __nv_bfloat16* __restrict__ dout,
+                                                          const float* __restrict__ stats, float* __restrict__ sums, ActGeom g, int64_t units, int units_per_cta) {
+    __shared__ float red[256 * 16];
+    constexpr int R = POOL ? 4 : 1;
+    const int c8n = g.C >> 3;
+    const int lanes = c8n < 256 ? c8n : 256;
+    const int par = 256 / lanes;
+    const int lane = threadIdx.x % lanes, usub = threadIdx.x / lanes;
+    const int c8 = blockIdx.x * lanes + lane;
+    for (int i = threadIdx.x; i < lanes * 16; i += 256) red[i] = 0.f;
+    __syncthreads();
+    if (c8 < c8n && usub < par) {
+        float mean[8], rstd[8], sc[8], sh[8], s[8], sx[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const int c = c8 * 8 + i;
+            mean[i] = stats[c]; rstd[i] = stats[g.C + c]; sc[i] = stats[2 * g.C + c]; sh[i] = stats[3 * g.C + c];
+            s[i] = 0.f; sx[i] = 0.f;
+        }
+        const int64_t u0 = (int64_t)blockIdx.y * units_per_cta;
+        const int64_t u1 = u0 + units_per_cta < units ? u0 + units_per_cta : units;
+        for (int64_t u = u0 + usub; u < u1; u += par) {
+            float yv[R][8], dz[R][8];
+            int64_t rows[R];
+            unit_dz<POOL>(y, res, dout, g, u, c8, sc, sh, yv, dz, rows);
+#pragma unroll
+            for (int q = 0; q < R; ++q)
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    s[i] += dz[q][i];
+                    sx[i] = fmaf(dz[q][i], (yv[q][i] - mean[i]) * rstd[i], sx[i]);
+                }
+        }
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            atomicAdd(&red[lane * 16 + i], s[i]);
+            atomicAdd(&red[lane * 16 + 8 + i], sx[i]);
+        }
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < lanes * 16; i += 256) {
+        const int l = i >> 4, j = i & 15, c = (blockIdx.x * lanes + l) * 8 + (j & 7);
+        if (c < g.C) atomicAdd(&sums[(j < 8 ? 0 : g.C) + c], red[i]);
+    }
+}
+
+template <bool POOL>
+__global__ void __launch_bounds__(256) k_bn_bwd_apply_v8(const __nv_bfloat16* __restrict__ y, const __nv_bfloat16* __restrict__ res, const __nv_bfloat16* __restrict__ dout,
+                                                         const float* __restrict__ stats, const float* __restrict__ sums, __nv_bfloat16* __restrict__ dy,
+                                                         __nv_bfloat16* __restrict__ dres, float* __restrict__ dgamma, float* __restrict__ dbeta, ActGeom g,
+                                                         float inv_m, int64_t units, int64_t total) {
+    constexpr int R = POOL ? 4 : 1;
+    const int c8n = g.C >> 3;
+    if (blockIdx.x == 0 && dgamma && dbeta && g.has_affine)            // parameter gradients into the flat fp32 buffer
+        for (int c = threadIdx.x; c < g.C; c += 256) { dbeta[c] += sums[c]; dgamma[c] += sums[g.C + c]; }
+    for (int64_t t = (int64_t)blockIdx.x * 256 + threadIdx.x; t < total; t += (int64_t)gridDim.x * 256) {
+        const int c8 = (int)(t % c8n);
+        const int64_t u = t / c8n;
+        float mean[8], rstd[8], sc[8], sh[8], m1[8], m2[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const int c = c8 * 8 + i;
+            mean[i] = g.has_affine ? stats[c] : 0.f; rstd[i] = g.has_affine ? stats[g.C + c] : 1.f;
+            sc[i] = g.has_affine ? stats[2 * g.C + c] : 1.f; sh[i] = g.has_affine ? stats[3 * g.C + c] : 0.f;
+            m1[i] = g.has_affine ? sums[c] * inv_m : 0.f; m2[i] = g.has_affine ? sums[g.C + c] * inv_m : 0.f;
+        }
+        float yv[R][8], dz[R][8];
+        int64_t rows[R];
+        unit_dz<POOL>(y, res, dout, g, u, c8, sc, sh, yv, dz, rows);
+#pragma unroll
+        for (int q = 0; q < R; ++q) {
+            float o[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i)
+                o[i] = g.has_affine ? sc[i] * (dz[q][i] - m1[i] - (yv[q][i] - mean[i]) * rstd[i] * m2[i]) : dz[q][i];
+            *reinterpret_cast<uint4*>(dy + rows[q] * g.C + c8 * 8) = pack8(o);
+            if (dres) *reinterpret_cast<uint4*>(dres + rows[q] * g.C + c8 * 8) = pack8(dz[q]);
+        }
     }
 }
 
@@ -477,6 +686,17 @@ extern "C" int ewdml_col2im(const void* dcol, void* dx, int N, int H, int W, int
 // sums: fp32 [2*C], must be zero on entry.  want_sq: also accumulate sum of squares in sums[C..2C).
 extern "C" int ewdml_colstats(const void* y, float* sums, int64_t M, int C, int want_sq, void* stream) {
     EWDML_CHECK_ARG(y && sums && M > 0 && C > 0 && C % 2 == 0);
+    if (C % 8 == 0) {
+        const int c8n = C / 8, lanes = c8n < 256 ? c8n : 256, rows_par = 256 / lanes;
+        const int gx = (c8n + lanes - 1) / lanes;
+        int gy = (int)((4 * 148 + gx - 1) / gx);
+        int64_t rows_per = (M + gy - 1) / gy;
+        if (rows_per < 8 * rows_par) rows_per = 8 * rows_par;
+        gy = (int)((M + rows_per - 1) / rows_per);
+        k_colstats_v8<<<dim3(gx, gy), 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)y, sums, M, C, want_sq, (int)rows_per);
+        NN_LAUNCH_CHECK();
+        return 0;
+    }
     const int cp = C / 2, lanes = cp < 256 ? cp : 256;
     const int gx = (cp + lanes - 1) / lanes;
     int gy = (int)((2 * 148 + gx - 1) / gx);
@@ -489,12 +709,19 @@ extern "C" int ewdml_colstats(const void* y, float* sums, int64_t M, int C, int 
     return 0;
 }
 
+extern "C" int ewdml_bn_finalize2(const float* sums, const float* gamma, const float* beta, float* running_mean, float* running_var,
+                                  float* stats, int C, int64_t M, float momentum, float eps, int64_t* num_batches, void* stream);
 extern "C" int ewdml_bn_finalize(const float* sums, const float* gamma, const float* beta, float* running_mean, float* running_var,
                                  float* stats, int C, int64_t M, float momentum, float eps, void* stream) {
+    return ewdml_bn_finalize2(sums, gamma, beta, running_mean, running_var, stats, C, M, momentum, eps, nullptr, stream);
+}
+// as above, and increments *num_batches (nn.BatchNorm2d.num_batches_tracked) in the same launch
+extern "C" int ewdml_bn_finalize2(const float* sums, const float* gamma, const float* beta, float* running_mean, float* running_var,
+                                  float* stats, int C, int64_t M, float momentum, float eps, int64_t* num_batches, void* stream) {
     EWDML_CHECK_ARG(sums && gamma && beta && stats && C > 0 && M > 0);
     const float unbias = M > 1 ? (float)((double)M / (double)(M - 1)) : 1.f;
     k_bn_finalize<<<(C + 127) / 128, 128, 0, (cudaStream_t)stream>>>(sums, gamma, beta, running_mean, running_var, stats, C,
-                                                                     (float)(1.0 / (double)M), unbias, momentum, eps);
+                                                                     (float)(1.0 / (double)M), unbias, momentum, eps, (long long*)num_batches);
     NN_LAUNCH_CHECK();
     return 0;
 }
@@ -532,6 +759,33 @@ extern "C" int ewdml_bn_act_bwd(const void* y, const float* stats, const void* r
     const int64_t M = (int64_t)N * H * W;
     ActGeom g = make_act(M, C, pool, N, H, W, relu, stats != nullptr);
     cudaStream_t st = (cudaStream_t)stream;
+    if (C % 8 == 0) {
+        const int64_t units = pool ? M / 4 : M;
+        if (stats) {
+            const int c8n = C / 8, lanes = c8n < 256 ? c8n : 256, par = 256 / lanes;
+            const int gx = (c8n + lanes - 1) / lanes;
+            int gy = (int)((4 * 148 + gx - 1) / gx);
+            int64_t per = (units + gy - 1) / gy;
+            if (per < 4 * par) per = 4 * par;
+            gy = (int)((units + per - 1) / per);
+            if (pool)
+                k_bn_bwd_reduce_v8<true><<<dim3(gx, gy), 256, 0, st>>>((const __nv_bfloat16*)y, (const __nv_bfloat16*)res, (const __nv_bfloat16*)dout,
+                                                                       stats, sums, g, units, (int)per);
+            else
+                k_bn_bwd_reduce_v8<false><<<dim3(gx, gy), 256, 0, st>>>((const __nv_bfloat16*)y, (const __nv_bfloat16*)res, (const __nv_bfloat16*)dout,
+                                                                        stats, sums, g, units, (int)per);
+            NN_LAUNCH_CHECK();
+        }
+        const int64_t total = units * (C / 8);
+        if (pool)
+            k_bn_bwd_apply_v8<true><<<grid_for(total), 256, 0, st>>>((const __nv_bfloat16*)y, (const __nv_bfloat16*)res, (const __nv_bfloat16*)dout, stats, sums,
+                                                                     (__nv_bfloat16*)dy, (__nv_bfloat16*)dres, dgamma, dbeta, g, (float)(1.0 / (double)M), units, total);
+        else
+            k_bn_bwd_apply_v8<false><<<grid_for(total), 256, 0, st>>>((const __nv_bfloat16*)y, (const __nv_bfloat16*)res, (const __nv_bfloat16*)dout, stats, sums,
+                                                                      (__nv_bfloat16*)dy, (__nv_bfloat16*)dres, dgamma, dbeta, g, (float)(1.0 / (double)M), units, total);
+        NN_LAUNCH_CHECK();
+        return 0;
+    }
     if (stats) {
         const int lanes = C < 256 ? C : 256;
         const int gx = (C + lanes - 1) / lanes;
@@ -551,6 +805,21 @@ extern "C" int ewdml_bn_act_bwd(const void* y, const float* stats, const void* r
     const int64_t total = M * C;
     k_bn_bwd_apply<<<grid_for(total), 256, 0, st>>>((const __nv_bfloat16*)y, (const __nv_bfloat16*)res, (const __nv_bfloat16*)dout, stats, sums,
                                                     (__nv_bfloat16*)dy, (__nv_bfloat16*)dres, g, (float)(1.0 / (double)M), total);
+    NN_LAUNCH_CHECK();
+    return 0;
+}
+
+// dst (bf16 [M][C]) = src (fp32 [M][C]) + bias; if sums != NULL also accumulates per-channel sum / sum of squares of the
+// rounded output into sums[2C] (zero on entry).  C % 8 == 0.
+extern "C" int ewdml_f32_to_bf16_stats(const float* src, const float* bias, void* dst, float* sums, int64_t M, int C, void* stream) {
+    EWDML_CHECK_ARG(src && dst && M > 0 && C > 0 && C % 8 == 0);
+    const int c8n = C / 8, lanes = c8n < 256 ? c8n : 256, rows_par = 256 / lanes;
+    const int gx = (c8n + lanes - 1) / lanes;
+    int gy = (int)((4 * 148 + gx - 1) / gx);
+    int64_t rows_per = (M + gy - 1) / gy;
+    if (rows_per < 4 * rows_par) rows_per = 4 * rows_par;
+    gy = (int)((M + rows_per - 1) / rows_per);
+    k_f32_to_bf16_stats<<<dim3(gx, gy), 256, 0, (cudaStream_t)stream>>>(src, bias, (__nv_bfloat16*)dst, sums, M, C, (int)rows_per);
     NN_LAUNCH_CHECK();
     return 0;
 }
@@ -683,7 +952,7 @@ extern "C" int ewdml_bn_stats_static(const void* y, const float* gamma, const fl
     NN_LAUNCH_CHECK();
     const float unbias = M > 1 ? (float)((double)M / (double)(M - 1)) : 1.f;
     k_bn_finalize<<<(C + 127) / 128, 128, 0, st>>>(sums, gamma, beta, running_mean, running_var, stats, C, (float)(1.0 / (double)M), unbias,
-                                                   momentum, eps);
+                                                   momentum, eps, nullptr);
     NN_LAUNCH_CHECK();
     return 0;
 }

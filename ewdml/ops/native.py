@@ -28,6 +28,8 @@ def _l():
             "ewdml_col2im": [vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, vp],
             "ewdml_colstats": [vp, vp, i64, i32, i32, vp],
             "ewdml_bn_finalize": [vp, vp, vp, vp, vp, vp, i32, i64, f32, f32, vp],
+            "ewdml_bn_finalize2": [vp, vp, vp, vp, vp, vp, i32, i64, f32, f32, vp, vp],
+            "ewdml_f32_to_bf16_stats": [vp, vp, vp, vp, i64, i32, vp],
             "ewdml_bn_act_fwd": [vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, vp],
             "ewdml_bn_act_bwd": [vp, vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, vp],
             "ewdml_add_vec_f32": [vp, vp, i32, vp],
@@ -91,6 +93,48 @@ def gemm_tn(a, b, **kw):
 
 
 # ======================================================================================
+# zero-initialised fp32 scratch: one arena per device, cleared with ONE memset per step
+# ======================================================================================
+class _Arena:
+    """Bump allocator over a pre-zeroed fp32 buffer.  ``begin_step`` clears the part used by the previous step, so
+    the dozens of small zero-filled scratch vectors of a step (BatchNorm sums, split-K accumulators) cost one memset
+    instead of one fill kernel each.  Without ``begin_step`` (unit tests) it falls back to ``torch.zeros``."""
+
+    def __init__(self):
+        self.buf, self.pos, self.hwm, self.active = None, 0, 0, False
+
+    def begin_step(self, device, nfloats: int = 48 << 20) -> None:
+        if self.buf is None or self.buf.device != device:
+            self.buf = torch.zeros(nfloats, dtype=torch.float32, device=device)
+            self.hwm = 0
+        self.hwm = max(self.hwm, self.pos)
+        if self.hwm:
+            self.buf[:self.hwm].zero_()
+        self.pos, self.active = 0, True
+
+    def zeros(self, n: int, device) -> torch.Tensor:
+        n_al = (n + 63) // 64 * 64
+        if not self.active or self.buf is None or self.buf.device != device or self.pos + n_al > self.buf.numel():
+            return torch.zeros(n, dtype=torch.float32, device=device)
+        out = self.buf[self.pos:self.pos + n]
+        self.pos += n_al
+        return out
+
+
+ARENA = _Arena()
+
+
+def begin_step(device) -> None:
+    ARENA.begin_step(device)
+
+
+def end_step() -> None:
+    """Stop handing out arena slices (anything after this point gets ordinary ``torch.zeros``)."""
+    ARENA.hwm = max(ARENA.hwm, ARENA.pos)
+    ARENA.active = False
+
+
+# ======================================================================================
 # layer functions
 # ======================================================================================
 BF16 = torch.bfloat16
@@ -150,7 +194,7 @@ def _grad2d(w: torch.nn.Parameter, rows: int, k: int) -> torch.Tensor:
 def _colsum_into(dy2d: torch.Tensor, target: torch.Tensor) -> None:
     """target (fp32 [C]) += column sums of dy2d ([M, C] bf16 contiguous)."""
     M, Cn = dy2d.shape
-    sums = torch.zeros(2 * Cn, dtype=torch.float32, device=dy2d.device)
+    sums = ARENA.zeros(2 * Cn, dy2d.device)
     L.check(_l().ewdml_colstats(_p(dy2d), _p(sums), M, Cn, 0, _stream()), "colstats")
     L.check(_l().ewdml_add_vec_f32(_p(sums), _p(target), Cn, _stream()), "add_vec")
 
@@ -183,20 +227,33 @@ class _ConvBlockFn(torch.autograd.Function):
             col = torch.empty(M, Kp, dtype=BF16, device=dev)
             L.check(lib.ewdml_im2col(_p(xn), _p(col), N, H, W, Cin, kh, kh, stride, pad, st), "im2col")
         wb = _weight_bf16(conv.weight, Cout, K)
-        y = gemm(col, wb, bias=conv.bias.detach() if conv.bias is not None else None)          # [M, Cout] bf16
+        bias = conv.bias.detach() if conv.bias is not None else None
+        train_bn = bn is not None and bn.training
+        sums = ARENA.zeros(2 * Cout, dev) if train_bn else None
+        tiles = ((M + 127) // 128) * ((Cout + 127) // 128)
+        kb = (Kp + 63) // 64
+        if tiles <= 96 and kb >= 16:
+            # few output tiles, long reduction: split-K into an fp32 accumulator, then one pass that adds the bias,
+            # rounds to bf16 and gathers the BatchNorm statistics
+            acc = ARENA.zeros(M * Cout, dev).view(M, Cout)
+            gemm(col, wb, out=acc, out_mode=OUT_ACCUM)
+            y = torch.empty(M, Cout, dtype=BF16, device=dev)
+            L.check(lib.ewdml_f32_to_bf16_stats(_p(acc), _p(bias), _p(y), _p(sums), M, Cout, st), "f32_to_bf16_stats")
+        else:
+            y = gemm(col, wb, bias=bias)                                              # [M, Cout] bf16
+            if train_bn:
+                L.check(lib.ewdml_colstats(_p(y), _p(sums), M, Cout, 1, st), "colstats")
         stats = None
         if bn is not None:
             stats = torch.empty(4 * Cout, dtype=torch.float32, device=dev)
             if bn.training:
-                sums = torch.zeros(2 * Cout, dtype=torch.float32, device=dev)
-                L.check(lib.ewdml_colstats(_p(y), _p(sums), M, Cout, 1, st), "colstats")
                 mom = bn.momentum if bn.momentum is not None else 0.1
-                L.check(lib.ewdml_bn_finalize(_p(sums), _p(bn.weight.detach()), _p(bn.bias.detach()),
-                                              _p(bn.running_mean) if bn.track_running_stats else None,
-                                              _p(bn.running_var) if bn.track_running_stats else None,
-                                              _p(stats), Cout, M, float(mom), float(bn.eps), st), "bn_finalize")
-                if bn.track_running_stats and bn.num_batches_tracked is not None:
-                    bn.num_batches_tracked += 1
+                track = bn.track_running_stats
+                L.check(lib.ewdml_bn_finalize2(_p(sums), _p(bn.weight.detach()), _p(bn.bias.detach()),
+                                               _p(bn.running_mean) if track else None, _p(bn.running_var) if track else None,
+                                               _p(stats), Cout, M, float(mom), float(bn.eps),
+                                               _p(bn.num_batches_tracked) if track and bn.num_batches_tracked is not None else None, st),
+                        "bn_finalize")
             else:
                 rstd = torch.rsqrt(bn.running_var + bn.eps)
                 sc = bn.weight.detach() * rstd
@@ -226,7 +283,7 @@ class _ConvBlockFn(torch.autograd.Function):
         if need_dz:
             dy = torch.empty(M, Cout, dtype=BF16, device=dev)
             dres = torch.empty(M, Cout, dtype=BF16, device=dev) if ctx.has_res else None
-            sums = torch.zeros(2 * Cout, dtype=torch.float32, device=dev)
+            sums = ARENA.zeros(2 * Cout, dev)
             dg = db = None
             if bn is not None:
                 if bn.weight.grad is None:
@@ -249,7 +306,14 @@ class _ConvBlockFn(torch.autograd.Function):
         dx = None
         if ctx.needs_input_grad[0]:
             wb = _weight_bf16(conv.weight, Cout, K)                      # [Cout, Kp]: used as the MN-major B operand [K=Cout][N=Kp]
-            dcol = gemm(dy, wb, False, True)                             # [M, Kp] bf16
+            tiles = ((M + 127) // 128) * ((Kp + 127) // 128)
+            if tiles <= 96 and Cout >= 1024:
+                acc = ARENA.zeros(M * Kp, dev).view(M, Kp)
+                gemm(dy, wb, False, True, out=acc, out_mode=OUT_ACCUM)
+                dcol = torch.empty(M, Kp, dtype=BF16, device=dev)
+                L.check(lib.ewdml_f32_to_bf16_stats(_p(acc), None, _p(dcol), None, M, Kp, st), "f32_to_bf16")
+            else:
+                dcol = gemm(dy, wb, False, True)                         # [M, Kp] bf16
             if direct:
                 dxn = dcol.view(N, H, W, Cin)
             else:

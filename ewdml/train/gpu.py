@@ -87,9 +87,11 @@ class GpuTrainer:
         self.graph_launches = L.launches() - before
         self.graph, self.static_loss, self.static_logits = g, loss, logits
 
-    def _step_body(self, x, y):
-        f = self.flat
-        f.grad.zero_()
+    def _forward_backward(self, x, y):
+        self.flat.grad.zero_()
+        if self.cfg.compute == "native":
+            from ..ops import native
+            native.begin_step(self.device)
         if self.autocast:
             with torch.autocast("cuda", dtype=torch.bfloat16):
                 logits = self.model(x)
@@ -98,6 +100,12 @@ class GpuTrainer:
             logits = self.model(x)
             loss = Lyr.cross_entropy(logits, y)
         loss.backward()
+        if self.cfg.compute == "native":
+            native.end_step()
+        return loss, logits
+
+    def _step_body(self, x, y):
+        loss, logits = self._forward_backward(x, y)
         self.exchange.step(self.step_idx, is_sync_step=True, want_stats=False)
         return loss.detach(), logits.detach()
 
@@ -116,16 +124,7 @@ class GpuTrainer:
             self.last_loss, self.last_logits = self.static_loss, self.static_logits
             from ..parallel.host_exchange import ExchangeStats
             return self.static_loss, ExchangeStats()
-        f = self.flat
-        f.grad.zero_()
-        if self.autocast:
-            with torch.autocast("cuda", dtype=torch.bfloat16):
-                logits = self.model(x)
-            loss = torch.nn.functional.cross_entropy(logits.float(), y)
-        else:
-            logits = self.model(x)
-            loss = Lyr.cross_entropy(logits, y)
-        loss.backward()
+        loss, logits = self._forward_backward(x, y)
         st = self.exchange.step(self.step_idx, is_sync_step=(self.step_idx % self.period == 0), want_stats=want_stats)
         self.step_idx += 1
         self.last_loss, self.last_logits = loss.detach(), logits.detach()

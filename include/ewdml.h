@@ -216,6 +216,11 @@ int ewdml_col2im(const void* dcol, void* dx, int N, int H, int W, int C, int KH,
 int ewdml_colstats(const void* y, float* sums, int64_t M, int C, int want_sq, void* stream);
 int ewdml_bn_finalize(const float* sums, const float* gamma, const float* beta, float* running_mean,
                       float* running_var, float* stats, int C, int64_t M, float momentum, float eps, void* stream);
+int ewdml_bn_finalize2(const float* sums, const float* gamma, const float* beta, float* running_mean,
+                       float* running_var, float* stats, int C, int64_t M, float momentum, float eps,
+                       int64_t* num_batches_tracked, void* stream);
+/* split-K epilogue: bf16 dst = fp32 src + bias, optionally accumulating BatchNorm column statistics in the same pass */
+int ewdml_f32_to_bf16_stats(const float* src, const float* bias, void* dst, float* sums, int64_t M, int C, void* stream);
 int ewdml_bn_act_fwd(const void* y, const float* stats, const void* res, void* out, int N, int H, int W, int C,
                      int relu, int pool, void* stream);
 int ewdml_bn_act_bwd(const void* y, const float* stats, const void* res, const void* dout, float* sums, void* dy,
