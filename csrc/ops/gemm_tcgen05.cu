@@ -31,10 +31,29 @@ constexpr int BM = 128;
 constexpr int BK = 64;              // 64 bf16 = 128 bytes = one swizzle row
 constexpr int UMMA_K = 16;
 
+// Implicit-GEMM convolution (3x3, stride 1, pad 1) without an im2col buffer.  Activations live in a zero-bordered
+// layout [N][H+2][W+2][C]; for a tile of consecutive padded pixel rows, tap (dh, dw) of the filter reads the SAME matrix
+// shifted by the constant row offset dh*(W+2)+dw, so every operand tile is still one plain 2-D TMA box:
+//   fprop : y[r]  = sum_tap  X[r + off(tap)] * W_tap^T          k-block -> (tap, 64-channel block)
+//   dgrad : dx[r] = sum_tap DY[r - off(tap)] * W_tap            k-block -> (tap, 64-channel block of C_out)
+//   wgrad : dW_tap += DY^T * X[. + off(tap)]                    n-tile  -> tap   (reduction over padded rows)
+// Rows that are border positions produce values that are simply not stored (epilogue maps padded -> compact rows).
+enum { CONV_NONE = 0, CONV_FPROP = 1, CONV_DGRAD = 2, CONV_WGRAD = 3 };
+struct ConvMap {
+    int mode;
+    int cblocks;            // 64-wide k-blocks per tap (fprop: C_in/64, dgrad: C_out/64)
+    int cin;                // C_in (dgrad: column offset of a tap in W; wgrad: n-tile -> tap)
+    int H, W;               // un-padded spatial size (for the padded -> compact row map)
+    int remap;              // 1: epilogue stores only interior rows, at their compact row index
+    int off[9];             // row offset of each tap in the padded layout
+};
+
 struct GemmArgs {
+    ConvMap cm;
     void* C;
     const float* bias;
     int M, N, K, ldc;
+    int m_store;                    // rows of C (== M except for the padded->compact conv epilogue)
     int out_mode;                   // 0: bf16 store, 1: fp32 store, 2: fp32 atomic add
     int kb_per_split, kb_total;
     float alpha;
@@ -181,19 +200,36 @@ __global__ void __launch_bounds__(192) k_gemm_tcgen05(const __grid_constant__ CU
                 mbar_wait(empty_bar(s), ph ^ 1);
                 mbar_expect_tx(full_bar(s), S::STAGE_BYTES);
                 const uint32_t a_dst = smem_base + s * S::STAGE_BYTES;
-                const int k0 = (kb0 + i) * BK;
+                const int kb = kb0 + i;
+                const int k0 = kb * BK;
+                int a_row = m_tile * BM, a_col = k0, b_row = n_tile * BN, b_col = k0;      // (row, col) = (outer, inner) of a K-major operand
+                if (g.cm.mode == CONV_FPROP) {
+                    const int tap = kb / g.cm.cblocks;
+                    a_row += g.cm.off[tap];
+                    a_col = (kb - tap * g.cm.cblocks) * BK;
+                } else if (g.cm.mode == CONV_DGRAD) {
+                    const int tap = kb / g.cm.cblocks;
+                    a_row -= g.cm.off[tap];
+                    a_col = (kb - tap * g.cm.cblocks) * BK;
+                    b_col = a_col;                          // B is MN-major here: (inner = tap*C_in + n0, outer = C_out block)
+                    b_row = tap * g.cm.cin + n_tile * BN;
+                } else if (g.cm.mode == CONV_WGRAD) {
+                    const int tap = (n_tile * BN) / g.cm.cin;
+                    b_row = n_tile * BN - tap * g.cm.cin;   // channel offset inside the tap
+                    b_col = k0 + g.cm.off[tap];             // shifted padded row (reduction index)
+                }
                 if constexpr (A_MN) {            // box = [64 k-rows][64 mn]: one slab per 64 rows of the tile
 #pragma unroll
-                    for (int h = 0; h < BM / 64; ++h) tma_load_2d(a_dst + h * (BK * 128), &tmA, full_bar(s), m_tile * BM + h * 64, k0);
+                    for (int h = 0; h < BM / 64; ++h) tma_load_2d(a_dst + h * (BK * 128), &tmA, full_bar(s), a_row + h * 64, a_col);
                 } else {
-                    tma_load_2d(a_dst, &tmA, full_bar(s), k0, m_tile * BM);
+                    tma_load_2d(a_dst, &tmA, full_bar(s), a_col, a_row);
                 }
                 if constexpr (B_MN) {
 #pragma unroll
                     for (int h = 0; h < BN / 64; ++h)
-                        tma_load_2d(a_dst + S::A_BYTES + h * (BK * 128), &tmB, full_bar(s), n_tile * BN + h * 64, k0);
+                        tma_load_2d(a_dst + S::A_BYTES + h * (BK * 128), &tmB, full_bar(s), b_row + h * 64, b_col);
                 } else {
-                    tma_load_2d(a_dst + S::A_BYTES, &tmB, full_bar(s), k0, n_tile * BN);
+                    tma_load_2d(a_dst + S::A_BYTES, &tmB, full_bar(s), b_col, b_row);
                 }
             }
         }
@@ -222,7 +258,13 @@ __global__ void __launch_bounds__(192) k_gemm_tcgen05(const __grid_constant__ CU
     } else {
         // ---- epilogue: warps 2..5 own TMEM lane quadrant (warp % 4) -----------------------------
         const int quad = warp & 3;
-        const int row = m_tile * BM + quad * 32 + lane;
+        int row = m_tile * BM + quad * 32 + lane;
+        if (g.cm.remap) {                       // padded pixel index -> compact pixel index, border rows are dropped
+            const int WP = g.cm.W + 2, HP = g.cm.H + 2;
+            const int wp = row % WP, t = row / WP, hp = t % HP, n = t / HP;
+            const bool interior = hp >= 1 && hp <= g.cm.H && wp >= 1 && wp <= g.cm.W;
+            row = interior ? (n * g.cm.H + hp - 1) * g.cm.W + (wp - 1) : g.m_store;
+        }
         if (nkb > 0) {
             mbar_wait(tmem_full_bar, 0);
             tcgen05_fence_after();
@@ -237,7 +279,7 @@ __global__ void __launch_bounds__(192) k_gemm_tcgen05(const __grid_constant__ CU
                 for (int j = 0; j < 32; ++j) v[j] = 0;
             }
             const int col0 = n_tile * BN + c * 32;
-            if (row >= g.M || col0 >= g.N) continue;
+            if (row >= g.m_store || col0 >= g.N) continue;
             float f[32];
 #pragma unroll
             for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]) * g.alpha;
@@ -342,16 +384,22 @@ int launch(const CUtensorMap& tA, const CUtensorMap& tB, const GemmArgs& g, int 
     return 0;
 }
 
+struct TmapDims { int64_t a_outer, a_inner, b_outer, b_inner; };   // rows / contiguous width of the matrices the maps describe
+
 template <bool A_MN, bool B_MN>
 int gemm_dispatch(const void* A, const void* B, void* C, int M, int N, int K, int lda, int ldb, int ldc, int out_mode,
-                  const float* bias, float alpha, int split_k, void* stream) {
+                  const float* bias, float alpha, int split_k, void* stream, const ConvMap* cm = nullptr,
+                  const TmapDims* td = nullptr, int bn_force = 0, int m_store = -1, int kb_total = -1) {
     EWDML_CHECK_ARG(A && B && C && M > 0 && N > 0 && K > 0);
     EWDML_CHECK_ARG(lda % 8 == 0 && ldb % 8 == 0 && ((uintptr_t)A % 16) == 0 && ((uintptr_t)B % 16) == 0);
     EWDML_CHECK_ARG(out_mode >= 0 && out_mode <= 2);
-    const int bn = N <= 64 ? 64 : 128;
+    const int bn = bn_force ? bn_force : (N <= 64 ? 64 : 128);
     GemmArgs g;
+    memset(&g, 0, sizeof(g));
+    if (cm) g.cm = *cm;
     g.C = C; g.bias = bias; g.M = M; g.N = N; g.K = K; g.ldc = ldc; g.out_mode = out_mode; g.alpha = alpha;
-    g.kb_total = (K + BK - 1) / BK;
+    g.m_store = m_store >= 0 ? m_store : M;
+    g.kb_total = kb_total > 0 ? kb_total : (K + BK - 1) / BK;
     int tiles = ((M + BM - 1) / BM) * ((N + bn - 1) / bn);
     int split = split_k;
     if (split <= 0) {
@@ -367,13 +415,24 @@ int gemm_dispatch(const void* A, const void* B, void* C, int M, int N, int K, in
     split = (g.kb_total + g.kb_per_split - 1) / g.kb_per_split;     // no empty splits
     CUtensorMap tA, tB;
     // K-major: matrix is [rows][K]; MN-major: matrix is [K][rows] (rows contiguous)
-    int rc = A_MN ? make_tmap(&tA, A, K, M, lda, 64) : make_tmap(&tA, A, M, K, lda, BM);
-    if (rc) return rc;
-    rc = B_MN ? make_tmap(&tB, B, K, N, ldb, 64) : make_tmap(&tB, B, N, K, ldb, bn);
+    int rc;
+    if (td) {
+        rc = make_tmap(&tA, A, td->a_outer, td->a_inner, lda, A_MN ? 64 : BM);
+        if (rc) return rc;
+        rc = make_tmap(&tB, B, td->b_outer, td->b_inner, ldb, B_MN ? 64 : bn);
+    } else {
+        rc = A_MN ? make_tmap(&tA, A, K, M, lda, 64) : make_tmap(&tA, A, M, K, lda, BM);
+        if (rc) return rc;
+        rc = B_MN ? make_tmap(&tB, B, K, N, ldb, 64) : make_tmap(&tB, B, N, K, ldb, bn);
+    }
     if (rc) return rc;
     cudaStream_t st = (cudaStream_t)stream;
-    if (bn == 64) return launch<64, 4, A_MN, B_MN>(tA, tB, g, split, st);
-    return launch<128, 3, A_MN, B_MN>(tA, tB, g, split, st);
+    // Pipeline depth: a CTA's k-block rate is (stages in flight) / (TMA round trip).  When the grid fits one CTA per SM
+    // there is no second resident CTA to hide that latency, so use the whole shared memory for a deep ring instead.
+    const int ctas = tiles * split;
+    const bool deep = ctas <= 160;
+    if (bn == 64) return deep ? launch<64, 8, A_MN, B_MN>(tA, tB, g, split, st) : launch<64, 4, A_MN, B_MN>(tA, tB, g, split, st);
+    return deep ? launch<128, 6, A_MN, B_MN>(tA, tB, g, split, st) : launch<128, 3, A_MN, B_MN>(tA, tB, g, split, st);
 }
 
 }  // namespace
@@ -395,4 +454,40 @@ extern "C" int ewdml_gemm_bf16(const void* A, const void* B, void* C, int M, int
 extern "C" int ewdml_gemm_bf16_tn(const void* A, const void* B, void* C, int M, int N, int K, int lda, int ldb, int ldc,
                                   int out_mode, const float* bias, float alpha, int split_k, void* stream) {
     return ewdml_gemm_bf16(A, B, C, M, N, K, lda, ldb, ldc, 0, 0, out_mode, bias, alpha, split_k, stream);
+}
+
+// Implicit-GEMM 3x3 / stride 1 / pad 1 convolution passes on zero-bordered NHWC activations [N][H+2][W+2][C] (bf16).
+//   pass 1 (fprop): A = padded x,   B = W [C_out][9*C_in],          C = y  compact [N*H*W][C_out]
+//   pass 2 (dgrad): A = padded dy,  B = W [C_out][9*C_in],          C = dx compact [N*H*W][C_in]
+//   pass 3 (wgrad): A = padded dy,  B = padded x,                   C = dW fp32 [C_out][9*C_in] (accumulated; out_mode forced to 2)
+// C_in and C_out must be multiples of 64.  out_mode as in ewdml_gemm_bf16 (2 = fp32 accumulate, allows split-K).
+extern "C" int ewdml_conv3x3_igemm(int pass, const void* A, const void* B, void* C, int N, int H, int W, int Cin, int Cout,
+                                   int out_mode, const float* bias, int split_k, void* stream) {
+    EWDML_CHECK_ARG(pass >= 1 && pass <= 3 && Cin % 64 == 0 && Cout % 64 == 0 && N > 0 && H > 0 && W > 0);
+    const int WP = W + 2, HP = H + 2;
+    const int64_t Mp64 = (int64_t)N * HP * WP, Mc64 = (int64_t)N * H * W;
+    EWDML_CHECK_ARG(Mp64 < (1ll << 31));
+    const int Mp = (int)Mp64, Mc = (int)Mc64, K9 = 9 * Cin;
+    ConvMap cm;
+    memset(&cm, 0, sizeof(cm));
+    for (int kh = 0; kh < 3; ++kh)
+        for (int kw = 0; kw < 3; ++kw) cm.off[kh * 3 + kw] = (kh - 1) * WP + (kw - 1);
+    cm.H = H; cm.W = W; cm.cin = Cin;
+    TmapDims td;
+    if (pass == 1) {
+        cm.mode = CONV_FPROP; cm.cblocks = Cin / 64; cm.remap = 1;
+        td = {Mp, Cin, Cout, K9};
+        return gemm_dispatch<false, false>(A, B, C, Mp, Cout, K9, Cin, K9, Cout, out_mode, bias, 1.f, split_k, stream, &cm, &td, 0, Mc,
+                                           9 * (Cin / 64));
+    }
+    if (pass == 2) {
+        cm.mode = CONV_DGRAD; cm.cblocks = Cout / 64; cm.remap = 1;
+        td = {Mp, Cout, Cout, K9};                 // B: matrix [C_out rows][9*C_in contiguous], used MN-major
+        return gemm_dispatch<false, true>(A, B, C, Mp, Cin, 9 * Cout, Cout, K9, Cin, out_mode, bias, 1.f, split_k, stream, &cm, &td,
+                                          Cin == 64 ? 64 : 128, Mc, 9 * (Cout / 64));
+    }
+    cm.mode = CONV_WGRAD; cm.remap = 0;
+    td = {Mp, Cout, Mp, Cin};                      // both MN-major: [padded rows][channels]
+    return gemm_dispatch<true, true>(A, B, C, Cout, K9, Mp, Cout, Cin, K9, 2, nullptr, 1.f, split_k, stream, &cm, &td,
+                                     Cin == 64 ? 64 : 128, Cout, (Mp + BK - 1) / BK);
 }

@@ -116,6 +116,20 @@ __global__ void __launch_bounds__(256) k_col2im(const __nv_bfloat16* __restrict_
     }
 }
 
+// compact NHWC -> zero-bordered [N][H+2][W+2][C] (operand layout of the implicit-GEMM 3x3 convolution)
+__global__ void __launch_bounds__(256) k_pad_nhwc(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ out, int N, int H, int W, int C, int64_t total) {
+    const int c8n = C >> 3, WP = W + 2, HP = H + 2;
+    for (int64_t t = (int64_t)blockIdx.x * 256 + threadIdx.x; t < total; t += (int64_t)gridDim.x * 256) {
+        const int c8 = (int)(t % c8n);
+        const int64_t r = t / c8n;
+        const int wp = (int)(r % WP), hp = (int)((r / WP) % HP), n = (int)(r / ((int64_t)WP * HP));
+        uint4 v = make_uint4(0, 0, 0, 0);
+        if (hp >= 1 && hp <= H && wp >= 1 && wp <= W)
+            v = *reinterpret_cast<const uint4*>(x + (((int64_t)n * H + hp - 1) * W + wp - 1) * C + c8 * 8);
+        *reinterpret_cast<uint4*>(out + r * C + c8 * 8) = v;
+    }
+}
+
 // ---------------------------------------------------------------------------------------------
 // per-channel column statistics of a [M, C] bf16 matrix: sum and (optionally) sum of squares, or the
 // two BatchNorm-backward sums.  Thread = one channel pair; a CTA covers `rows_par` rows at a time.
@@ -132,6 +146,22 @@ struct ActGeom {
 // z value before activation for element (row, c): scale*y + shift (+ residual)
 __device__ __forceinline__ float pre_act(float y, float sc, float sh, float res) { return fmaf(sc, y, sh) + res; }
 
+// Fold NV per-thread partial sums into the CTA's shared accumulator red[lane*16 + i].  Threads whose index differs by a
+// multiple of `lanes` hold partials of the same channels; when lanes < 32 those threads sit in the same warp, so they are
+// combined with shuffles first and only one thread per (warp, channel group) touches shared memory.
+template <int NV>
+__device__ __forceinline__ void fold_partials(float (&v)[NV], float* red, int lanes, int lane, int base) {
+    const bool shuffle = lanes < 32 && (lanes & (lanes - 1)) == 0;
+    if (shuffle) {
+        for (int d = lanes; d < 32; d <<= 1)
+#pragma unroll
+            for (int i = 0; i < NV; ++i) v[i] += __shfl_xor_sync(0xffffffffu, v[i], d);
+        if ((int)(threadIdx.x & 31) >= lanes) return;
+    }
+#pragma unroll
+    for (int i = 0; i < NV; ++i) atomicAdd(&red[lane * 16 + base + i], v[i]);
+}
+
 // 8 channels per thread (one 16-byte load per row), `lanes` threads along channels, 256/lanes rows in flight
 // per CTA; per-CTA reduction in shared memory, then one global atomic per channel per CTA.
 __global__ void __launch_bounds__(256) k_colstats_v8(const __nv_bfloat16* __restrict__ y, float* __restrict__ sums, int64_t M, int C, int want_sq,
@@ -146,20 +176,21 @@ __global__ void __launch_bounds__(256) k_colstats_v8(const __nv_bfloat16* __rest
     const int64_t r1 = r0 + rows_per_cta < M ? r0 + rows_per_cta : M;
     for (int i = threadIdx.x; i < lanes * 16; i += 256) red[i] = 0.f;
     __syncthreads();
-    if (c8 < c8n && rsub < rows_par) {
+    {
         float s[8], q[8];
 #pragma unroll
         for (int i = 0; i < 8; ++i) { s[i] = 0.f; q[i] = 0.f; }
-        for (int64_t r = r0 + rsub; r < r1; r += rows_par) {
-            float f[8];
-            unpack8(*reinterpret_cast<const uint4*>(y + r * C + c8 * 8), f);
+        if (c8 < c8n && rsub < rows_par) {
+            for (int64_t r = r0 + rsub; r < r1; r += rows_par) {
+                float f[8];
+                unpack8(*reinterpret_cast<const uint4*>(y + r * C + c8 * 8), f);
 #pragma unroll
-            for (int i = 0; i < 8; ++i) { s[i] += f[i]; q[i] = fmaf(f[i], f[i], q[i]); }
+                for (int i = 0; i < 8; ++i) { s[i] += f[i]; q[i] = fmaf(f[i], f[i], q[i]); }
+            }
         }
-#pragma unroll
-        for (int i = 0; i < 8; ++i) {
-            atomicAdd(&red[lane * 16 + i], s[i]);
-            if (want_sq) atomicAdd(&red[lane * 16 + 8 + i], q[i]);
+        if (lanes * rows_par == 256 || (c8 < c8n && rsub < rows_par)) {
+            fold_partials<8>(s, red, lanes, lane, 0);
+            if (want_sq) fold_partials<8>(q, red, lanes, lane, 8);
         }
     }
     __syncthreads();
@@ -475,11 +506,18 @@ __global__ void __launch_bounds__(256) k_bn_bwd_reduce_v8(const __nv_bfloat16* _
                     sx[i] = fmaf(dz[q][i], (yv[q][i] - mean[i]) * rstd[i], sx[i]);
                 }
         }
+        if (lanes * par != 256) {
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
-            atomicAdd(&red[lane * 16 + i], s[i]);
-            atomicAdd(&red[lane * 16 + 8 + i], sx[i]);
+            for (int i = 0; i < 8; ++i) { atomicAdd(&red[lane * 16 + i], s[i]); atomicAdd(&red[lane * 16 + 8 + i], sx[i]); }
+        } else {
+            fold_partials<8>(s, red, lanes, lane, 0);
+            fold_partials<8>(sx, red, lanes, lane, 8);
         }
+    } else if (lanes * par == 256) {
+        // (unreachable when the CTA is full: every thread has c8 < c8n or the whole warp is out of range)
+        float z[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+        fold_partials<8>(z, red, lanes, lane, 0);
+        fold_partials<8>(z, red, lanes, lane, 8);
     }
     __syncthreads();
     for (int i = threadIdx.x; i < lanes * 16; i += 256) {
@@ -820,6 +858,14 @@ extern "C" int ewdml_f32_to_bf16_stats(const float* src, const float* bias, void
     if (rows_per < 4 * rows_par) rows_per = 4 * rows_par;
     gy = (int)((M + rows_per - 1) / rows_per);
     k_f32_to_bf16_stats<<<dim3(gx, gy), 256, 0, (cudaStream_t)stream>>>(src, bias, (__nv_bfloat16*)dst, sums, M, C, (int)rows_per);
+    NN_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int ewdml_pad_nhwc(const void* x, void* out, int N, int H, int W, int C, void* stream) {
+    EWDML_CHECK_ARG(x && out && C % 8 == 0);
+    const int64_t total = (int64_t)N * (H + 2) * (W + 2) * (C / 8);
+    k_pad_nhwc<<<grid_for(total), 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)x, (__nv_bfloat16*)out, N, H, W, C, total);
     NN_LAUNCH_CHECK();
     return 0;
 }

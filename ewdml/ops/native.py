@@ -25,6 +25,8 @@ def _l():
         sig = {
             "ewdml_gemm_bf16": [vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, i32, vp, f32, i32, vp],
             "ewdml_im2col": [vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, vp],
+            "ewdml_conv3x3_igemm": [i32, vp, vp, vp, i32, i32, i32, i32, i32, i32, vp, i32, vp],
+            "ewdml_pad_nhwc": [vp, vp, i32, i32, i32, i32, vp],
             "ewdml_col2im": [vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, vp],
             "ewdml_colstats": [vp, vp, i64, i32, i32, vp],
             "ewdml_bn_finalize": [vp, vp, vp, vp, vp, vp, i32, i64, f32, f32, vp],
@@ -58,6 +60,7 @@ def _p(t: Optional[torch.Tensor]):
 
 
 OUT_BF16, OUT_F32, OUT_ACCUM = 0, 1, 2
+USE_IGEMM = True      # implicit-GEMM path for 3x3 / stride 1 / pad 1 convolutions with C_in, C_out % 64 == 0
 
 # device step state of the active trainer (uint32[4] tensor) -- lets dropout masks change on graph replays
 STEP_STATE = {"tensor": None}
@@ -221,28 +224,40 @@ class _ConvBlockFn(torch.autograd.Function):
         Kp = _r8(K)
         xn = to_nhwc_bf16(x)
         direct = kh == 1 and stride == 1 and pad == 0 and Cin % 8 == 0
-        if direct:
-            col = xn.view(M, Cin)
-        else:
-            col = torch.empty(M, Kp, dtype=BF16, device=dev)
-            L.check(lib.ewdml_im2col(_p(xn), _p(col), N, H, W, Cin, kh, kh, stride, pad, st), "im2col")
+        igemm = USE_IGEMM and kh == 3 and stride == 1 and pad == 1 and Cin % 64 == 0 and Cout % 64 == 0
         wb = _weight_bf16(conv.weight, Cout, K)
         bias = conv.bias.detach() if conv.bias is not None else None
         train_bn = bn is not None and bn.training
         sums = ARENA.zeros(2 * Cout, dev) if train_bn else None
-        tiles = ((M + 127) // 128) * ((Cout + 127) // 128)
-        kb = (Kp + 63) // 64
-        if tiles <= 96 and kb >= 16:
-            # few output tiles, long reduction: split-K into an fp32 accumulator, then one pass that adds the bias,
-            # rounds to bf16 and gathers the BatchNorm statistics
-            acc = ARENA.zeros(M * Cout, dev).view(M, Cout)
-            gemm(col, wb, out=acc, out_mode=OUT_ACCUM)
-            y = torch.empty(M, Cout, dtype=BF16, device=dev)
-            L.check(lib.ewdml_f32_to_bf16_stats(_p(acc), _p(bias), _p(y), _p(sums), M, Cout, st), "f32_to_bf16_stats")
+        if igemm:
+            # implicit GEMM: zero-bordered copy of x, every filter tap is a row-shifted TMA load of the same matrix
+            col = torch.empty(N, H + 2, W + 2, Cin, dtype=BF16, device=dev)
+            L.check(lib.ewdml_pad_nhwc(_p(xn), _p(col), N, H, W, Cin, st), "pad_nhwc")
+            m_rows, kb = N * (H + 2) * (W + 2), 9 * (Cin // 64)
         else:
-            y = gemm(col, wb, bias=bias)                                              # [M, Cout] bf16
-            if train_bn:
-                L.check(lib.ewdml_colstats(_p(y), _p(sums), M, Cout, 1, st), "colstats")
+            if direct:
+                col = xn.view(M, Cin)
+            else:
+                col = torch.empty(M, Kp, dtype=BF16, device=dev)
+                L.check(lib.ewdml_im2col(_p(xn), _p(col), N, H, W, Cin, kh, kh, stride, pad, st), "im2col")
+            m_rows, kb = M, (Kp + 63) // 64
+        tiles = ((m_rows + 127) // 128) * ((Cout + 127) // 128)
+        split = tiles <= 96 and kb >= 16
+        # few output tiles + long reduction: split-K into an fp32 accumulator, then one pass that adds the bias, rounds
+        # to bf16 and gathers the BatchNorm statistics
+        acc = ARENA.zeros(M * Cout, dev).view(M, Cout) if split else None
+        y = torch.empty(M, Cout, dtype=BF16, device=dev)
+        if igemm:
+            L.check(lib.ewdml_conv3x3_igemm(1, _p(col), _p(wb), _p(acc if split else y), N, H, W, Cin, Cout,
+                                            OUT_ACCUM if split else OUT_BF16, None if split else _p(bias), 0, st), "igemm fprop")
+        elif split:
+            gemm(col, wb, out=acc, out_mode=OUT_ACCUM)
+        else:
+            gemm(col, wb, out=y, bias=bias)
+        if split:
+            L.check(lib.ewdml_f32_to_bf16_stats(_p(acc), _p(bias), _p(y), _p(sums), M, Cout, st), "f32_to_bf16_stats")
+        elif train_bn:
+            L.check(lib.ewdml_colstats(_p(y), _p(sums), M, Cout, 1, st), "colstats")
         stats = None
         if bn is not None:
             stats = torch.empty(4 * Cout, dtype=torch.float32, device=dev)
@@ -264,7 +279,7 @@ class _ConvBlockFn(torch.autograd.Function):
         L.check(lib.ewdml_bn_act_fwd(_p(y), _p(stats), _p(resn), _p(out), N, HO, WO, Cout, int(relu), int(pool), st), "bn_act_fwd")
         ctx.save_for_backward(col, y, stats if stats is not None else torch.empty(0, device=dev),
                               resn if resn is not None else torch.empty(0, device=dev))
-        ctx.meta = (conv, bn, relu, pool, N, H, W, Cin, HO, WO, Cout, kh, stride, pad, M, K, Kp, direct)
+        ctx.meta = (conv, bn, relu, pool, N, H, W, Cin, HO, WO, Cout, kh, stride, pad, M, K, Kp, direct, igemm)
         ctx.has_res = residual is not None
         return out.permute(0, 3, 1, 2)
 
@@ -273,7 +288,7 @@ class _ConvBlockFn(torch.autograd.Function):
         lib = _l()
         st = _stream()
         col, y, stats, resn = ctx.saved_tensors
-        conv, bn, relu, pool, N, H, W, Cin, HO, WO, Cout, kh, stride, pad, M, K, Kp, direct = ctx.meta
+        conv, bn, relu, pool, N, H, W, Cin, HO, WO, Cout, kh, stride, pad, M, K, Kp, direct, igemm = ctx.meta
         dev = dout.device
         stats = stats if stats.numel() else None
         resn = resn if resn.numel() else None
@@ -296,30 +311,46 @@ class _ConvBlockFn(torch.autograd.Function):
         else:
             dy = dn.view(M, Cout)
             dres = dy if ctx.has_res else None
-        # weight gradient: dW[Cout, K] += dy^T col   (both operands MN-major, split-K, fp32 atomics into the flat buffer)
         gw = _grad2d(conv.weight, Cout, K)
-        gemm(dy, col[:, :K] if Kp != K else col, True, True, out=gw, out_mode=OUT_ACCUM)
         if conv.bias is not None and bn is None:
             if conv.bias.grad is None:
                 conv.bias.grad = torch.zeros_like(conv.bias)
             _colsum_into(dy, conv.bias.grad)
         dx = None
-        if ctx.needs_input_grad[0]:
-            wb = _weight_bf16(conv.weight, Cout, K)                      # [Cout, Kp]: used as the MN-major B operand [K=Cout][N=Kp]
-            tiles = ((M + 127) // 128) * ((Kp + 127) // 128)
-            if tiles <= 96 and Cout >= 1024:
-                acc = ARENA.zeros(M * Kp, dev).view(M, Kp)
-                gemm(dy, wb, False, True, out=acc, out_mode=OUT_ACCUM)
-                dcol = torch.empty(M, Kp, dtype=BF16, device=dev)
-                L.check(lib.ewdml_f32_to_bf16_stats(_p(acc), None, _p(dcol), None, M, Kp, st), "f32_to_bf16")
-            else:
-                dcol = gemm(dy, wb, False, True)                         # [M, Kp] bf16
-            if direct:
-                dxn = dcol.view(N, H, W, Cin)
-            else:
+        if igemm:
+            dyp = torch.empty(N, H + 2, W + 2, Cout, dtype=BF16, device=dev)
+            L.check(lib.ewdml_pad_nhwc(_p(dy), _p(dyp), N, H, W, Cout, st), "pad_nhwc dy")
+            L.check(lib.ewdml_conv3x3_igemm(3, _p(dyp), _p(col), _p(gw), N, H, W, Cin, Cout, OUT_ACCUM, None, 0, st), "igemm wgrad")
+            if ctx.needs_input_grad[0]:
+                wb = _weight_bf16(conv.weight, Cout, K)
+                tiles = ((N * (H + 2) * (W + 2) + 127) // 128) * ((Cin + 127) // 128)
                 dxn = torch.empty(N, H, W, Cin, dtype=BF16, device=dev)
-                L.check(lib.ewdml_col2im(_p(dcol), _p(dxn), N, H, W, Cin, kh, kh, stride, pad, st), "col2im")
-            dx = dxn.permute(0, 3, 1, 2)
+                if tiles <= 96:
+                    acc = ARENA.zeros(M * Cin, dev)
+                    L.check(lib.ewdml_conv3x3_igemm(2, _p(dyp), _p(wb), _p(acc), N, H, W, Cin, Cout, OUT_ACCUM, None, 0, st), "igemm dgrad")
+                    L.check(lib.ewdml_f32_to_bf16_stats(_p(acc), None, _p(dxn), None, M, Cin, st), "f32_to_bf16")
+                else:
+                    L.check(lib.ewdml_conv3x3_igemm(2, _p(dyp), _p(wb), _p(dxn), N, H, W, Cin, Cout, OUT_BF16, None, 0, st), "igemm dgrad")
+                dx = dxn.permute(0, 3, 1, 2)
+        else:
+            # weight gradient: dW[Cout, K] += dy^T col (both operands MN-major, split-K, fp32 atomics into the flat buffer)
+            gemm(dy, col[:, :K] if Kp != K else col, True, True, out=gw, out_mode=OUT_ACCUM)
+            if ctx.needs_input_grad[0]:
+                wb = _weight_bf16(conv.weight, Cout, K)                  # [Cout, Kp]: used as the MN-major B operand [K=Cout][N=Kp]
+                tiles = ((M + 127) // 128) * ((Kp + 127) // 128)
+                if tiles <= 96 and Cout >= 1024:
+                    acc = ARENA.zeros(M * Kp, dev).view(M, Kp)
+                    gemm(dy, wb, False, True, out=acc, out_mode=OUT_ACCUM)
+                    dcol = torch.empty(M, Kp, dtype=BF16, device=dev)
+                    L.check(lib.ewdml_f32_to_bf16_stats(_p(acc), None, _p(dcol), None, M, Kp, st), "f32_to_bf16")
+                else:
+                    dcol = gemm(dy, wb, False, True)                     # [M, Kp] bf16
+                if direct:
+                    dxn = dcol.view(N, H, W, Cin)
+                else:
+                    dxn = torch.empty(N, H, W, Cin, dtype=BF16, device=dev)
+                    L.check(lib.ewdml_col2im(_p(dcol), _p(dxn), N, H, W, Cin, kh, kh, stride, pad, st), "col2im")
+                dx = dxn.permute(0, 3, 1, 2)
         dr = dres.view(N, HO, WO, Cout).permute(0, 3, 1, 2) if (ctx.has_res and ctx.needs_input_grad[1]) else None
         return dx, dr, None, None, None, None, None
 

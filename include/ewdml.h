@@ -207,6 +207,13 @@ int ewdml_gemm_bf16(const void* A, const void* B, void* C, int M, int N, int K, 
 /* K5 operand builders (nn.Conv2d, vgg.py:53, resnet.py:19-55): NHWC bf16 x -> col[M][Kp], Kp = round_up(KH*KW*C, 8);
  * and the data-gradient gather dcol -> dx.                                                              */
 int ewdml_im2col(const void* x, void* col, int N, int H, int W, int C, int KH, int KW, int stride, int pad, void* stream);
+/* Implicit-GEMM 3x3 / stride 1 / pad 1 convolution (no im2col buffer): activations in the zero-bordered layout
+ * [N][H+2][W+2][C] built by ewdml_pad_nhwc; pass 1 = fprop (A = padded x, B = W, C = y compact), pass 2 = dgrad
+ * (A = padded dy, B = W, C = dx compact), pass 3 = wgrad (A = padded dy, B = padded x, C = dW fp32 accumulated).
+ * C_in, C_out multiples of 64.  Every operand tile is a plain 2-D TMA box shifted by a per-tap row offset.           */
+int ewdml_conv3x3_igemm(int pass, const void* A, const void* B, void* C, int N, int H, int W, int Cin, int Cout,
+                        int out_mode, const float* bias, int split_k, void* stream);
+int ewdml_pad_nhwc(const void* x, void* out, int N, int H, int W, int C, void* stream);
 int ewdml_col2im(const void* dcol, void* dx, int N, int H, int W, int C, int KH, int KW, int stride, int pad, void* stream);
 
 /* K7/K8 (nn.BatchNorm2d train mode, ReLU, residual add, MaxPool2d(2,2); vgg.py:51-55, resnet.py:20-63):

@@ -36,6 +36,10 @@ def _round(t):
     (64, 256, 1, 2, 0, 8, True, False, False, False),     # shortcut conv
     (32, 32, 3, 1, 1, 8, True, True, False, True),        # residual add
     (16, 24, 5, 1, 0, 12, False, True, True, False),      # no BN (LeNet-like), bias grad
+    (128, 64, 3, 1, 1, 8, True, True, False, False),       # implicit GEMM, C_in 128 (two k-blocks per tap)
+    (64, 64, 3, 1, 1, 4, True, True, True, False),         # implicit GEMM, BN=64 tiles, tiny spatial size
+    (256, 512, 3, 1, 1, 2, True, True, True, False),       # implicit GEMM + split-K (few tiles, K = 2304)
+    (512, 512, 3, 1, 1, 4, True, True, False, True),       # implicit GEMM + split-K + residual
 ])
 def test_conv_block_forward_backward(cin, cout, k, stride, pad, hw, bn, relu, pool, res):
     from ewdml.ops import native
