@@ -158,7 +158,8 @@ struct Smem {
     static constexpr int B_BYTES = BN * BK * 2;
     static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
     static constexpr int BAR_OFF = STAGES * STAGE_BYTES;
-    static constexpr int TOTAL = BAR_OFF + 8 * (2 * STAGES + 1) + 16 + 1024;   // + alignment slack
+    static constexpr int BIAS_OFF = BAR_OFF + 8 * (2 * STAGES + 1) + 16;
+    static constexpr int TOTAL = BIAS_OFF + BN * 4 + 1024;                     // + alignment slack
 };
 
 template <int BN, int STAGES, bool A_MN, bool B_MN>
@@ -258,6 +259,16 @@ __global__ void __launch_bounds__(192) k_gemm_tcgen05(const __grid_constant__ CU
     } else {
         // ---- epilogue: warps 2..5 own TMEM lane quadrant (warp % 4) -----------------------------
         const int quad = warp & 3;
+        // stage this tile's bias slice in shared memory while the main loop runs (no global loads on the critical path)
+        float* s_bias = reinterpret_cast<float*>(smem + S::BIAS_OFF);
+        const bool use_bias = g.bias != nullptr && blockIdx.z == 0;
+        if (use_bias) {
+            for (int j = threadIdx.x - 64; j < BN; j += 128) {
+                const int c = n_tile * BN + j;
+                s_bias[j] = c < g.N ? g.bias[c] : 0.f;
+            }
+            asm volatile("bar.sync 1, 128;" ::: "memory");       // epilogue warps only
+        }
         int row = m_tile * BM + quad * 32 + lane;
         if (g.cm.remap) {                       // padded pixel index -> compact pixel index, border rows are dropped
             const int WP = g.cm.W + 2, HP = g.cm.H + 2;
@@ -283,10 +294,9 @@ __global__ void __launch_bounds__(192) k_gemm_tcgen05(const __grid_constant__ CU
             float f[32];
 #pragma unroll
             for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]) * g.alpha;
-            if (g.bias != nullptr && blockIdx.z == 0) {
+            if (use_bias) {
 #pragma unroll
-                for (int j = 0; j < 32; ++j)
-                    if (col0 + j < g.N) f[j] += g.bias[col0 + j];
+                for (int j = 0; j < 32; ++j) f[j] += s_bias[c * 32 + j];
             }
             const bool full = col0 + 32 <= g.N;
             if (g.out_mode == 0) {
@@ -302,7 +312,9 @@ __global__ void __launch_bounds__(192) k_gemm_tcgen05(const __grid_constant__ CU
                         *reinterpret_cast<uint4*>(out + j) = pk;
                     }
                 } else {
-                    for (int j = 0; j < 32 && col0 + j < g.N; ++j) out[j] = __float2bfloat16_rn(f[j]);
+#pragma unroll
+                    for (int j = 0; j < 32; ++j)
+                        if (col0 + j < g.N) out[j] = __float2bfloat16_rn(f[j]);
                 }
             } else if (g.out_mode == 1) {
                 float* out = reinterpret_cast<float*>(g.C) + (size_t)row * g.ldc + col0;
@@ -310,7 +322,9 @@ __global__ void __launch_bounds__(192) k_gemm_tcgen05(const __grid_constant__ CU
 #pragma unroll
                     for (int j = 0; j < 32; j += 4) *reinterpret_cast<float4*>(out + j) = make_float4(f[j], f[j + 1], f[j + 2], f[j + 3]);
                 } else {
-                    for (int j = 0; j < 32 && col0 + j < g.N; ++j) out[j] = f[j];
+#pragma unroll
+                    for (int j = 0; j < 32; ++j)
+                        if (col0 + j < g.N) out[j] = f[j];
                 }
             } else {
                 float* out = reinterpret_cast<float*>(g.C) + (size_t)row * g.ldc + col0;
@@ -321,7 +335,9 @@ __global__ void __launch_bounds__(192) k_gemm_tcgen05(const __grid_constant__ CU
                                      "f"(f[j + 3])
                                      : "memory");
                 } else {
-                    for (int j = 0; j < 32 && col0 + j < g.N; ++j) atomicAdd(out + j, f[j]);
+#pragma unroll
+                    for (int j = 0; j < 32; ++j)
+                        if (col0 + j < g.N) atomicAdd(out + j, f[j]);
                 }
             }
         }

@@ -55,19 +55,32 @@ __global__ void __launch_bounds__(256) k_im2col_vec8(const __nv_bfloat16* __rest
     }
 }
 
-// any C (1, 3, 20 ...): one element per thread, zero padding of [K, Kp)
+// any C (1, 3, 20 ...): one thread builds 8 consecutive k entries (one 16-byte store), zero padding of [K, Kp)
 __global__ void __launch_bounds__(256) k_im2col_scalar(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ col, ConvGeom g, int64_t total) {
+    const int kgn = g.Kp >> 3;
     for (int64_t t = (int64_t)blockIdx.x * 256 + threadIdx.x; t < total; t += (int64_t)gridDim.x * 256) {
-        const int kidx = (int)(t % g.Kp);
-        const int64_t m = t / g.Kp;
-        __nv_bfloat16 v = __float2bfloat16(0.f);
-        if (kidx < g.K) {
-            const int c = kidx % g.C, tap = kidx / g.C;
-            const int wo = (int)(m % g.WO), ho = (int)((m / g.WO) % g.HO), n = (int)(m / ((int64_t)g.WO * g.HO));
-            const int h = ho * g.stride - g.pad + tap / g.KW, w = wo * g.stride - g.pad + tap % g.KW;
-            if (h >= 0 && h < g.H && w >= 0 && w < g.W) v = x[(((int64_t)n * g.H + h) * g.W + w) * g.C + c];
+        const int kg = (int)(t % kgn);
+        const int64_t m = t / kgn;
+        const int wo = (int)(m % g.WO), ho = (int)((m / g.WO) % g.HO), n = (int)(m / ((int64_t)g.WO * g.HO));
+        const int h0 = ho * g.stride - g.pad, w0 = wo * g.stride - g.pad;
+        const __nv_bfloat16* img = x + (int64_t)n * g.H * g.W * g.C;
+        unsigned short v[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const int kidx = kg * 8 + i;
+            v[i] = 0;
+            if (kidx < g.K) {
+                const int tap = kidx / g.C, c = kidx - tap * g.C;
+                const int kh = tap / g.KW, kw = tap - kh * g.KW;
+                const int h = h0 + kh, w = w0 + kw;
+                if (h >= 0 && h < g.H && w >= 0 && w < g.W)
+                    v[i] = *reinterpret_cast<const unsigned short*>(img + ((int64_t)h * g.W + w) * g.C + c);
+            }
         }
-        col[t] = v;
+        uint4 pk;
+        pk.x = v[0] | ((uint32_t)v[1] << 16); pk.y = v[2] | ((uint32_t)v[3] << 16);
+        pk.z = v[4] | ((uint32_t)v[5] << 16); pk.w = v[6] | ((uint32_t)v[7] << 16);
+        *reinterpret_cast<uint4*>(col + m * g.Kp + kg * 8) = pk;
     }
 }
 
@@ -113,6 +126,98 @@ __global__ void __launch_bounds__(256) k_col2im(const __nv_bfloat16* __restrict_
         } else {
             dst[0] = __float2bfloat16_rn(acc[0]);
         }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// First-layer convolution (C_in <= 4, e.g. RGB): K = KH*KW*C_in is far too small for a tensor-core tile, and
+// an im2col buffer would be 10x the size of the image.  Direct form: one thread computes 8 output channels of one
+// output pixel with the filter bank in shared memory; reads the image once (fp32 or bf16), writes y once.
+// ---------------------------------------------------------------------------------------------
+template <typename TIn>
+__global__ void __launch_bounds__(256) k_conv_small_fwd(const TIn* __restrict__ x, const __nv_bfloat16* __restrict__ w, const float* __restrict__ bias,
+                                                        __nv_bfloat16* __restrict__ y, ConvGeom g, int Cout, int64_t total) {
+    extern __shared__ float s_w[];                      // [K][Cout]
+    for (int i = threadIdx.x; i < g.K * Cout; i += 256) {
+        const int co = i / g.K, k = i - co * g.K;
+        s_w[k * Cout + co] = __bfloat162float(w[i]);
+    }
+    __syncthreads();
+    const int c8n = Cout >> 3;
+    for (int64_t t = (int64_t)blockIdx.x * 256 + threadIdx.x; t < total; t += (int64_t)gridDim.x * 256) {
+        const int c8 = (int)(t % c8n);
+        const int64_t m = t / c8n;
+        const int wo = (int)(m % g.WO), ho = (int)((m / g.WO) % g.HO), n = (int)(m / ((int64_t)g.WO * g.HO));
+        float acc[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) acc[i] = bias ? bias[c8 * 8 + i] : 0.f;
+        for (int kh = 0; kh < g.KH; ++kh) {
+            const int h = ho * g.stride - g.pad + kh;
+            if (h < 0 || h >= g.H) continue;
+            for (int kw = 0; kw < g.KW; ++kw) {
+                const int wi = wo * g.stride - g.pad + kw;
+                if (wi < 0 || wi >= g.W) continue;
+                const TIn* px = x + (((int64_t)n * g.H + h) * g.W + wi) * g.C;
+                for (int c = 0; c < g.C; ++c) {
+                    // the GEMM path rounds the input to bf16 first; do the same so both paths agree bit for bit on inputs
+                    const float xv = __bfloat162float(__float2bfloat16_rn((float)px[c]));
+                    const float* wr = s_w + ((kh * g.KW + kw) * g.C + c) * Cout + c8 * 8;
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) acc[i] = fmaf(xv, wr[i], acc[i]);
+                }
+            }
+        }
+        *reinterpret_cast<uint4*>(y + m * Cout + c8 * 8) = pack8(acc);
+    }
+}
+
+// dW[co][k] += sum_m dy[m][co] * x_patch[m][k]: thread = (co, tap group); pixels are staged in batches of 64
+template <typename TIn>
+__global__ void __launch_bounds__(256) k_conv_small_wgrad(const TIn* __restrict__ x, const __nv_bfloat16* __restrict__ dy, float* __restrict__ dw, ConvGeom g,
+                                                          int Cout, int64_t M) {
+    constexpr int PB = 64, KMAX = 36;
+    __shared__ float s_x[PB][KMAX + 1];
+    __shared__ float s_dy[PB][128];
+    const int groups = 256 / Cout;                       // Cout in {64, 128}
+    const int co = threadIdx.x % Cout, grp = threadIdx.x / Cout;
+    float acc[20];
+#pragma unroll
+    for (int i = 0; i < 20; ++i) acc[i] = 0.f;
+    const int64_t nb = (M + PB - 1) / PB;
+    for (int64_t b = blockIdx.x; b < nb; b += gridDim.x) {
+        const int64_t m0 = b * PB;
+        for (int i = threadIdx.x; i < PB * g.K; i += 256) {
+            const int p = i / g.K, k = i - p * g.K;
+            const int64_t m = m0 + p;
+            float v = 0.f;
+            if (m < M) {
+                const int c = k % g.C, tap = k / g.C;
+                const int wo = (int)(m % g.WO), ho = (int)((m / g.WO) % g.HO), n = (int)(m / ((int64_t)g.WO * g.HO));
+                const int h = ho * g.stride - g.pad + tap / g.KW, wi = wo * g.stride - g.pad + tap % g.KW;
+                if (h >= 0 && h < g.H && wi >= 0 && wi < g.W)
+                    v = __bfloat162float(__float2bfloat16_rn((float)x[(((int64_t)n * g.H + h) * g.W + wi) * g.C + c]));
+            }
+            s_x[p][k] = v;
+        }
+        for (int i = threadIdx.x; i < PB * Cout; i += 256) {
+            const int p = i / Cout, c = i - p * Cout;
+            s_dy[p][c] = (m0 + p < M) ? __bfloat162float(dy[(m0 + p) * Cout + c]) : 0.f;
+        }
+        __syncthreads();
+        for (int p = 0; p < PB; ++p) {
+            const float d = s_dy[p][co];
+#pragma unroll
+            for (int j = 0; j < 20; ++j) {
+                const int k = grp + j * groups;
+                if (k < g.K) acc[j] = fmaf(d, s_x[p][k], acc[j]);
+            }
+        }
+        __syncthreads();
+    }
+#pragma unroll
+    for (int j = 0; j < 20; ++j) {
+        const int k = grp + j * groups;
+        if (k < g.K) atomicAdd(&dw[co * g.K + k], acc[j]);
     }
 }
 
@@ -699,7 +804,7 @@ extern "C" int ewdml_im2col(const void* x, void* col, int N, int H, int W, int C
         const int64_t total = M * KH * KW * (C / 8);
         k_im2col_vec8<<<grid_for(total), 256, 0, st>>>((const __nv_bfloat16*)x, (__nv_bfloat16*)col, g, total);
     } else {
-        const int64_t total = M * g.Kp;
+        const int64_t total = M * (g.Kp / 8);
         k_im2col_scalar<<<grid_for(total), 256, 0, st>>>((const __nv_bfloat16*)x, (__nv_bfloat16*)col, g, total);
     }
     NN_LAUNCH_CHECK();
@@ -858,6 +963,36 @@ extern "C" int ewdml_f32_to_bf16_stats(const float* src, const float* bias, void
     if (rows_per < 4 * rows_par) rows_per = 4 * rows_par;
     gy = (int)((M + rows_per - 1) / rows_per);
     k_f32_to_bf16_stats<<<dim3(gx, gy), 256, 0, (cudaStream_t)stream>>>(src, bias, (__nv_bfloat16*)dst, sums, M, C, (int)rows_per);
+    NN_LAUNCH_CHECK();
+    return 0;
+}
+
+// First-layer convolution, direct form.  x: NHWC, fp32 (x_is_f32 = 1) or bf16; w: bf16 [C_out][KH*KW*C_in]; y: bf16 [N*HO*WO][C_out].
+// C_in <= 4, KH*KW*C_in <= 36, C_out a multiple of 8 and <= 256.
+extern "C" int ewdml_conv_small_fwd(const void* x, int x_is_f32, const void* w, const float* bias, void* y, int N, int H, int W, int Cin, int Cout,
+                                    int KH, int KW, int stride, int pad, void* stream) {
+    EWDML_CHECK_ARG(x && w && y && Cin >= 1 && Cin <= 4 && KH * KW * Cin <= 36 && Cout % 8 == 0 && Cout <= 256);
+    ConvGeom g = make_geom(N, H, W, Cin, KH, KW, stride, pad);
+    const int64_t total = (int64_t)N * g.HO * g.WO * (Cout / 8);
+    const size_t smem = sizeof(float) * g.K * Cout;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (x_is_f32) k_conv_small_fwd<float><<<grid_for(total), 256, smem, st>>>((const float*)x, (const __nv_bfloat16*)w, bias, (__nv_bfloat16*)y, g, Cout, total);
+    else k_conv_small_fwd<__nv_bfloat16><<<grid_for(total), 256, smem, st>>>((const __nv_bfloat16*)x, (const __nv_bfloat16*)w, bias, (__nv_bfloat16*)y, g, Cout, total);
+    NN_LAUNCH_CHECK();
+    return 0;
+}
+// dw (fp32 [C_out][KH*KW*C_in], accumulated) += dy^T patches(x).  C_out in {64, 128}.
+extern "C" int ewdml_conv_small_wgrad(const void* x, int x_is_f32, const void* dy, float* dw, int N, int H, int W, int Cin, int Cout, int KH, int KW,
+                                      int stride, int pad, void* stream) {
+    EWDML_CHECK_ARG(x && dy && dw && Cin >= 1 && Cin <= 4 && KH * KW * Cin <= 36 && (Cout == 64 || Cout == 128));
+    ConvGeom g = make_geom(N, H, W, Cin, KH, KW, stride, pad);
+    const int64_t M = (int64_t)N * g.HO * g.WO;
+    EWDML_CHECK_ARG((g.K + 256 / Cout - 1) / (256 / Cout) <= 20);
+    const int64_t nb = (M + 63) / 64;
+    const int grid = (int)(nb < 2 * 148 ? nb : 2 * 148);
+    cudaStream_t st = (cudaStream_t)stream;
+    if (x_is_f32) k_conv_small_wgrad<float><<<grid, 256, 0, st>>>((const float*)x, (const __nv_bfloat16*)dy, dw, g, Cout, M);
+    else k_conv_small_wgrad<__nv_bfloat16><<<grid, 256, 0, st>>>((const __nv_bfloat16*)x, (const __nv_bfloat16*)dy, dw, g, Cout, M);
     NN_LAUNCH_CHECK();
     return 0;
 }

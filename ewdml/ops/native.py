@@ -27,6 +27,8 @@ def _l():
             "ewdml_im2col": [vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, vp],
             "ewdml_conv3x3_igemm": [i32, vp, vp, vp, i32, i32, i32, i32, i32, i32, vp, i32, vp],
             "ewdml_pad_nhwc": [vp, vp, i32, i32, i32, i32, vp],
+            "ewdml_conv_small_fwd": [vp, i32, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, i32, vp],
+            "ewdml_conv_small_wgrad": [vp, i32, vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, i32, vp],
             "ewdml_col2im": [vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, vp],
             "ewdml_colstats": [vp, vp, i64, i32, i32, vp],
             "ewdml_bn_finalize": [vp, vp, vp, vp, vp, vp, i32, i64, f32, f32, vp],
@@ -60,6 +62,7 @@ def _p(t: Optional[torch.Tensor]):
 
 
 OUT_BF16, OUT_F32, OUT_ACCUM = 0, 1, 2
+USE_SMALL_CONV = False   # direct first-layer kernels (kept for reference; im2col + tcgen05 GEMM measured faster on B200)
 USE_IGEMM = True      # implicit-GEMM path for 3x3 / stride 1 / pad 1 convolutions with C_in, C_out % 64 == 0
 
 # device step state of the active trainer (uint32[4] tensor) -- lets dropout masks change on graph replays
@@ -167,7 +170,7 @@ def to_nhwc_bf16(x: torch.Tensor) -> torch.Tensor:
     return xn.to(BF16)
 
 
-def _weight_bf16(w: torch.nn.Parameter, rows: int, k: int) -> torch.Tensor:
+def _weight_bf16(w: torch.nn.Parameter, rows: int, k: int, pad: bool = True) -> torch.Tensor:
     """bf16 [rows, Kp] K-major weight matrix: the shadow copy kept by the fused optimizer when present."""
     sh = getattr(w, "_ewdml_bf16", None)
     if sh is None:
@@ -175,7 +178,7 @@ def _weight_bf16(w: torch.nn.Parameter, rows: int, k: int) -> torch.Tensor:
         src = src.permute(0, 2, 3, 1) if src.dim() == 4 else src
         sh = src.reshape(rows, k).to(BF16).contiguous().view(-1)
     wb = sh.view(rows, k)
-    if k % 8 == 0:
+    if k % 8 == 0 or not pad:
         return wb
     kp = _r8(k)
     out = torch.empty(rows, kp, dtype=BF16, device=w.device)
@@ -222,14 +225,27 @@ class _ConvBlockFn(torch.autograd.Function):
         HO, WO = (H + 2 * pad - kh) // stride + 1, (W + 2 * pad - kh) // stride + 1
         M, K = N * HO * WO, kh * kh * Cin
         Kp = _r8(K)
-        xn = to_nhwc_bf16(x)
+        small = (USE_SMALL_CONV and Cin <= 4 and kh * kh * Cin <= 36 and Cout in (64, 128) and not ctx.needs_input_grad[0]
+                 and x.dtype in (torch.float32, BF16))
+        if small:
+            xn = x.permute(0, 2, 3, 1).contiguous()          # NHWC view of a channels-last tensor: no copy, no cast
+        else:
+            xn = to_nhwc_bf16(x)
         direct = kh == 1 and stride == 1 and pad == 0 and Cin % 8 == 0
         igemm = USE_IGEMM and kh == 3 and stride == 1 and pad == 1 and Cin % 64 == 0 and Cout % 64 == 0
-        wb = _weight_bf16(conv.weight, Cout, K)
+        wb = _weight_bf16(conv.weight, Cout, K, pad=not small)
         bias = conv.bias.detach() if conv.bias is not None else None
         train_bn = bn is not None and bn.training
         sums = ARENA.zeros(2 * Cout, dev) if train_bn else None
-        if igemm:
+        if small:
+            igemm = direct = False
+            col = xn
+            y = torch.empty(M, Cout, dtype=BF16, device=dev)
+            L.check(lib.ewdml_conv_small_fwd(_p(xn), int(xn.dtype == torch.float32), _p(wb), _p(bias), _p(y), N, H, W, Cin, Cout,
+                                             kh, kh, stride, pad, st), "conv_small_fwd")
+            if train_bn:
+                L.check(lib.ewdml_colstats(_p(y), _p(sums), M, Cout, 1, st), "colstats")
+        elif igemm:
             # implicit GEMM: zero-bordered copy of x, every filter tap is a row-shifted TMA load of the same matrix
             col = torch.empty(N, H + 2, W + 2, Cin, dtype=BF16, device=dev)
             L.check(lib.ewdml_pad_nhwc(_p(xn), _p(col), N, H, W, Cin, st), "pad_nhwc")
@@ -241,13 +257,18 @@ class _ConvBlockFn(torch.autograd.Function):
                 col = torch.empty(M, Kp, dtype=BF16, device=dev)
                 L.check(lib.ewdml_im2col(_p(xn), _p(col), N, H, W, Cin, kh, kh, stride, pad, st), "im2col")
             m_rows, kb = M, (Kp + 63) // 64
+        if small:
+            m_rows, kb = M, 1
         tiles = ((m_rows + 127) // 128) * ((Cout + 127) // 128)
-        split = tiles <= 96 and kb >= 16
+        split = (not small) and tiles <= 96 and kb >= 16
         # few output tiles + long reduction: split-K into an fp32 accumulator, then one pass that adds the bias, rounds
         # to bf16 and gathers the BatchNorm statistics
         acc = ARENA.zeros(M * Cout, dev).view(M, Cout) if split else None
-        y = torch.empty(M, Cout, dtype=BF16, device=dev)
-        if igemm:
+        if not small:
+            y = torch.empty(M, Cout, dtype=BF16, device=dev)
+        if small:
+            pass
+        elif igemm:
             L.check(lib.ewdml_conv3x3_igemm(1, _p(col), _p(wb), _p(acc if split else y), N, H, W, Cin, Cout,
                                             OUT_ACCUM if split else OUT_BF16, None if split else _p(bias), 0, st), "igemm fprop")
         elif split:
@@ -256,7 +277,7 @@ class _ConvBlockFn(torch.autograd.Function):
             gemm(col, wb, out=y, bias=bias)
         if split:
             L.check(lib.ewdml_f32_to_bf16_stats(_p(acc), _p(bias), _p(y), _p(sums), M, Cout, st), "f32_to_bf16_stats")
-        elif train_bn:
+        elif train_bn and not small:
             L.check(lib.ewdml_colstats(_p(y), _p(sums), M, Cout, 1, st), "colstats")
         stats = None
         if bn is not None:
@@ -279,7 +300,7 @@ class _ConvBlockFn(torch.autograd.Function):
         L.check(lib.ewdml_bn_act_fwd(_p(y), _p(stats), _p(resn), _p(out), N, HO, WO, Cout, int(relu), int(pool), st), "bn_act_fwd")
         ctx.save_for_backward(col, y, stats if stats is not None else torch.empty(0, device=dev),
                               resn if resn is not None else torch.empty(0, device=dev))
-        ctx.meta = (conv, bn, relu, pool, N, H, W, Cin, HO, WO, Cout, kh, stride, pad, M, K, Kp, direct, igemm)
+        ctx.meta = (conv, bn, relu, pool, N, H, W, Cin, HO, WO, Cout, kh, stride, pad, M, K, Kp, direct, igemm, small)
         ctx.has_res = residual is not None
         return out.permute(0, 3, 1, 2)
 
@@ -288,7 +309,7 @@ class _ConvBlockFn(torch.autograd.Function):
         lib = _l()
         st = _stream()
         col, y, stats, resn = ctx.saved_tensors
-        conv, bn, relu, pool, N, H, W, Cin, HO, WO, Cout, kh, stride, pad, M, K, Kp, direct, igemm = ctx.meta
+        conv, bn, relu, pool, N, H, W, Cin, HO, WO, Cout, kh, stride, pad, M, K, Kp, direct, igemm, small = ctx.meta
         dev = dout.device
         stats = stats if stats.numel() else None
         resn = resn if resn.numel() else None
@@ -317,7 +338,10 @@ class _ConvBlockFn(torch.autograd.Function):
                 conv.bias.grad = torch.zeros_like(conv.bias)
             _colsum_into(dy, conv.bias.grad)
         dx = None
-        if igemm:
+        if small:
+            L.check(lib.ewdml_conv_small_wgrad(_p(col), int(col.dtype == torch.float32), _p(dy), _p(gw), N, H, W, Cin, Cout, kh, kh,
+                                               stride, pad, st), "conv_small_wgrad")
+        elif igemm:
             dyp = torch.empty(N, H + 2, W + 2, Cout, dtype=BF16, device=dev)
             L.check(lib.ewdml_pad_nhwc(_p(dy), _p(dyp), N, H, W, Cout, st), "pad_nhwc dy")
             L.check(lib.ewdml_conv3x3_igemm(3, _p(dyp), _p(col), _p(gw), N, H, W, Cin, Cout, OUT_ACCUM, None, 0, st), "igemm wgrad")

@@ -213,6 +213,11 @@ int ewdml_im2col(const void* x, void* col, int N, int H, int W, int C, int KH, i
  * C_in, C_out multiples of 64.  Every operand tile is a plain 2-D TMA box shifted by a per-tap row offset.           */
 int ewdml_conv3x3_igemm(int pass, const void* A, const void* B, void* C, int N, int H, int W, int Cin, int Cout,
                         int out_mode, const float* bias, int split_k, void* stream);
+/* First-layer convolution in direct form (C_in <= 4: an im2col/GEMM tile would be almost empty).  x is NHWC fp32 or bf16. */
+int ewdml_conv_small_fwd(const void* x, int x_is_f32, const void* w, const float* bias, void* y, int N, int H, int W,
+                         int Cin, int Cout, int KH, int KW, int stride, int pad, void* stream);
+int ewdml_conv_small_wgrad(const void* x, int x_is_f32, const void* dy, float* dw, int N, int H, int W, int Cin,
+                           int Cout, int KH, int KW, int stride, int pad, void* stream);
 int ewdml_pad_nhwc(const void* x, void* out, int N, int H, int W, int C, void* stream);
 int ewdml_col2im(const void* dcol, void* dx, int N, int H, int W, int C, int KH, int KW, int stride, int pad, void* stream);
 
