@@ -40,30 +40,41 @@ __device__ __forceinline__ float decode_value(uint32_t code, int cw, int val, fl
     return __fmul_rn(dq, sign ? -lvl : lvl);
 }
 
-__device__ __forceinline__ void sgd_update4(const ApplyArgs& a, size_t idx, float4 g, const bool first_step) {
-    float4 p = *reinterpret_cast<const float4*>(a.param + idx);
-    float gg[4] = {g.x, g.y, g.z, g.w};
-    float pp[4] = {p.x, p.y, p.z, p.w};
-    float mm[4] = {0.f, 0.f, 0.f, 0.f};
-    const bool use_m = a.sgd.momentum != 0.f && a.momentum != nullptr;
-    if (use_m && !first_step) {
-        float4 m = *reinterpret_cast<const float4*>(a.momentum + idx);
-        mm[0] = m.x; mm[1] = m.y; mm[2] = m.z; mm[3] = m.w;
-    }
+// Momentum-SGD coefficients resolved once per kernel so the per-element update is branch-free:
+//   d   = g + wd * p
+//   buf = cm * m + cd * d          (first step: cm = 0, cd = 1  ->  buf = d, optim/sgd.py:79-82)
+//   d2  = cn1 * d + cn2 * buf      (nesterov: d + mu * buf; plain: buf; no momentum: d)
+//   p  -= lr * d2
+struct SgdCoef {
+    float wd, cm, cd, cn1, cn2, lr;
+    bool use_m;
+};
+__device__ __forceinline__ SgdCoef make_coef(const ApplyArgs& a, bool first_step) {
+    SgdCoef c;
+    c.use_m = a.sgd.momentum != 0.f && a.momentum != nullptr;
+    c.wd = a.sgd.weight_decay;
+    c.cm = first_step ? 0.f : a.sgd.momentum;
+    c.cd = first_step ? 1.f : 1.f - a.sgd.dampening;
+    c.cn1 = c.use_m ? (a.sgd.nesterov ? 1.f : 0.f) : 1.f;
+    c.cn2 = c.use_m ? (a.sgd.nesterov ? a.sgd.momentum : 1.f) : 0.f;
+    c.lr = a.sgd.lr;
+    return c;
+}
+__device__ __forceinline__ void sgd_update4(const ApplyArgs& a, const SgdCoef& c, size_t idx, float4 g) {
+    const float4 p = *reinterpret_cast<const float4*>(a.param + idx);
+    float4 m = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (c.use_m && c.cm != 0.f) m = *reinterpret_cast<const float4*>(a.momentum + idx);
+    float gg[4] = {g.x, g.y, g.z, g.w}, pp[4] = {p.x, p.y, p.z, p.w}, mm[4] = {m.x, m.y, m.z, m.w};
 #pragma unroll
     for (int q = 0; q < 4; ++q) {
-        float d = gg[q];
-        if (a.sgd.weight_decay != 0.f) d = __fmaf_rn(a.sgd.weight_decay, pp[q], d);
-        if (use_m) {
-            float buf = first_step ? d : __fadd_rn(__fmul_rn(a.sgd.momentum, mm[q]),
-                                                         __fmul_rn(1.f - a.sgd.dampening, d));
-            mm[q] = buf;
-            d = a.sgd.nesterov ? __fmaf_rn(a.sgd.momentum, buf, d) : buf;
-        }
-        pp[q] = __fsub_rn(pp[q], __fmul_rn(a.sgd.lr, d));
+        const float d = fmaf(c.wd, pp[q], gg[q]);
+        const float buf = fmaf(c.cd, d, c.cm * mm[q]);
+        mm[q] = buf;
+        const float d2 = fmaf(c.cn2, buf, c.cn1 * d);
+        pp[q] = fmaf(-c.lr, d2, pp[q]);
     }
     *reinterpret_cast<float4*>(a.param + idx) = make_float4(pp[0], pp[1], pp[2], pp[3]);
-    if (use_m) *reinterpret_cast<float4*>(a.momentum + idx) = make_float4(mm[0], mm[1], mm[2], mm[3]);
+    if (c.use_m) *reinterpret_cast<float4*>(a.momentum + idx) = make_float4(mm[0], mm[1], mm[2], mm[3]);
     if (a.param_bf16) {
         __nv_bfloat162 lo = __floats2bfloat162_rn(pp[0], pp[1]), hi = __floats2bfloat162_rn(pp[2], pp[3]);
         uint2 pk;
@@ -89,7 +100,11 @@ __global__ void __launch_bounds__(256) k_recv_apply(const ApplyArgs a) {
     __syncthreads();
     if (!s_ok) return;
     const float inv_scale = a.divisor;
+    // a power-of-two contributor count (1, 2, 4, 8 GPUs) divides exactly by multiplying with its reciprocal
+    const bool pow2 = (__float_as_uint(inv_scale) & 0x007FFFFFu) == 0u;
+    const float rcp = __fdiv_rn(1.f, inv_scale);
     const bool first_step = a.state ? (a.state[2] != 0) : (a.sgd.first_step != 0);
+    const SgdCoef coef = make_coef(a, first_step);
     for (int t = blockIdx.x; t < a.ntiles; t += gridDim.x) {
         const TileDesc td = a.tiles[t];
         const uint32_t n4 = (td.len + 3) >> 2;
@@ -111,18 +126,18 @@ __global__ void __launch_bounds__(256) k_recv_apply(const ApplyArgs a) {
                         const uint32_t code = get_bits(codes, j * a.code_bits, a.code_bits);
                         if (e < td.len) acc[e] += decode_value(code, a.code_bits, a.val, dq);   // e unique per source
                     }
-                } else {  // BITMAP: thread w owns bitmap word w = elements [32w, 32w+32)
+                } else {  // BITMAP (thread-major, see encode.cu): word t, bit 4j+q  <->  element (t + 256 j) * 4 + q
                     const uint32_t word = reinterpret_cast<const uint32_t*>(slot + a.layout.bitmap)[(size_t)t * 256 + tid];
                     uint32_t total;
                     uint32_t pos = block_excl_scan(__popc(word), scan_smem, &total);
                     const uint32_t* codes = reinterpret_cast<const uint32_t*>(chunk);
                     uint32_t m = word;
                     while (m) {
-                        const int j = __ffs(m) - 1;
+                        const int b = __ffs(m) - 1;
                         m &= m - 1;
                         if (pos < cnt) {
                             const uint32_t code = get_bits(codes, pos * a.code_bits, a.code_bits);
-                            acc[tid * 32 + j] += decode_value(code, a.code_bits, a.val, dq);
+                            acc[((tid + 256 * (b >> 2)) << 2) + (b & 3)] += decode_value(code, a.code_bits, a.val, dq);
                         }
                         ++pos;
                     }
@@ -143,11 +158,15 @@ __global__ void __launch_bounds__(256) k_recv_apply(const ApplyArgs a) {
             } else {
                 g = reinterpret_cast<const float4*>(acc)[i];
             }
-            g.x = __fdiv_rn(g.x, inv_scale); g.y = __fdiv_rn(g.y, inv_scale);
-            g.z = __fdiv_rn(g.z, inv_scale); g.w = __fdiv_rn(g.w, inv_scale);
+            if (pow2) {
+                g.x *= rcp; g.y *= rcp; g.z *= rcp; g.w *= rcp;
+            } else {
+                g.x = __fdiv_rn(g.x, inv_scale); g.y = __fdiv_rn(g.y, inv_scale);
+                g.z = __fdiv_rn(g.z, inv_scale); g.w = __fdiv_rn(g.w, inv_scale);
+            }
             const size_t idx = (size_t)td.start + i * 4;
             if (a.out_mode == EWDML_OUT_SGD) {
-                sgd_update4(a, idx, g, first_step);
+                sgd_update4(a, coef, idx, g);
             } else if (a.out_mode == EWDML_OUT_GRAD) {
                 *reinterpret_cast<float4*>(a.out + idx) = g;
             } else {  // ASSIGN: weights pulled from the server
@@ -167,10 +186,11 @@ __global__ void __launch_bounds__(256) k_recv_apply(const ApplyArgs a) {
 
 // Local fused SGD (no exchange): optim/sgd.py:59-92 over the flat buffers.
 __global__ void __launch_bounds__(256) k_sgd_apply(const float* __restrict__ grad, ApplyArgs a, int64_t n4, float gscale) {
+    const SgdCoef coef = make_coef(a, a.state ? (a.state[2] != 0) : (a.sgd.first_step != 0));
     for (int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x; i < n4; i += (int64_t)gridDim.x * 256) {
         float4 g = *reinterpret_cast<const float4*>(grad + i * 4);
         g.x *= gscale; g.y *= gscale; g.z *= gscale; g.w *= gscale;
-        sgd_update4(a, (size_t)i * 4, g, a.state ? (a.state[2] != 0) : (a.sgd.first_step != 0));
+        sgd_update4(a, coef, (size_t)i * 4, g);
     }
 }
 

@@ -1,8 +1,9 @@
 // K1: fused select + QSGD quantise + bit-pack + peer store ("sparse allgather send").
 //
-// One CTA per 8192-element tile (full read #2 of the gradient).  The tile is staged in shared
-// memory so that thread t owns elements [32t, 32t+32): its selection mask IS bitmap word t, a block
-// scan of the popcounts gives ordered output positions, and the tile's chunk
+// One CTA per 8192-element tile (full read #2 of the gradient).  Each thread keeps its 32 elements in
+// registers (eight coalesced 16-byte loads); warp ballots turn the per-element selection into the
+// tile's bitmap in a bit-sliced order, a block scan of the word popcounts gives ordered output
+// positions, and the tile's chunk
 //     [u16 local index x cnt]  (IDX16 mode only)   [bit-packed codes x cnt]
 // is assembled in shared memory, given a byte range of the payload by ONE atomicAdd, and written
 // with 16-byte stores straight into the receive slot of every destination over NVLink (or local
@@ -38,13 +39,14 @@ __device__ __forceinline__ void put_bits(uint32_t* words, uint32_t bitpos, uint3
     if (sh + nbits > 32) atomicOr(&words[w + 1], code >> (32 - sh));
 }
 
-template <int MODE>
+template <int MODE, int SEL, int VAL>
 __global__ void __launch_bounds__(256) k_encode_push(const EncodeArgs a) {
     extern __shared__ __align__(16) uint32_t smem[];
-    // layout: tile values/codes [8448 words] | idx16 staging [4096 words] | code staging [cw*256 words (+4)]
-    uint32_t* s_tile = smem;
-    uint16_t* s_idx = reinterpret_cast<uint16_t*>(smem + 8448);
-    uint32_t* s_code = smem + 8448 + 4096;
+    // layout: bitmap [256 words] | offsets [256 words] | idx16 staging [4096 words] | code staging [cw*256 words (+4)]
+    uint32_t* s_bitmap = smem;
+    uint32_t* s_offs = smem + 256;
+    uint16_t* s_idx = reinterpret_cast<uint16_t*>(smem + 512);
+    uint32_t* s_code = smem + 512 + 4096;
     __shared__ uint32_t scan_smem[40];
     __shared__ uint32_t s_off, s_last;
 
@@ -64,82 +66,98 @@ __global__ void __launch_bounds__(256) k_encode_push(const EncodeArgs a) {
                 st_na_v4(dst + (size_t)i * 16, *reinterpret_cast<const uint4*>(src + i * 4));
         }
     } else {
+        // Thread t holds elements (t + 256 j) * 4 + q, j = 0..7, q = 0..3 (eight coalesced 16-byte loads) and builds its own
+        // 32-bit selection word (bit 4j+q).  Word t IS the tile's bitmap word t (a thread-major bit order that needs no
+        // data movement); entries are ordered by (thread, bit), positions come from a block scan of the popcounts.
         const SegInfo si = a.info[td.seg];
         const int cw = a.code_bits;
-        const int code_words = (cw * 256 + 3);           // <= cw*8192/32 words, +padding for 16 B copies
-        // ---- stage the tile ------------------------------------------------------------------
+        const int code_words = (cw * 256 + 3);
         const float* src = a.grad + td.start;
+        uint32_t v[8][4];
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
-            uint32_t e = (tid + 256 * j) * 4;
-            if (e < td.len) {
-                float4 v = *reinterpret_cast<const float4*>(src + e);
-                s_tile[PAD(e)] = __float_as_uint(v.x);
-                s_tile[PAD(e + 1)] = __float_as_uint(v.y);
-                s_tile[PAD(e + 2)] = __float_as_uint(v.z);
-                s_tile[PAD(e + 3)] = __float_as_uint(v.w);
-            }
+            const uint32_t e = (tid + 256 * j) * 4;
+            uint4 u = make_uint4(0, 0, 0, 0);
+            if (e < td.len) u = *reinterpret_cast<const uint4*>(src + e);
+            v[j][0] = u.x; v[j][1] = u.y; v[j][2] = u.z; v[j][3] = u.w;
         }
         for (int i = tid; i < code_words; i += 256) s_code[i] = 0;
-        __syncthreads();
-        // ---- select + quantise: thread owns elements [32 tid, 32 tid + 32) --------------------
+        // ---- selection word: branch-free compares, ties handled afterwards (they are rare) ----
         uint32_t mask = 0;
-        const uint32_t e0 = tid * 32;
-        const float levels_f = (float)a.levels;
-        uint32_t cached_group = 0xFFFFFFFFu;
-        Philox4 rnd;
-        rnd.v[0] = rnd.v[1] = rnd.v[2] = rnd.v[3] = 0;
-        if (e0 < td.len) {
-#pragma unroll 4
-            for (int j = 0; j < 32; ++j) {
-                const uint32_t e = e0 + j;
-                if (e >= td.len) break;
-                const uint32_t bits = s_tile[PAD(e)];
-                const uint32_t key = bits & 0x7FFFFFFFu;
-                bool sel = true;
-                if (a.sel == EWDML_SEL_TOPK) {
-                    sel = key > si.thr_key;
-                    if (!sel && key == si.thr_key && si.need_eq)
-                        sel = atomicAdd(&a.info[td.seg].eq_taken, 1u) < si.need_eq;
+        if (SEL == EWDML_SEL_TOPK) {
+            uint32_t meq = 0;
+#pragma unroll
+            for (int j = 0; j < 8; ++j)
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    const uint32_t key = v[j][q] & 0x7FFFFFFFu;
+                    mask |= (key > si.thr_key ? 1u : 0u) << (4 * j + q);
+                    meq |= (key == si.thr_key ? 1u : 0u) << (4 * j + q);
                 }
-                uint32_t code = bits;                       // RAW32: the fp32 bit pattern
-                if (sel && a.val == EWDML_VAL_QSGD) {
-                    const uint32_t gidx = td.start + e;     // global element index -> RNG counter
-                    const uint32_t group = gidx >> 2;
-                    if (group != cached_group) {
-                        rnd = philox4x32_10(group, a.rng_stream, 0u, 0u, a.seed_lo, step);
-                        cached_group = group;
+            if (td.len != EWDML_TILE) {                              // partial tile: drop the out-of-range lanes
+#pragma unroll
+                for (int j = 0; j < 8; ++j)
+#pragma unroll
+                    for (int q = 0; q < 4; ++q)
+                        if ((tid + 256 * j) * 4 + q >= td.len) { mask &= ~(1u << (4 * j + q)); meq &= ~(1u << (4 * j + q)); }
+            }
+            if (meq && si.need_eq) {                                 // exact ties with the threshold: take tickets
+                uint32_t m = meq;
+                while (m) {
+                    const int b = __ffs(m) - 1;
+                    m &= m - 1;
+                    if (atomicAdd(&a.info[td.seg].eq_taken, 1u) < si.need_eq) mask |= 1u << b;
+                }
+            }
+        } else {
+#pragma unroll
+            for (int j = 0; j < 8; ++j)
+#pragma unroll
+                for (int q = 0; q < 4; ++q)
+                    if ((tid + 256 * j) * 4 + q < td.len) mask |= 1u << (4 * j + q);
+        }
+        // ---- QSGD: stochastic level for the selected elements; level 0 is dropped from the selection ----
+        if (VAL == EWDML_VAL_QSGD && mask) {
+            const float levels_f = (float)a.levels;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                if ((mask >> (4 * j)) & 0xFu) {
+                    const uint32_t gidx0 = td.start + (tid + 256 * j) * 4;       // multiple of 4: one Philox block per float4
+                    const Philox4 rnd = philox4x32_10(gidx0 >> 2, a.rng_stream, 0u, 0u, a.seed_lo, step);
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) {
+                        if (mask & (1u << (4 * j + q))) {
+                            const uint32_t bits = v[j][q];
+                            const float u = philox_to_uniform(rnd.v[q]);
+                            const float lf = __fmul_rn(si.scale, __uint_as_float(bits & 0x7FFFFFFFu));
+                            const float prev = floorf(lf);
+                            float lvl = prev + ((u < __fsub_rn(lf, prev)) ? 1.f : 0.f);
+                            lvl = fminf(lvl, levels_f);
+                            if (lvl >= 1.f) v[j][q] = ((bits >> 31) << (cw - 1)) | ((uint32_t)lvl - 1u);
+                            else mask &= ~(1u << (4 * j + q));
+                        }
                     }
-                    const uint32_t ln = gidx & 3;
-                    const uint32_t rx = ln == 0 ? rnd.v[0] : (ln == 1 ? rnd.v[1] : (ln == 2 ? rnd.v[2] : rnd.v[3]));
-                    const float u = philox_to_uniform(rx);
-                    const float lf = __fmul_rn(si.scale, __uint_as_float(key));
-                    const float prev = floorf(lf);
-                    float lvl = prev + ((u < __fsub_rn(lf, prev)) ? 1.f : 0.f);
-                    lvl = fminf(lvl, levels_f);
-                    sel = lvl >= 1.f;                        // level 0 carries no information
-                    code = ((bits >> 31) << (cw - 1)) | ((uint32_t)lvl - 1u);
-                }
-                if (sel) {
-                    mask |= 1u << j;
-                    s_tile[PAD(e)] = code;                  // keep the code in place of the value
                 }
             }
         }
-        const uint32_t cnt = __popc(mask);
+        s_bitmap[tid] = mask;
         uint32_t total;
-        const uint32_t pos0 = block_excl_scan(cnt, scan_smem, &total);
-        // ---- assemble the chunk in shared memory --------------------------------------------
-        {
-            uint32_t m = mask, p = pos0;
-            while (m) {
-                const int j = __ffs(m) - 1;
-                m &= m - 1;
-                const uint32_t code = s_tile[PAD(e0 + j)];
-                if (MODE == EWDML_MODE_IDX16) s_idx[p] = (uint16_t)(e0 + j);
-                if (cw == 32) s_code[p] = code;
-                else put_bits(s_code, p * cw, code, cw);
-                ++p;
+        const uint32_t pos0 = block_excl_scan(__popc(mask), scan_smem, &total);
+        const uint32_t myword = mask;
+        // ---- assemble the chunk in shared memory (only threads that own selected elements do work) ----
+        if (mask) {
+            uint32_t p = pos0;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    if (mask & (1u << (4 * j + q))) {
+                        if (MODE == EWDML_MODE_IDX16) s_idx[p] = (uint16_t)((tid + 256 * j) * 4 + q);
+                        if (cw == 32) s_code[p] = v[j][q];
+                        else put_bits(s_code, p * cw, v[j][q], cw);
+                        ++p;
+                    }
+                }
             }
         }
         const uint32_t idx_bytes = MODE == EWDML_MODE_IDX16 ? align16(total * 2) : 0;
@@ -164,7 +182,7 @@ __global__ void __launch_bounds__(256) k_encode_push(const EncodeArgs a) {
                 *reinterpret_cast<uint2*>(slot + a.layout.dir + (size_t)blockIdx.x * 8) = de;
             }
             if (MODE == EWDML_MODE_BITMAP)
-                reinterpret_cast<uint32_t*>(slot + a.layout.bitmap)[(size_t)blockIdx.x * 256 + tid] = mask;
+                reinterpret_cast<uint32_t*>(slot + a.layout.bitmap)[(size_t)blockIdx.x * 256 + tid] = myword;
             if (!overflow) {
                 char* dst = slot + a.layout.data + off;
                 const uint4* si4 = reinterpret_cast<const uint4*>(s_idx);
@@ -178,7 +196,9 @@ __global__ void __launch_bounds__(256) k_encode_push(const EncodeArgs a) {
     // ---- completion: last CTA publishes header, norms and flags ------------------------------
     __syncthreads();
     if (tid == 0) {
-        __threadfence_system();
+        // device-scope fence is enough here: this CTA's stores are ordered before its counter increment, the last CTA
+        // observes every increment and issues the system-scope fence + release before any peer can see the flag
+        __threadfence();
         s_last = atomicAdd(&a.ctr->ctas_done, 1u) == (uint32_t)(a.ntiles - 1);
     }
     __syncthreads();
@@ -221,7 +241,7 @@ int ewdml_launch_select(ewdml_plan* p, const float* grad, cudaStream_t st);
 
 static size_t encode_smem_bytes(const ewdml_codec& c) {
     if (c.mode == EWDML_MODE_DENSE) return 0;
-    return (size_t)(8448 + 4096 + c.code_bits * 256 + 4) * 4;
+    return (size_t)(512 + 4096 + c.code_bits * 256 + 4) * 4;
 }
 
 static int send_impl(ewdml_plan* p, const float* grad, const ewdml_dests* dests, const ewdml_dests* dests_odd,
@@ -242,28 +262,27 @@ static int send_impl(ewdml_plan* p, const float* grad, const ewdml_dests* dests,
     a.err_word = ewdml_device_error_word();
     if (!a.err_word) return EWDML_ERR_CUDA;
     const size_t smem = encode_smem_bytes(p->codec);
-    static bool attr_set[3] = {false, false, false};
-    switch (p->codec.mode) {
-        case EWDML_MODE_DENSE:
-            k_encode_push<EWDML_MODE_DENSE><<<p->ntiles, 256, 0, st>>>(a);
-            break;
-        case EWDML_MODE_IDX16:
-            if (!attr_set[1]) {
-                EWDML_CUDA(cudaFuncSetAttribute(k_encode_push<EWDML_MODE_IDX16>,
-                                                cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
-                attr_set[1] = true;
-            }
-            k_encode_push<EWDML_MODE_IDX16><<<p->ntiles, 256, smem, st>>>(a);
-            break;
-        default:
-            if (!attr_set[2]) {
-                EWDML_CUDA(cudaFuncSetAttribute(k_encode_push<EWDML_MODE_BITMAP>,
-                                                cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
-                attr_set[2] = true;
-            }
-            k_encode_push<EWDML_MODE_BITMAP><<<p->ntiles, 256, smem, st>>>(a);
-            break;
+#define ENC_LAUNCH(MODE_, SEL_, VAL_)                                                                                   \
+    do {                                                                                                              \
+        EWDML_CUDA(cudaFuncSetAttribute(k_encode_push<MODE_, SEL_, VAL_>, cudaFuncAttributeMaxDynamicSharedMemorySize,  \
+                                        100 * 1024));                                                                 \
+        k_encode_push<MODE_, SEL_, VAL_><<<p->ntiles, 256, smem, st>>>(a);                                            \
+    } while (0)
+    const int sel = p->codec.sel, val = p->codec.val;
+    if (p->codec.mode == EWDML_MODE_DENSE) {
+        k_encode_push<EWDML_MODE_DENSE, 0, 0><<<p->ntiles, 256, 0, st>>>(a);
+    } else if (p->codec.mode == EWDML_MODE_IDX16) {
+        if (sel == EWDML_SEL_TOPK && val == EWDML_VAL_QSGD) ENC_LAUNCH(EWDML_MODE_IDX16, EWDML_SEL_TOPK, EWDML_VAL_QSGD);
+        else if (sel == EWDML_SEL_TOPK) ENC_LAUNCH(EWDML_MODE_IDX16, EWDML_SEL_TOPK, EWDML_VAL_RAW32);
+        else if (val == EWDML_VAL_QSGD) ENC_LAUNCH(EWDML_MODE_IDX16, EWDML_SEL_ALL, EWDML_VAL_QSGD);
+        else ENC_LAUNCH(EWDML_MODE_IDX16, EWDML_SEL_ALL, EWDML_VAL_RAW32);
+    } else {
+        if (sel == EWDML_SEL_TOPK && val == EWDML_VAL_QSGD) ENC_LAUNCH(EWDML_MODE_BITMAP, EWDML_SEL_TOPK, EWDML_VAL_QSGD);
+        else if (sel == EWDML_SEL_TOPK) ENC_LAUNCH(EWDML_MODE_BITMAP, EWDML_SEL_TOPK, EWDML_VAL_RAW32);
+        else if (val == EWDML_VAL_QSGD) ENC_LAUNCH(EWDML_MODE_BITMAP, EWDML_SEL_ALL, EWDML_VAL_QSGD);
+        else ENC_LAUNCH(EWDML_MODE_BITMAP, EWDML_SEL_ALL, EWDML_VAL_RAW32);
     }
+#undef ENC_LAUNCH
     EWDML_LAUNCH_CHECK();
     ewdml_counter_add(EWDML_CTR_SEND_CALLS, 1);
     return 0;
