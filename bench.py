@@ -45,7 +45,7 @@ def parse():
     p.add_argument("--topk-ratio", type=float, default=0.01)
     p.add_argument("--qsgd-levels", type=int, default=128)
     p.add_argument("--exchange", type=str, default="allgather", choices=["allgather", "allreduce", "ps"])
-    p.add_argument("--compute", type=str, default=os.environ.get("EWDML_BENCH_COMPUTE", "torch"),
+    p.add_argument("--compute", type=str, default=os.environ.get("EWDML_BENCH_COMPUTE", "native"),
                    choices=["torch", "native"])
     p.add_argument("--dtype", type=str, default="bf16")
     p.add_argument("--no-e2e", action="store_true")

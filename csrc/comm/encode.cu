@@ -40,7 +40,7 @@ __device__ __forceinline__ void put_bits(uint32_t* words, uint32_t bitpos, uint3
 }
 
 template <int MODE, int SEL, int VAL>
-__global__ void __launch_bounds__(256) k_encode_push(const EncodeArgs a) {
+__global__ void __launch_bounds__(256, 2) k_encode_push(const EncodeArgs a) {
     extern __shared__ __align__(16) uint32_t smem[];
     // layout: bitmap [256 words] | offsets [256 words] | idx16 staging [4096 words] | code staging [cw*256 words (+4)]
     uint32_t* s_bitmap = smem;
@@ -50,7 +50,8 @@ __global__ void __launch_bounds__(256) k_encode_push(const EncodeArgs a) {
     __shared__ uint32_t scan_smem[40];
     __shared__ uint32_t s_off, s_last;
 
-    const TileDesc td = a.tiles[blockIdx.x];
+    int tile = blockIdx.x;
+    TileDesc td = a.tiles[tile];
     const int tid = threadIdx.x;
     const uint32_t seq = a.state ? a.state[0] : a.seq;
     const uint32_t step = a.state ? a.state[1] : a.step;
@@ -69,120 +70,190 @@ __global__ void __launch_bounds__(256) k_encode_push(const EncodeArgs a) {
         // Thread t holds elements (t + 256 j) * 4 + q, j = 0..7, q = 0..3 (eight coalesced 16-byte loads) and builds its own
         // 32-bit selection word (bit 4j+q).  Word t IS the tile's bitmap word t (a thread-major bit order that needs no
         // data movement); entries are ordered by (thread, bit), positions come from a block scan of the popcounts.
-        const SegInfo si = a.info[td.seg];
         const int cw = a.code_bits;
         const int code_words = (cw * 256 + 3);
-        const float* src = a.grad + td.start;
         uint32_t v[8][4];
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
             const uint32_t e = (tid + 256 * j) * 4;
             uint4 u = make_uint4(0, 0, 0, 0);
-            if (e < td.len) u = *reinterpret_cast<const uint4*>(src + e);
+            if (e < td.len) u = *reinterpret_cast<const uint4*>(a.grad + td.start + e);
             v[j][0] = u.x; v[j][1] = u.y; v[j][2] = u.z; v[j][3] = u.w;
         }
+        // persistent loop: the next tile's loads are issued before this tile is processed
+        uint32_t my_entries = 0;
+        unsigned long long my_bytes = 0;
+        while (true) {
+        const int next = tile + gridDim.x;
+        TileDesc ntd = td;
+        uint4 nv[8];
+        if (next < a.ntiles) {
+            ntd = a.tiles[next];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                const uint32_t e = (tid + 256 * j) * 4;
+                nv[j] = e < ntd.len ? *reinterpret_cast<const uint4*>(a.grad + ntd.start + e) : make_uint4(0, 0, 0, 0);
+            }
+        }
+        const SegInfo si = a.info[td.seg];
         for (int i = tid; i < code_words; i += 256) s_code[i] = 0;
         // ---- selection word: branch-free compares, ties handled afterwards (they are rare) ----
         uint32_t mask = 0;
         if (SEL == EWDML_SEL_TOPK) {
-            uint32_t meq = 0;
-#pragma unroll
-            for (int j = 0; j < 8; ++j)
-#pragma unroll
-                for (int q = 0; q < 4; ++q) {
-                    const uint32_t key = v[j][q] & 0x7FFFFFFFu;
-                    mask |= (key > si.thr_key ? 1u : 0u) << (4 * j + q);
-                    meq |= (key == si.thr_key ? 1u : 0u) << (4 * j + q);
-                }
-            if (td.len != EWDML_TILE) {                              // partial tile: drop the out-of-range lanes
-#pragma unroll
-                for (int j = 0; j < 8; ++j)
-#pragma unroll
-                    for (int q = 0; q < 4; ++q)
-                        if ((tid + 256 * j) * 4 + q >= td.len) { mask &= ~(1u << (4 * j + q)); meq &= ~(1u << (4 * j + q)); }
-            }
-            if (meq && si.need_eq) {                                 // exact ties with the threshold: take tickets
-                uint32_t m = meq;
-                while (m) {
-                    const int b = __ffs(m) - 1;
-                    m &= m - 1;
-                    if (atomicAdd(&a.info[td.seg].eq_taken, 1u) < si.need_eq) mask |= 1u << b;
-                }
-            }
-        } else {
+            // selected <=> key > thr, evaluated as the sign of (thr - key) and shifted into the word from the top: four
+            // integer instructions per element.  thr = 0xFFFFFFFF (-1) selects everything.
+            const uint32_t thr = si.thr_key;
 #pragma unroll
             for (int j = 0; j < 8; ++j)
 #pragma unroll
                 for (int q = 0; q < 4; ++q)
-                    if ((tid + 256 * j) * 4 + q < td.len) mask |= 1u << (4 * j + q);
+                    mask = (mask >> 1) | ((thr - (v[j][q] & 0x7FFFFFFFu)) & 0x80000000u);
+            uint32_t valid = 0xFFFFFFFFu;
+            if (td.len != EWDML_TILE) {                              // partial tile: drop the out-of-range lanes
+                valid = 0;
+#pragma unroll
+                for (int j = 0; j < 8; ++j)
+#pragma unroll
+                    for (int q = 0; q < 4; ++q)
+                        if ((tid + 256 * j) * 4 + q < td.len) valid |= 1u << (4 * j + q);
+                mask &= valid;
+            }
+            if (si.need_eq) {                                        // genuine tie at the threshold (rare): take tickets
+                uint32_t meq = 0;
+#pragma unroll
+                for (int j = 0; j < 8; ++j)
+#pragma unroll
+                    for (int q = 0; q < 4; ++q)
+                        meq |= ((v[j][q] & 0x7FFFFFFFu) == thr ? 1u : 0u) << (4 * j + q);
+                meq &= valid;
+                while (meq) {
+                    const int b = __ffs(meq) - 1;
+                    meq &= meq - 1;
+                    if (atomicAdd(&a.info[td.seg].eq_taken, 1u) < si.need_eq) mask |= 1u << b;
+                }
+            }
+        } else {
+            mask = 0xFFFFFFFFu;
+            if (td.len != EWDML_TILE) {
+                mask = 0;
+#pragma unroll
+                for (int j = 0; j < 8; ++j)
+#pragma unroll
+                    for (int q = 0; q < 4; ++q)
+                        if ((tid + 256 * j) * 4 + q < td.len) mask |= 1u << (4 * j + q);
+            }
         }
-        // ---- QSGD: stochastic level for the selected elements; level 0 is dropped from the selection ----
-        if (VAL == EWDML_VAL_QSGD && mask) {
+        uint32_t total;
+        uint32_t myword = mask;
+        if constexpr (MODE == EWDML_MODE_IDX16 && SEL == EWDML_SEL_TOPK) {
+            // Sparse path (density <= 1/16): selected elements are rare, so do not drag 32 predicated code blocks through
+            // every warp.  Stage 1: each selected element is re-read from global memory (an L2 hit) and appended to a
+            // shared list.  Stage 2: the list is processed densely, one entry per thread: QSGD level, drop level 0,
+            // append (index, code) to the chunk.  Entry order inside a chunk is arbitrary -- the receiver does not care.
+            uint32_t* s_cnt = s_bitmap;                               // [0]: list length, [1]: chunk entries
+            uint16_t* s_le = reinterpret_cast<uint16_t*>(s_code + code_words + 1);
+            uint32_t* s_lv = reinterpret_cast<uint32_t*>(s_le + EWDML_TILE);
+            if (tid < 2) s_cnt[tid] = 0;
+            __syncthreads();
+            uint32_t m = mask;
+            while (m) {
+                const int b = __ffs(m) - 1;
+                m &= m - 1;
+                const uint32_t e = ((tid + 256 * (b >> 2)) << 2) + (b & 3);
+                const uint32_t bits = __float_as_uint(a.grad[td.start + e]);
+                const uint32_t slot = atomicAdd(&s_cnt[0], 1u);
+                s_le[slot] = (uint16_t)e;
+                s_lv[slot] = bits;
+            }
+            __syncthreads();
+            const uint32_t n1 = s_cnt[0];
             const float levels_f = (float)a.levels;
-#pragma unroll
-            for (int j = 0; j < 8; ++j) {
-                if ((mask >> (4 * j)) & 0xFu) {
-                    const uint32_t gidx0 = td.start + (tid + 256 * j) * 4;       // multiple of 4: one Philox block per float4
-                    const Philox4 rnd = philox4x32_10(gidx0 >> 2, a.rng_stream, 0u, 0u, a.seed_lo, step);
-#pragma unroll
-                    for (int q = 0; q < 4; ++q) {
-                        if (mask & (1u << (4 * j + q))) {
-                            const uint32_t bits = v[j][q];
-                            const float u = philox_to_uniform(rnd.v[q]);
-                            const float lf = __fmul_rn(si.scale, __uint_as_float(bits & 0x7FFFFFFFu));
-                            const float prev = floorf(lf);
-                            float lvl = prev + ((u < __fsub_rn(lf, prev)) ? 1.f : 0.f);
-                            lvl = fminf(lvl, levels_f);
-                            if (lvl >= 1.f) v[j][q] = ((bits >> 31) << (cw - 1)) | ((uint32_t)lvl - 1u);
-                            else mask &= ~(1u << (4 * j + q));
+            for (uint32_t i = tid; i < n1; i += 256) {
+                const uint32_t e = s_le[i], bits = s_lv[i];
+                uint32_t code = bits;
+                bool keep = true;
+                if (VAL == EWDML_VAL_QSGD) {
+                    const uint32_t gidx = td.start + e;
+                    const Philox4 rnd = philox4x32_10(gidx >> 2, a.rng_stream, 0u, 0u, a.seed_lo, step);
+                    const uint32_t ln = gidx & 3;
+                    const uint32_t rx = ln == 0 ? rnd.v[0] : (ln == 1 ? rnd.v[1] : (ln == 2 ? rnd.v[2] : rnd.v[3]));
+                    const float u = philox_to_uniform(rx);
+                    const float lf = __fmul_rn(si.scale, __uint_as_float(bits & 0x7FFFFFFFu));
+                    const float prev = floorf(lf);
+                    float lvl = prev + ((u < __fsub_rn(lf, prev)) ? 1.f : 0.f);
+                    lvl = fminf(lvl, levels_f);
+                    keep = lvl >= 1.f;                                // level 0 carries no information
+                    code = ((bits >> 31) << (cw - 1)) | ((uint32_t)lvl - 1u);
+                }
+                if (keep) {
+                    const uint32_t p = atomicAdd(&s_cnt[1], 1u);
+                    s_idx[p] = (uint16_t)e;
+                    if (cw == 32) s_code[p] = code;
+                    else put_bits(s_code, p * cw, code, cw);
+                }
+            }
+            __syncthreads();
+            total = s_cnt[1];
+        } else {
+            // ---- QSGD: stochastic level for the selected elements; level 0 is dropped from the selection ----
+            if (VAL == EWDML_VAL_QSGD && mask) {
+                const float levels_f = (float)a.levels;
+    #pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    if ((mask >> (4 * j)) & 0xFu) {
+                        const uint32_t gidx0 = td.start + (tid + 256 * j) * 4;       // multiple of 4: one Philox block per float4
+                        const Philox4 rnd = philox4x32_10(gidx0 >> 2, a.rng_stream, 0u, 0u, a.seed_lo, step);
+    #pragma unroll
+                        for (int q = 0; q < 4; ++q) {
+                            if (mask & (1u << (4 * j + q))) {
+                                const uint32_t bits = v[j][q];
+                                const float u = philox_to_uniform(rnd.v[q]);
+                                const float lf = __fmul_rn(si.scale, __uint_as_float(bits & 0x7FFFFFFFu));
+                                const float prev = floorf(lf);
+                                float lvl = prev + ((u < __fsub_rn(lf, prev)) ? 1.f : 0.f);
+                                lvl = fminf(lvl, levels_f);
+                                if (lvl >= 1.f) v[j][q] = ((bits >> 31) << (cw - 1)) | ((uint32_t)lvl - 1u);
+                                else mask &= ~(1u << (4 * j + q));
+                            }
                         }
                     }
                 }
             }
-        }
-        s_bitmap[tid] = mask;
-        uint32_t total;
-        const uint32_t pos0 = block_excl_scan(__popc(mask), scan_smem, &total);
-        const uint32_t myword = mask;
-        // ---- assemble the chunk in shared memory (only threads that own selected elements do work) ----
-        if (mask) {
-            uint32_t p = pos0;
-#pragma unroll
-            for (int j = 0; j < 8; ++j) {
-#pragma unroll
-                for (int q = 0; q < 4; ++q) {
-                    if (mask & (1u << (4 * j + q))) {
-                        if (MODE == EWDML_MODE_IDX16) s_idx[p] = (uint16_t)((tid + 256 * j) * 4 + q);
-                        if (cw == 32) s_code[p] = v[j][q];
-                        else put_bits(s_code, p * cw, v[j][q], cw);
-                        ++p;
+            const uint32_t pos0 = block_excl_scan(__popc(mask), scan_smem, &total);
+            myword = mask;
+            // ---- assemble the chunk in shared memory (only threads that own selected elements do work) ----
+            if (mask) {
+                uint32_t p = pos0;
+    #pragma unroll
+                for (int j = 0; j < 8; ++j) {
+    #pragma unroll
+                    for (int q = 0; q < 4; ++q) {
+                        if (mask & (1u << (4 * j + q))) {
+                            if (MODE == EWDML_MODE_IDX16) s_idx[p] = (uint16_t)((tid + 256 * j) * 4 + q);
+                            if (cw == 32) s_code[p] = v[j][q];
+                            else put_bits(s_code, p * cw, v[j][q], cw);
+                            ++p;
+                        }
                     }
                 }
             }
         }
         const uint32_t idx_bytes = MODE == EWDML_MODE_IDX16 ? align16(total * 2) : 0;
         const uint32_t code_bytes = align16((total * cw + 7) >> 3);
-        if (tid == 0) {
-            unsigned long long off = atomicAdd(&a.ctr->data_used, (unsigned long long)(idx_bytes + code_bytes));
-            if (off + idx_bytes + code_bytes > a.layout.data_cap) {
-                atomicExch(&a.ctr->overflow, 1u);
-                off = 0;
-            }
-            s_off = (uint32_t)off;
-            atomicAdd(&a.ctr->entries, total);
-        }
+        my_entries += total;                             // (identical in every thread; thread 0 publishes them once per CTA)
+        my_bytes += idx_bytes + code_bytes;
         __syncthreads();
-        const uint32_t off = s_off;
-        const bool overflow = a.ctr->overflow != 0;
+        const uint32_t off = (uint32_t)tile * a.layout.chunk_stride;
+        const bool overflow = false;
         // ---- push to every destination ------------------------------------------------------
         for (int d = 0; d < D.n; ++d) {
             char* slot = (char*)D.slot[d];
             if (tid == 0) {
                 uint2 de = make_uint2(off, overflow ? 0u : total);
-                *reinterpret_cast<uint2*>(slot + a.layout.dir + (size_t)blockIdx.x * 8) = de;
+                *reinterpret_cast<uint2*>(slot + a.layout.dir + (size_t)tile * 8) = de;
             }
             if (MODE == EWDML_MODE_BITMAP)
-                reinterpret_cast<uint32_t*>(slot + a.layout.bitmap)[(size_t)blockIdx.x * 256 + tid] = myword;
+                reinterpret_cast<uint32_t*>(slot + a.layout.bitmap)[(size_t)tile * 256 + tid] = myword;
             if (!overflow) {
                 char* dst = slot + a.layout.data + off;
                 const uint4* si4 = reinterpret_cast<const uint4*>(s_idx);
@@ -192,6 +263,17 @@ __global__ void __launch_bounds__(256) k_encode_push(const EncodeArgs a) {
                     st_na_v4(dst + idx_bytes + (size_t)i * 16, sc4[i]);
             }
         }
+        if (next >= a.ntiles) break;
+        __syncthreads();                                 // staging buffers are reused by the next tile
+#pragma unroll
+        for (int j = 0; j < 8; ++j) { v[j][0] = nv[j].x; v[j][1] = nv[j].y; v[j][2] = nv[j].z; v[j][3] = nv[j].w; }
+        td = ntd;
+        tile = next;
+        }   // persistent tile loop
+        if (tid == 0) {
+            atomicAdd(&a.ctr->entries, my_entries);
+            atomicAdd(&a.ctr->data_used, my_bytes);
+        }
     }
     // ---- completion: last CTA publishes header, norms and flags ------------------------------
     __syncthreads();
@@ -199,7 +281,7 @@ __global__ void __launch_bounds__(256) k_encode_push(const EncodeArgs a) {
         // device-scope fence is enough here: this CTA's stores are ordered before its counter increment, the last CTA
         // observes every increment and issues the system-scope fence + release before any peer can see the flag
         __threadfence();
-        s_last = atomicAdd(&a.ctr->ctas_done, 1u) == (uint32_t)(a.ntiles - 1);
+        s_last = atomicAdd(&a.ctr->ctas_done, 1u) == gridDim.x - 1;
     }
     __syncthreads();
     if (s_last) {
@@ -241,7 +323,9 @@ int ewdml_launch_select(ewdml_plan* p, const float* grad, cudaStream_t st);
 
 static size_t encode_smem_bytes(const ewdml_codec& c) {
     if (c.mode == EWDML_MODE_DENSE) return 0;
-    return (size_t)(512 + 4096 + c.code_bits * 256 + 4) * 4;
+    size_t words = 512 + 4096 + (size_t)c.code_bits * 256 + 4;
+    if (c.mode == EWDML_MODE_IDX16 && c.sel == EWDML_SEL_TOPK) words += 4 + EWDML_TILE / 2 + EWDML_TILE;   // sparse-path lists
+    return words * 4;
 }
 
 static int send_impl(ewdml_plan* p, const float* grad, const ewdml_dests* dests, const ewdml_dests* dests_odd,
@@ -265,8 +349,8 @@ static int send_impl(ewdml_plan* p, const float* grad, const ewdml_dests* dests,
 #define ENC_LAUNCH(MODE_, SEL_, VAL_)                                                                                   \
     do {                                                                                                              \
         EWDML_CUDA(cudaFuncSetAttribute(k_encode_push<MODE_, SEL_, VAL_>, cudaFuncAttributeMaxDynamicSharedMemorySize,  \
-                                        100 * 1024));                                                                 \
-        k_encode_push<MODE_, SEL_, VAL_><<<p->ntiles, 256, smem, st>>>(a);                                            \
+                                        160 * 1024));                                                                 \
+        k_encode_push<MODE_, SEL_, VAL_><<<p->ntiles < 2 * 148 ? p->ntiles : 2 * 148, 256, smem, st>>>(a);                                            \
     } while (0)
     const int sel = p->codec.sel, val = p->codec.val;
     if (p->codec.mode == EWDML_MODE_DENSE) {

@@ -91,11 +91,18 @@ extern "C" int ewdml_plan_create(ewdml_plan** out, int nseg, const int64_t* seg_
     int64_t data_off = round_up_i64(L.bitmap + bitmap_bytes, 128);
     if (data_off > 0xFFFFFFFFll) { delete p; ewdml_set_error("plan too large"); return EWDML_ERR_ARG; }
     L.data = (uint32_t)data_off;
+    L.chunk_stride = 0;
     if (codec->mode == EWDML_MODE_DENSE) {
         L.data_cap = (uint64_t)total * 4;
     } else {
-        L.data_cap = (uint64_t)((codec->mode == EWDML_MODE_IDX16 ? 2 * emax : 0) +
-                                (emax * codec->code_bits + 7) / 8 + 48ll * p->ntiles + 256);
+        // Every tile owns a fixed, worst-case sized chunk (all 8192 elements selected).  Only the bytes actually
+        // produced are written or read, so the slack costs address space, not bandwidth -- and the encode kernel needs
+        // no global allocator (a same-address atomic with return value per tile serialises the whole grid).
+        const uint32_t idx_max = codec->mode == EWDML_MODE_IDX16 ? EWDML_TILE * 2 : 0;
+        const uint32_t code_max = (uint32_t)(((int64_t)EWDML_TILE * codec->code_bits + 7) / 8 + 15) & ~15u;
+        L.chunk_stride = idx_max + code_max;
+        L.data_cap = (uint64_t)L.chunk_stride * (uint64_t)p->ntiles;
+        if (L.data_cap > 0xFFFF0000ull) { delete p; ewdml_set_error("plan too large for 32-bit chunk offsets"); return EWDML_ERR_ARG; }
     }
     L.total = (uint64_t)round_up_i64((int64_t)(L.data + L.data_cap), 256);
 

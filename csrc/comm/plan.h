@@ -48,6 +48,8 @@ struct SlotLayout {       // byte offsets inside a payload slot
     uint32_t bitmap;      // u32[ntiles * TILE/32]   (BITMAP mode)
     uint32_t data;        // chunk area
     uint64_t data_cap;    // bytes available in the chunk area
+    uint32_t chunk_stride; // compressed modes: tile t's chunk lives at data + t * chunk_stride (worst-case size, so no allocator)
+    uint32_t pad_;
     uint64_t total;       // slot size
 };
 

@@ -17,6 +17,8 @@
 #include "plan.h"
 
 #define KEY(v) (__float_as_uint(v) & 0x7FFFFFFFu)
+// selection test shared with encode.cu: keys are < 2^31, thr may be 0xFFFFFFFF (= -1, "select everything")
+#define SEL_GT(key, thr) ((int32_t)((thr) - (key)) < 0)
 
 __global__ void __launch_bounds__(256) k_sample_hist(const float* __restrict__ grad,
                                                      const SegDesc* __restrict__ segs,
@@ -101,61 +103,95 @@ __global__ void __launch_bounds__(256) k_bounds(const SegDesc* __restrict__ segs
     }
 }
 
-// full read #1
-__global__ void __launch_bounds__(256) k_band(const float* __restrict__ grad, const TileDesc* __restrict__ tiles,
-                                              SegInfo* __restrict__ info, uint32_t* __restrict__ cand,
-                                              const SegDesc* __restrict__ segs, double* __restrict__ tile_sumsq) {
+// full read #1.  Persistent CTAs: the next tile's eight 16-byte loads per thread are issued before the current tile is
+// processed, so global loads stay in flight through the scan / compaction phases.
+__global__ void __launch_bounds__(256, 2) k_band(const float* __restrict__ grad, const TileDesc* __restrict__ tiles,
+                                                 SegInfo* __restrict__ info, uint32_t* __restrict__ cand,
+                                                 const SegDesc* __restrict__ segs, double* __restrict__ tile_sumsq, int ntiles) {
     __shared__ uint32_t scan_smem[40];
-    __shared__ double red_smem[32];
+    __shared__ float ss_smem[8];
     __shared__ uint32_t s_base;
-    const TileDesc td = tiles[blockIdx.x];
-    const uint32_t key_lo = info[td.seg].key_lo, key_hi = info[td.seg].key_hi;
-    const float* base = grad + td.start;
-    float4 v[8];
+    const int tid = threadIdx.x;
+    int tile = blockIdx.x;
+    if (tile >= ntiles) return;
+    TileDesc td = tiles[tile];
+    uint4 v[8], nv[8];
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
-        uint32_t e = (threadIdx.x + 256 * j) * 4;
-        v[j] = e < td.len ? *reinterpret_cast<const float4*>(base + e) : make_float4(0.f, 0.f, 0.f, 0.f);
+        const uint32_t e = (tid + 256 * j) * 4;
+        v[j] = e < td.len ? *reinterpret_cast<const uint4*>(grad + td.start + e) : make_uint4(0, 0, 0, 0);
     }
-    uint32_t ncand = 0, nhi = 0;
-    float ss = 0.f;
+    while (true) {
+        const int next = tile + gridDim.x;
+        TileDesc ntd = td;
+        if (next < ntiles) {
+            ntd = tiles[next];
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-        uint32_t e = (threadIdx.x + 256 * j) * 4;
-        const float x[4] = {v[j].x, v[j].y, v[j].z, v[j].w};
-#pragma unroll
-        for (int q = 0; q < 4; ++q) {
-            if (e + q < td.len) {
-                uint32_t key = KEY(x[q]);
-                if (key >= key_hi) { ++nhi; ss += x[q] * x[q]; }
-                else if (key >= key_lo) ++ncand;
+            for (int j = 0; j < 8; ++j) {
+                const uint32_t e = (tid + 256 * j) * 4;
+                nv[j] = e < ntd.len ? *reinterpret_cast<const uint4*>(grad + ntd.start + e) : make_uint4(0, 0, 0, 0);
             }
         }
-    }
-    double tot = block_sum<double>((double)ss, red_smem);
-    uint32_t ctot, hitot;
-    uint32_t excl = block_excl_scan(ncand, scan_smem, &ctot);
-    (void)block_excl_scan(nhi, scan_smem, &hitot);
-    if (threadIdx.x == 0) {
-        tile_sumsq[blockIdx.x] = tot;
-        if (hitot) atomicAdd(&info[td.seg].cnt_hi, hitot);
-        s_base = ctot ? atomicAdd(&info[td.seg].ncand, ctot) : 0;
-    }
-    __syncthreads();
-    if (ncand) {
-        uint32_t* out = cand + segs[td.seg].offset + s_base + excl;
+        const uint32_t key_lo = info[td.seg].key_lo, key_hi = info[td.seg].key_hi;
+        // masks by subtraction: bit i of mge_x = (key_i >= x) via the sign of (key - x); built by shift-insert from the top
+        uint32_t mge_hi = 0, mge_lo = 0;
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
-            uint32_t e = (threadIdx.x + 256 * j) * 4;
-            const float x[4] = {v[j].x, v[j].y, v[j].z, v[j].w};
+            const uint32_t x[4] = {v[j].x, v[j].y, v[j].z, v[j].w};
 #pragma unroll
             for (int q = 0; q < 4; ++q) {
-                if (e + q < td.len) {
-                    uint32_t key = KEY(x[q]);
-                    if (key < key_hi && key >= key_lo) *out++ = key;
-                }
+                const uint32_t key = x[q] & 0x7FFFFFFFu;
+                mge_hi = (mge_hi >> 1) | (~(key - key_hi) & 0x80000000u);
+                mge_lo = (mge_lo >> 1) | (~(key - key_lo) & 0x80000000u);
             }
         }
+        if (key_hi > 0x7FFFFFFFu) mge_hi = 0;           // key_hi = 0xFFFFFFFF: nothing is "definitely selected"
+        uint32_t mhi = mge_hi, mcand = mge_lo & ~mge_hi;
+        float ss = 0.f;
+        if (td.len != EWDML_TILE) {                     // partial tile: out-of-range lanes were loaded as +0.0f
+            uint32_t valid = 0;
+#pragma unroll
+            for (int j = 0; j < 8; ++j)
+#pragma unroll
+                for (int q = 0; q < 4; ++q)
+                    if ((tid + 256 * j) * 4 + q < td.len) valid |= 1u << (4 * j + q);
+            mhi &= valid; mcand &= valid;
+        }
+        // the few elements at or above the band are re-read from global memory (L2 hits) instead of dragging 32
+        // predicated blocks through every warp
+        for (uint32_t m = mhi; m; m &= m - 1) {
+            const int b = __ffs(m) - 1;
+            const float f = grad[td.start + (((tid + 256 * (b >> 2)) << 2) + (b & 3))];
+            ss = fmaf(f, f, ss);
+        }
+        ss = warp_sum(ss);
+        if ((tid & 31) == 0) ss_smem[tid >> 5] = ss;
+        uint32_t tot;
+        const uint32_t packed = __popc(mcand) | (__popc(mhi) << 16);
+        const uint32_t excl = block_excl_scan(packed, scan_smem, &tot) & 0xFFFFu;
+        if (tid == 0) {
+            double t = 0.0;
+#pragma unroll
+            for (int w = 0; w < 8; ++w) t += (double)ss_smem[w];
+            tile_sumsq[tile] = t;
+            const uint32_t ctot = tot & 0xFFFFu, hitot = tot >> 16;
+            if (hitot) atomicAdd(&info[td.seg].cnt_hi, hitot);
+            s_base = ctot ? atomicAdd(&info[td.seg].ncand, ctot) : 0;
+        }
+        __syncthreads();
+        if (mcand) {
+            uint32_t* out = cand + segs[td.seg].offset + s_base + excl;
+            for (uint32_t m = mcand; m; m &= m - 1) {
+                const int b = __ffs(m) - 1;
+                *out++ = __float_as_uint(grad[td.start + (((tid + 256 * (b >> 2)) << 2) + (b & 3))]) & 0x7FFFFFFFu;
+            }
+        }
+        if (next >= ntiles) break;
+        __syncthreads();                                // s_base / ss_smem are reused by the next tile
+#pragma unroll
+        for (int j = 0; j < 8; ++j) v[j] = nv[j];
+        td = ntd;
+        tile = next;
     }
 }
 
@@ -189,7 +225,7 @@ __device__ uint32_t radix_round(const uint32_t* keys, const float* raw, uint32_t
 
 template <bool RAW>
 __device__ void exact_select(const uint32_t* keys, const float* raw, uint32_t n, uint32_t rank, uint32_t* h,
-                             uint32_t* scan_smem, uint32_t* s_digit, uint32_t* s_r, uint32_t* thr, uint32_t* need_eq) {
+                             uint32_t* scan_smem, uint32_t* s_digit, uint32_t* s_r, uint32_t* thr, uint32_t* need_eq, uint32_t* n_eq) {
     if (threadIdx.x == 0) *s_r = rank;
     __syncthreads();
     uint32_t d0 = radix_round<RAW>(keys, raw, n, 20, 0x7FF, 32, 0, s_r, h, scan_smem, s_digit);
@@ -198,6 +234,7 @@ __device__ void exact_select(const uint32_t* keys, const float* raw, uint32_t n,
     uint32_t d2 = radix_round<RAW>(keys, raw, n, 0, 0x1FF, 9, p1, s_r, h, scan_smem, s_digit);
     *thr = (p1 << 9) | d2;
     *need_eq = *s_r;
+    *n_eq = h[d2];                 // last round's bins are exact keys: how many keys equal the threshold
     __syncthreads();
 }
 
@@ -213,20 +250,23 @@ __global__ void __launch_bounds__(1024) k_refine(const float* __restrict__ grad,
     const uint32_t cnt_hi = si.cnt_hi, ncand = si.ncand;
     const uint32_t* keys = cand + sg.offset;
     const float* raw = grad + sg.offset;
-    uint32_t thr, need_eq;
+    uint32_t thr, need_eq, n_eq = 0;
     bool fallback = false;
     if (cnt_hi <= sg.k && sg.k - cnt_hi <= ncand) {
         uint32_t r = sg.k - cnt_hi;
         if (r == 0) {
-            // everything at or above key_hi is selected and nothing else; key_hi == 0 means "all"
-            if (si.key_hi == 0) { thr = 0; need_eq = 0xFFFFFFFFu; }
-            else { thr = si.key_hi - 1; need_eq = 0; }
+            // everything at or above key_hi is selected and nothing else (key_hi == 0 -> thr = -1 -> "all", see SEL_GT)
+            thr = si.key_hi - 1; need_eq = 0;
         }
-        else exact_select<false>(keys, raw, ncand, r, h, scan_smem, &s_digit, &s_r, &thr, &need_eq);
+        else exact_select<false>(keys, raw, ncand, r, h, scan_smem, &s_digit, &s_r, &thr, &need_eq, &n_eq);
     } else {
         fallback = true;                           // the sampled band missed: exact scan of the raw segment
-        exact_select<true>(keys, raw, sg.numel, sg.k, h, scan_smem, &s_digit, &s_r, &thr, &need_eq);
+        exact_select<true>(keys, raw, sg.numel, sg.k, h, scan_smem, &s_digit, &s_r, &thr, &need_eq, &n_eq);
     }
+    // The usual case is a unique k-th magnitude (or all of its duplicates wanted): fold the ties into the strict
+    // comparison by lowering the threshold one ulp, so the encode kernel needs a single compare per element and no
+    // tickets.  Only a genuine tie (more equal keys than slots left) keeps need_eq != 0.
+    if (need_eq != 0 && need_eq == n_eq) { thr -= 1; need_eq = 0; }
     double sumsq = 0.0;
     if (want_norm) {
         double acc = 0.0;
@@ -234,16 +274,16 @@ __global__ void __launch_bounds__(1024) k_refine(const float* __restrict__ grad,
             for (uint32_t t = threadIdx.x; t < sg.ntiles; t += blockDim.x) acc += tile_sumsq[sg.tile0 + t];
             for (uint32_t i = threadIdx.x; i < ncand; i += blockDim.x) {
                 uint32_t key = keys[i];
-                if (key > thr) { double f = (double)__uint_as_float(key); acc += f * f; }
+                if (SEL_GT(key, thr)) { double f = (double)__uint_as_float(key); acc += f * f; }
             }
         } else {
             for (uint32_t i = threadIdx.x; i < sg.numel; i += blockDim.x) {
                 uint32_t key = KEY(raw[i]);
-                if (key > thr) { double f = (double)__uint_as_float(key); acc += f * f; }
+                if (SEL_GT(key, thr)) { double f = (double)__uint_as_float(key); acc += f * f; }
             }
         }
         sumsq = block_sum<double>(acc, red_smem);
-        double t = (double)__uint_as_float(thr);
+        double t = need_eq ? (double)__uint_as_float(thr) : 0.0;
         sumsq += (double)need_eq * t * t;
     }
     if (threadIdx.x == 0) {
@@ -307,7 +347,8 @@ int ewdml_launch_select(ewdml_plan* p, const float* grad, cudaStream_t st) {
         EWDML_LAUNCH_CHECK();
         k_bounds<<<p->nseg, 256, 0, st>>>(p->d_seg, p->d_hist, p->d_seginfo);
         EWDML_LAUNCH_CHECK();
-        k_band<<<p->ntiles, 256, 0, st>>>(grad, p->d_tile, p->d_seginfo, p->d_cand, p->d_seg, p->d_tile_sumsq);
+        k_band<<<p->ntiles < 2 * 148 ? p->ntiles : 2 * 148, 256, 0, st>>>(grad, p->d_tile, p->d_seginfo, p->d_cand, p->d_seg,
+                                                                      p->d_tile_sumsq, p->ntiles);
         EWDML_LAUNCH_CHECK();
         k_refine<<<p->nseg, 1024, 0, st>>>(grad, p->d_seg, p->d_seginfo, p->d_cand, p->d_tile_sumsq, want_norm,
                                            (float)c.levels);

@@ -142,8 +142,9 @@ def test_topk_exact_selection_matches_oracle(ratio, W):
     for s, si in zip(emu.segs, info):
         k = topk_count(s.numel, ratio)
         keys = g[0][s.offset:s.offset + s.numel].abs().cpu().view(torch.int32).long()
-        n_gt = int((keys > si["thr_key"]).sum())
-        n_eq = int((keys == si["thr_key"]).sum())
+        thr = si["thr_key"] - (1 << 32) if si["thr_key"] >= (1 << 31) else si["thr_key"]     # signed: -1 = select all
+        n_gt = int((keys > thr).sum())
+        n_eq = int((keys == thr).sum())
         assert n_gt + min(si["need_eq"], n_eq) == k
     st = emu.plans[0].stats()
     assert st["entries"] == sum(topk_count(s.numel, ratio) for s in emu.segs) and st["error"] == 0
@@ -193,7 +194,7 @@ def test_degenerate_segments_zero_constant_ties():
     k1 = topk_count(s1.numel, 0.1)
     assert int((c != 0).sum()) <= k1                                # exactly k ties taken, minus level-0 drops
     info = emu.plans[0].seginfo()
-    assert info[1]["need_eq"] == k1 and info[1]["norm"] == pytest.approx(0.5 * math.sqrt(k1), rel=1e-5)
+    assert info[1]["need_eq"] == k1 and info[1]["norm"] == pytest.approx(0.5 * math.sqrt(k1), rel=1e-5)   # genuine tie
     # topk (raw values) on the constant segment keeps exactly k elements
     emu2 = Emu(sizes, "topk", 1, ratio=0.1)
     out2 = emu2.exchange(g)[0].cpu()
