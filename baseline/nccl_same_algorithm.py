@@ -67,7 +67,9 @@ def main(a):
             ix[offs[i]:offs[i + 1]] = idx.to(torch.int32)
             nm[i] = norm
         if world > 1:
-            dist.all_gather_into_tensor(g_lv, lv); dist.all_gather_into_tensor(g_ix, ix); dist.all_gather_into_tensor(g_nm, nm)
+            # NCCL has no int16: ship the level buffer as raw bytes
+            dist.all_gather_into_tensor(g_lv.view(torch.uint8), lv.view(torch.uint8))
+            dist.all_gather_into_tensor(g_ix, ix); dist.all_gather_into_tensor(g_nm, nm)
         else:
             g_lv.copy_(lv); g_ix.copy_(ix); g_nm.copy_(nm)
         for i, p in enumerate(params):

@@ -185,8 +185,12 @@ def run_ewdml(a):
     for _ in range(max(3, a.warmup)):
         one_step(x0, y0)
     barrier()
-    if not a.no_graph and role == "worker":
-        tr.capture(x0, y0)
+    if not a.no_graph:
+        if role == "worker":
+            tr.capture(x0, y0)              # runs 3 eager steps on a side stream, then records the graph
+        else:
+            for _ in range(3):              # the parameter server takes part in those 3 exchanges
+                one_step(x0, y0)
         for _ in range(max(3, a.warmup)):
             one_step(x0, y0)
         barrier()

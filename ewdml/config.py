@@ -190,7 +190,7 @@ class Registry:
 registry = Registry()
 registry.register("select_tile", 8192, "elements per tile in the select/encode kernels")
 registry.register("exchange_ctas", 0, "CTAs for the exchange kernels (0 = 2 x SM count)")
-registry.register("spin_limit", 1 << 28, "device-side flag spin iteration cap before the error word is set")
+registry.register("spin_limit", 1 << 24, "device-side flag spin iteration cap before the error word is set")
 registry.register("allreduce_algo", "auto", "dense allreduce algorithm: auto | oneshot | twoshot")
 registry.register("oneshot_max_bytes", 1 << 20, "auto: use one-shot allreduce at or below this size")
 registry.register("trace", False, "print one line per native collective call (libompitrace analogue)")

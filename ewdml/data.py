@@ -181,8 +181,9 @@ class DeviceFeeder:
             self._dy = [torch.empty(batch_size, dtype=torch.int64, device=device) for _ in range(2)]
             self._ev = [torch.cuda.Event() for _ in range(2)]
             self._consumed = [None, None]
-            self._k = 0
-            self._prefetch()
+            self._ready = [False, False]
+            self._k, self._last = 0, 0
+            self._prefetch(0)
 
     def _next_indices(self) -> torch.Tensor:
         if self._pos + self.bs > self.n:
@@ -195,39 +196,46 @@ class DeviceFeeder:
     def _as_nchw(self, x: torch.Tensor) -> torch.Tensor:
         return x.permute(0, 3, 1, 2) if self.nhwc else x
 
-    def _prefetch(self) -> None:
-        k = self._k
+    def _prefetch(self, k: int) -> None:
+        """Gather the next shuffled batch into pinned slot k and enqueue its H2D copy on the copy stream."""
         sel = self._next_indices()
+        self._ev[k].synchronize()                      # the previous copy out of the pinned staging buffer k has finished
         if self._consumed[k] is not None:
-            # the device buffer may still be read by the step that consumed it
-            self._stream.wait_event(self._consumed[k])
+            self._stream.wait_event(self._consumed[k])  # the step that read device buffer k has finished
         torch.index_select(self.data, 0, sel, out=self._hx[k])
         torch.index_select(self.targets, 0, sel, out=self._hy[k])
         with torch.cuda.stream(self._stream):
             self._dx[k].copy_(self._hx[k], non_blocking=True)
             self._dy[k].copy_(self._hy[k], non_blocking=True)
             self._ev[k].record(self._stream)
+        self._ready[k] = True
 
     def next(self) -> Tuple[torch.Tensor, torch.Tensor]:
+        """Device batch for this step.  Call ``mark_consumed()`` right after launching the step: the host-side
+        gather + H2D copy of the FOLLOWING batch then overlaps the GPU work of this one."""
         if not self._cuda:
             sel = self._next_indices()
             return self._as_nchw(self.data[sel]), self.targets[sel]
         k = self._k
+        if not self._ready[k]:
+            self._prefetch(k)
         torch.cuda.current_stream(self.device).wait_event(self._ev[k])
-        x, y = self._as_nchw(self._dx[k]), self._dy[k]
+        self._ready[k] = False
         self._k ^= 1
-        # the pinned staging buffer of the other slot was consumed by the copy issued two calls ago
-        self._ev[self._k].synchronize()
-        self._prefetch()
-        return x, y
+        self._last = k
+        return self._as_nchw(self._dx[k]), self._dy[k]
 
     def mark_consumed(self) -> None:
-        """Record that the batch returned by the previous next() has been consumed."""
-        if self._cuda:
-            k = self._k ^ 1
-            ev = torch.cuda.Event()
-            ev.record(torch.cuda.current_stream(self.device))
-            self._consumed[k] = ev
+        """The step using the batch from the last ``next()`` has been enqueued: remember when it finishes and start
+        preparing the next batch now, while the GPU is busy."""
+        if not self._cuda:
+            return
+        k = self._last
+        ev = torch.cuda.Event()
+        ev.record(torch.cuda.current_stream(self.device))
+        self._consumed[k] = ev
+        if not self._ready[self._k]:
+            self._prefetch(self._k)
 
     def __iter__(self) -> Iterator[Tuple[torch.Tensor, torch.Tensor]]:
         for _ in range(self.steps_per_epoch):

@@ -99,8 +99,10 @@ def _worker(rank, world, port, out_dir):
     pg.close()
 
 
-def test_two_gpu_exchange_and_allreduce(tmp_path):
-    world = 2
+@pytest.mark.parametrize("world", [2, 8])
+def test_two_gpu_exchange_and_allreduce(tmp_path, world):
+    if torch.cuda.device_count() < world:
+        pytest.skip(f"needs {world} GPUs")
     mp.spawn(_worker, args=(world, _free_port(), str(tmp_path)), nprocs=world, join=True)
     for r in range(world):
         res = json.load(open(os.path.join(str(tmp_path), f"r{r}.json")))
@@ -142,7 +144,7 @@ def _trainer(rank, world, port, out_dir, exchange, method):
 
 @pytest.mark.parametrize("exchange,method", [("allgather", 0), ("allreduce", 3), ("ps", 1), ("ps", 3), ("ps", 5)])
 def test_two_gpu_training_replicas_stay_identical(tmp_path, exchange, method):
-    world = 2 if exchange != "ps" else min(3, torch.cuda.device_count())
+    world = min(4, torch.cuda.device_count()) if exchange != "ps" else min(5, torch.cuda.device_count())
     if exchange == "ps" and world < 2:
         pytest.skip("needs 2 GPUs")
     mp.spawn(_trainer, args=(world, _free_port(), str(tmp_path), exchange, method), nprocs=world, join=True)
