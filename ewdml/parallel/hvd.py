@@ -2,7 +2,9 @@
 DistributedOptimizer(compression=...)`` (what ``horvod_pytorch.py:125-201`` uses from ``horovod.torch``).
 
 Backed by ``torch.distributed`` (gloo on CPU, NCCL on GPU) for the generic tensor calls and by the
-framework's compressors for gradients.  Behavioural fix relative to the reference's Horovod path
+framework's compressors for gradients; ``init("native")`` instead brings up the peer-memory runtime and
+routes ``allreduce`` / ``broadcast_parameters`` of CUDA tensors through the collective engine
+(:mod:`ewdml.parallel.collectives`), with no ``torch.distributed`` process group at all.  Behavioural fix relative to the reference's Horovod path
 (SURVEY.md 3.4): compressed gradients are all-gathered as (levels, norm) pairs and every pair is
 dequantised with ITS OWN norm before averaging; the reference averages the levels of different
 ranks and rescales by the local norm.
@@ -22,6 +24,15 @@ _state = {"init": False}
 
 
 def init(backend: Optional[str] = None) -> None:
+    if backend == "native":
+        if _state.get("engine") is None:
+            from .collectives import CollectiveEngine
+            from .peer import PeerGroup
+            device = torch.device("cuda", int(os.environ.get("LOCAL_RANK", os.environ.get("RANK", "0"))))
+            torch.cuda.set_device(device)
+            pg = PeerGroup.from_env(device)
+            _state.update(pg=pg, engine=CollectiveEngine.create(pg), init=True)
+        return
     if dist.is_initialized():
         _state["init"] = True
         return
@@ -33,16 +44,29 @@ def init(backend: Optional[str] = None) -> None:
     _state["init"] = True
 
 
+def engine():
+    """The native collective engine when ``init("native")`` was used, else None."""
+    return _state.get("engine")
+
+
 def shutdown() -> None:
+    if _state.get("engine") is not None:
+        _state["engine"].close()
+        _state["pg"].close()
+        _state.update(engine=None, pg=None)
     if dist.is_initialized():
         dist.destroy_process_group()
 
 
 def rank() -> int:
+    if _state.get("engine") is not None:
+        return _state["engine"].rank
     return dist.get_rank() if dist.is_initialized() else 0
 
 
 def size() -> int:
+    if _state.get("engine") is not None:
+        return _state["engine"].world
     return dist.get_world_size() if dist.is_initialized() else 1
 
 
@@ -68,6 +92,11 @@ def _adasum_pair(a: torch.Tensor, b: torch.Tensor) -> torch.Tensor:
 def allreduce(tensor: torch.Tensor, name: Optional[str] = None, op: str = Average,
               prescale_factor: float = 1.0, postscale_factor: float = 1.0) -> torch.Tensor:
     t = tensor.detach().clone() * prescale_factor
+    eng = _state.get("engine")
+    if eng is not None and t.is_cuda and op != Adasum:
+        t32 = t.float().contiguous()
+        eng.all_reduce(t32, scale=(1.0 / size() if op == Average else 1.0) * postscale_factor)
+        return t32.to(tensor.dtype)
     if size() > 1:
         if op == Adasum:
             parts = [torch.empty_like(t) for _ in range(size())]
@@ -86,6 +115,10 @@ def allreduce(tensor: torch.Tensor, name: Optional[str] = None, op: str = Averag
 def broadcast_parameters(params, root_rank: int = 0) -> None:
     items = params.items() if isinstance(params, dict) else params
     if size() == 1:
+        return
+    eng = _state.get("engine")
+    if eng is not None:
+        eng.broadcast_parameters([p for _, p in items if torch.is_tensor(p)], root_rank)
         return
     for _, p in items:
         if torch.is_tensor(p):

@@ -17,6 +17,10 @@ SEL_ALL, SEL_TOPK = 0, 1
 VAL_QSGD, VAL_RAW32 = 0, 1
 OUT_SGD, OUT_GRAD, OUT_ASSIGN = 0, 1, 2
 AR_AUTO, AR_ONESHOT, AR_TWOSHOT = 0, 1, 2
+(COLL_BCAST, COLL_GATHER, COLL_SCATTER, COLL_ALLGATHER, COLL_ALLTOALL, COLL_REDUCE, COLL_REDUCE_SCATTER,
+ COLL_ALLREDUCE, COLL_SEND, COLL_RECV, COLL_BARRIER) = range(11)
+ALGO_AUTO, ALGO_ONESHOT, ALGO_TWOSHOT = 0, 1, 2
+PHASE_PUT, PHASE_WAIT, PHASE_BOTH = 1, 2, 3
 (CTR_LAUNCHES, CTR_SEND_CALLS, CTR_RECV_CALLS, CTR_ALLREDUCE_CALLS, CTR_BYTES_SENT, CTR_BYTES_RECV,
  CTR_COMPUTE_LAUNCHES) = range(7)
 
@@ -110,6 +114,19 @@ def load() -> C.CDLL:
         "ewdml_peer_matrix_add": (None, [i32, i64]),
         "ewdml_peer_matrix_get": (i32, [P(i64)]),
         "ewdml_set_trace": (None, [i32]),
+        "ewdml_engine_window_bytes": (i64, [i32, i64]),
+        "ewdml_engine_flag_bytes": (i64, []),
+        "ewdml_engine_create": (i32, [P(vp), i32, i32, P(vp), P(vp), i64]),
+        "ewdml_engine_destroy": (i32, [vp]),
+        "ewdml_engine_set_algo": (i32, [vp, i32, i32]),
+        "ewdml_engine_select_algo": (i32, [vp, i32, i64]),
+        "ewdml_engine_calls": (i64, [vp, i32]),
+        "ewdml_engine_slot_payload": (i64, [vp]),
+        "ewdml_coll_op_name": (C.c_char_p, [i32]),
+        "ewdml_coll": (i32, [vp, i32, vp, vp, i64, i32, f32, i32, vp]),
+        "ewdml_coll_send": (i32, [vp, vp, i64, i32, i32, vp]),
+        "ewdml_coll_recv": (i32, [vp, vp, i64, i32, i32, vp]),
+        "ewdml_coll_sendrecv": (i32, [vp, vp, i64, i32, vp, i64, i32, i32, vp]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(lib, name)

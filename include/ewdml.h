@@ -150,6 +150,49 @@ int ewdml_get_device_error(uint32_t* out, void* stream);
 int ewdml_set_spin_limit(uint64_t iters);
 
 /* ------------------------------------------------------------------------------------------
+ * N3: collective engine on arbitrary device buffers (replaces the coll framework + coll/base + coll/tuned,
+ * ompi:ompi/mca/coll/coll.h:142-255, ompi:ompi/mca/coll/tuned/coll_tuned_decision_fixed.c:55-217, and pml/ob1
+ * tagged send/recv, ompi:ompi/mca/pml/ob1/pml_ob1_isend.c:147).  Every operation is one kernel: remote stores
+ * into the destination ranks' symmetric windows + release flag, then acquire-wait + copy or ordered sum out of
+ * the local window.  `win[r]` / `flags[r]` are rank r's window and flag block as mapped in this process
+ * (ewdml_engine_window_bytes / ewdml_engine_flag_bytes bytes, zero-initialised).  Sizes are bytes, multiples
+ * of 16; buffers 16-byte aligned; reductions are fp32 sums in rank order times `scale`.  One engine is used
+ * from one stream at a time.
+ * ------------------------------------------------------------------------------------------ */
+typedef struct ewdml_engine ewdml_engine;
+enum { EWDML_COLL_BCAST = 0, EWDML_COLL_GATHER, EWDML_COLL_SCATTER, EWDML_COLL_ALLGATHER, EWDML_COLL_ALLTOALL,
+       EWDML_COLL_REDUCE, EWDML_COLL_REDUCE_SCATTER, EWDML_COLL_ALLREDUCE, EWDML_COLL_SEND, EWDML_COLL_RECV,
+       EWDML_COLL_BARRIER, EWDML_COLL_OP_COUNT };
+enum { EWDML_ALGO_AUTO = 0, EWDML_ALGO_ONESHOT = 1, EWDML_ALGO_TWOSHOT = 2 };
+enum { EWDML_PHASE_PUT = 1, EWDML_PHASE_WAIT = 2, EWDML_PHASE_BOTH = 3 };
+int64_t ewdml_engine_window_bytes(int world, int64_t slot_payload);
+int64_t ewdml_engine_flag_bytes(void);
+int ewdml_engine_create(ewdml_engine** out, int rank, int world, void* const* win, uint32_t* const* flags,
+                        int64_t slot_payload);
+int ewdml_engine_destroy(ewdml_engine* e);
+/* decision layer: forced algorithm per operation (also EWDML_COLL_ALLREDUCE_ALGO=oneshot|twoshot and
+ * EWDML_COLL_ONESHOT_MAX_BYTES in the environment), and the query the engine itself uses            */
+int ewdml_engine_set_algo(ewdml_engine* e, int op, int algo);
+int ewdml_engine_select_algo(const ewdml_engine* e, int op, int64_t nbytes);
+int64_t ewdml_engine_calls(const ewdml_engine* e, int op);
+int64_t ewdml_engine_slot_payload(const ewdml_engine* e);
+const char* ewdml_coll_op_name(int op);
+/* n = bytes per rank-sized piece: bcast/allreduce/reduce: the whole message; gather/allgather: each rank's
+ * contribution (dst holds world * n at the root / everywhere); scatter/alltoall/reduce_scatter: each piece
+ * (src holds world * n).  bcast uses `dst` on every rank (source at the root).  Messages larger than the slot
+ * payload are pipelined in slot-sized pieces.  phases = EWDML_PHASE_BOTH in production; PUT then WAIT as two
+ * calls (n <= slot payload) lets several emulated ranks share one device without kernels waiting on each other. */
+int ewdml_coll(ewdml_engine* e, int op, const void* src, void* dst, int64_t n, int root, float scale, int phases,
+               void* stream);
+/* tagged point-to-point; messages between a pair match in order, a tag/size mismatch sets the device error word */
+int ewdml_coll_send(ewdml_engine* e, const void* src, int64_t n, int peer, int tag, void* stream);
+int ewdml_coll_recv(ewdml_engine* e, void* dst, int64_t n, int peer, int tag, void* stream);
+/* a pair owns two slots: a send longer than 2 x slot payload completes only once the receiver consumes (rendezvous);
+ * sendrecv alternates outgoing and incoming pieces so ring shifts of any length cannot dead-lock (MPI_Sendrecv) */
+int ewdml_coll_sendrecv(ewdml_engine* e, const void* src, int64_t n_send, int to, void* dst, int64_t n_recv, int from,
+                        int tag, void* stream);
+
+/* ------------------------------------------------------------------------------------------
  * N1: symmetric peer heap (replaces BTL smcuda + common_cuda.c IPC paths,
  * ompi:opal/mca/common/cuda/common_cuda.c:1006-1152, and OSHMEM memheap).
  * ------------------------------------------------------------------------------------------ */

@@ -91,6 +91,52 @@ def _worker(rank, world, port, out_dir):
         torch.cuda.synchronize()
         res[f"allreduce_{q}"] = bool(torch.allclose(x.cpu(), expect, rtol=1e-6))
         pg.host_barrier(f"ar_out_{q}")
+    # ---- collective engine (N3), single-kernel form, messages pipelined through 64 KiB slots ----------------
+    from ewdml.parallel.collectives import CollectiveEngine
+    eng = CollectiveEngine.create(pg, slot_payload=1 << 16)
+    m = 50000                                            # 200 kB per rank: 4 pieces
+    mine = (torch.arange(m, dtype=torch.float32) + 1e6 * rank).to(dev)
+    everyone = torch.cat([torch.arange(m, dtype=torch.float32) + 1e6 * r for r in range(world)]).to(dev)
+    ag = torch.zeros(world * m, device=dev)
+    eng.all_gather(mine, ag)
+    res["eng_allgather"] = bool(torch.equal(ag, everyone))
+    total = sum((torch.arange(m, dtype=torch.float32) + 1e6 * r) for r in range(world)).to(dev)
+    for algo in ("oneshot", "twoshot"):
+        eng.set_algo("allreduce", algo)
+        t = mine.clone()
+        if algo == "twoshot":
+            t = t[:m // (4 * world) * (4 * world)].clone()
+        eng.all_reduce(t, scale=1.0 / world)
+        res[f"eng_allreduce_{algo}"] = bool(torch.allclose(t, total[:t.numel()] / world, rtol=1e-6))
+    b = mine.clone()
+    eng.broadcast(b, root=world - 1)
+    res["eng_bcast"] = bool(torch.equal(b, everyone[(world - 1) * m:]))
+    piece = 4096
+    a2a_in = (torch.arange(world * piece, dtype=torch.float32) + 1e6 * rank).to(dev)
+    a2a_out = torch.zeros(world * piece, device=dev)
+    eng.all_to_all(a2a_in, a2a_out)
+    exp = torch.cat([torch.arange(rank * piece, (rank + 1) * piece, dtype=torch.float32) + 1e6 * s for s in range(world)]).to(dev)
+    res["eng_alltoall"] = bool(torch.equal(a2a_out, exp))
+    rs_out = torch.zeros(piece, device=dev)
+    eng.reduce_scatter(a2a_in, rs_out)
+    exp = sum(torch.arange(rank * piece, (rank + 1) * piece, dtype=torch.float32) + 1e6 * s for s in range(world)).to(dev)
+    res["eng_reduce_scatter"] = bool(torch.allclose(rs_out, exp, rtol=1e-6))
+    nxt, prv = (rank + 1) % world, (rank - 1) % world
+    got = torch.zeros(m, device=dev)
+    for rep in range(3):                                 # ring shift, messages of 4 pieces, both parities
+        eng.sendrecv(mine, nxt, got, prv, tag=rep)
+    res["eng_sendrecv"] = bool(torch.equal(got, everyone[prv * m:(prv + 1) * m]))
+    small = mine[:1024].clone()                          # plain send / recv: one piece, no rendezvous
+    got2 = torch.zeros(1024, device=dev)
+    if rank % 2 == 0:
+        eng.send(small, nxt, tag=5)
+        eng.recv(got2, prv, tag=5)
+    else:
+        eng.recv(got2, prv, tag=5)
+        eng.send(small, nxt, tag=5)
+    res["eng_send_then_recv"] = bool(torch.equal(got2, everyone[prv * m:prv * m + 1024]))
+    eng.barrier()
+    torch.cuda.synchronize()
     err = C.c_uint32(0)
     L.check(lib.ewdml_get_device_error(C.byref(err), st))
     res["device_error"] = err.value
