@@ -24,7 +24,7 @@ NETWORKS = ("LeNet", "ResNet18", "ResNet34", "ResNet50", "ResNet101", "ResNet152
 DATASETS = ("MNIST", "Cifar10", "Cifar100", "SVHN")
 COMPRESSORS = ("none", "qsgd", "topk", "topk-qsgd")
 EXCHANGES = ("ps", "allgather", "allreduce")
-# The six "methods" of the report (Report.zip!main.tex:80-119); see ewdml/parallel/methods.py.
+# The six "methods" of the report (Report.zip!main.tex:80-119); resolved by TrainConfig.resolved_*() below.
 METHODS = (0, 1, 2, 3, 4, 5, 6)
 
 
@@ -70,7 +70,7 @@ class TrainConfig:
     compressor: str = ""            # "" = derive from --compress-grad / --method
     qsgd_levels: int = 128          # qsgd.py:9
     topk_ratio: float = 0.5         # qsgd.py:10 (slides use 0.4)
-    bucket_size: int = 0            # 0 = one bucket per parameter tensor (reference semantics)
+    bucket_size: int = 0            # bytes per exchange bucket; 0 = the whole model in one launch (per-tensor norms / top-k either way)
     sync_period: int = 1            # 20 in the report's method 6
     exchange: str = "ps"            # ps | allgather | allreduce
     pull: str = ""                  # "" = derive; weights | grads
@@ -92,7 +92,7 @@ class TrainConfig:
     fault_inject_rank: int = -1
     timeout_s: float = 300.0        # collective timeout for the watchdog
     shard_data: bool = True         # per-rank sharding (reference has none; fix per Appendix A)
-    overlap: bool = True            # launch exchange buckets from autograd hooks
+    overlap: bool = False           # launch each bucket's exchange from backward (autograd hooks) on a side stream
     graphs: bool = False            # capture the step in a CUDA graph
 
     # ------------------------------------------------------------------

@@ -11,6 +11,7 @@ from typing import Optional
 
 import torch
 
+from ..parallel import overlap as _overlap
 from ..runtime import lib as L
 
 _lib = None
@@ -376,6 +377,10 @@ class _ConvBlockFn(torch.autograd.Function):
                     L.check(lib.ewdml_col2im(_p(dcol), _p(dxn), N, H, W, Cin, kh, kh, stride, pad, st), "col2im")
                 dx = dxn.permute(0, 3, 1, 2)
         dr = dres.view(N, HO, WO, Cout).permute(0, 3, 1, 2) if (ctx.has_res and ctx.needs_input_grad[1]) else None
+        if _overlap._ACTIVE:       # gradients went straight into the flat buffer: tell the bucket scheduler
+            for prm in (conv.weight, conv.bias, bn.weight if bn is not None else None, bn.bias if bn is not None else None):
+                if prm is not None:
+                    _overlap.notify_grad_ready(prm)
         return dx, dr, None, None, None, None, None
 
 
@@ -449,6 +454,10 @@ class _LinearFn(torch.autograd.Function):
             wb = _weight_bf16(lin.weight, lin.out_features, lin.in_features)
             dx = _empty2d(B, lin.in_features, dy.device)
             gemm(dy, wb, False, True, out=dx)                                # dx = dy W
+        if _overlap._ACTIVE:
+            _overlap.notify_grad_ready(lin.weight)
+            if lin.bias is not None:
+                _overlap.notify_grad_ready(lin.bias)
         return dx, None, None, None
 
 

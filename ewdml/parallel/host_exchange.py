@@ -40,9 +40,9 @@ class ExchangeStats:
     t_recv: float = 0.0
 
 
-def _codec(flat: FlatModel, cfg, rank: int, compressor: Optional[str] = None) -> HostCodec:
-    return HostCodec(flat.segments, compressor or cfg.resolved_compressor(), cfg.qsgd_levels,
-                     cfg.topk_ratio, seed=cfg.seed, rank=rank)
+def _codec(flat: FlatModel, cfg, rank: int, compressor: Optional[str] = None, segments=None) -> HostCodec:
+    return HostCodec(segments if segments is not None else flat.segments, compressor or cfg.resolved_compressor(),
+                     cfg.qsgd_levels, cfg.topk_ratio, seed=cfg.seed, rank=rank)
 
 
 class Exchange:
@@ -52,6 +52,23 @@ class Exchange:
         self.flat, self.cfg, self.optimizer, self.group = flat, cfg, optimizer, group
         self.rank = dist.get_rank(group) if dist.is_initialized() else 0
         self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        # error feedback (optional, off = reference semantics): what the compressor dropped is added to the next gradient
+        ef = bool(getattr(cfg, "error_feedback", False)) and cfg.resolved_compressor() != "none"
+        self.residual = torch.zeros(flat.total, dtype=torch.float32) if ef else None
+        self._own = torch.zeros(flat.total, dtype=torch.float32) if ef else None
+
+    def _ef_source(self) -> torch.Tensor:
+        """The vector to compress: the gradient, plus the carried residual when error feedback is on."""
+        if self.residual is None:
+            return self.flat.grad
+        self.residual.add_(self.flat.grad.detach().cpu())
+        return self.residual
+
+    def _ef_update(self, codec: HostCodec, msg: torch.Tensor) -> None:
+        if self.residual is not None:
+            codec.decode(msg, out=self._own, accumulate=False, total=self.flat.total)
+            for seg in codec.segments:                      # only this codec's segments (bucketed exchanges)
+                self.residual[seg.offset:seg.offset + seg.numel].sub_(self._own[seg.offset:seg.offset + seg.numel])
 
     def local_step(self) -> ExchangeStats:
         """Local SGD on this rank's own gradient (non-sync steps of method 6)."""
@@ -98,7 +115,8 @@ class PSWorker(Exchange):
             return self.local_step()
         st = ExchangeStats()
         t0 = time.perf_counter()
-        msg = self.push.encode(self.flat.grad, step_idx)
+        msg = self.push.encode(self._ef_source(), step_idx)
+        self._ef_update(self.push, msg)
         dist.gather(msg, None, dst=0, group=self.group)
         st.t_send = time.perf_counter() - t0
         st.bytes_sent = msg.numel()
@@ -163,34 +181,72 @@ class PSServer(Exchange):
 # Server-less strategies
 # --------------------------------------------------------------------------------------
 class AllgatherExchange(Exchange):
+    """``--bucket-size`` splits the model into contiguous buckets; with ``--overlap`` each bucket is encoded and its
+    ``all_gather`` started (``async_op``) from the backward pass as soon as its gradients exist
+    (:mod:`ewdml.parallel.overlap`), and ``finish_overlap`` waits, decodes and applies."""
+
     def __init__(self, flat, cfg, optimizer, group=None):
         super().__init__(flat, cfg, optimizer, group)
-        self.codecs = [_codec(flat, cfg, r) for r in range(self.world)]
-        n = self.codecs[0].nbytes
-        self._slots = [torch.zeros(n, dtype=torch.uint8) for _ in range(self.world)]
+        from .overlap import partition_buckets
+        self.buckets = partition_buckets(flat.segments, getattr(cfg, "bucket_size", 0))
+        self.codecs = [[_codec(flat, cfg, r, segments=flat.segments[lo:hi]) for r in range(self.world)]
+                       for lo, hi in self.buckets]
+        self._slots = [[torch.zeros(c[0].nbytes, dtype=torch.uint8) for _ in range(self.world)] for c in self.codecs]
         self._avg = torch.zeros(flat.total, dtype=torch.float32)
+        self._works, self._sent = [], 0
+
+    def _launch(self, b: int, step_idx: int, async_op: bool, src: torch.Tensor):
+        msg = self.codecs[b][self.rank].encode(src, step_idx)
+        self._ef_update(self.codecs[b][self.rank], msg)
+        self._sent += msg.numel()
+        if self.world > 1:
+            return dist.all_gather(self._slots[b], msg, group=self.group, async_op=async_op)
+        self._slots[b][0].copy_(msg)
+        return None
+
+    def _apply_all(self) -> None:
+        self._avg.zero_()
+        for b in range(len(self.buckets)):
+            for r in range(self.world):
+                self.codecs[b][r].decode(self._slots[b][r], out=self._avg, accumulate=True, total=self.flat.total)
+        self._avg.div_(self.world)
+        avg = self._avg.to(self.flat.param.device)
+        self.optimizer.step(grads=[self.flat.view(avg, i) for i in range(len(self.flat.segments))])
 
     def step(self, step_idx: int, is_sync_step: bool = True) -> ExchangeStats:
         if not is_sync_step:
             return self.local_step()
         st = ExchangeStats()
         t0 = time.perf_counter()
-        msg = self.codecs[self.rank].encode(self.flat.grad, step_idx)
-        if self.world > 1:
-            dist.all_gather(self._slots, msg, group=self.group)
-        else:
-            self._slots[0].copy_(msg)
+        self._sent = 0
+        src = self._ef_source()
+        for b in range(len(self.buckets) - 1, -1, -1):      # last layers first, the order backward produces them
+            self._launch(b, step_idx, False, src)
         st.t_send = time.perf_counter() - t0
         t0 = time.perf_counter()
-        self._avg.zero_()
-        for r in range(self.world):
-            self.codecs[r].decode(self._slots[r], out=self._avg, accumulate=True)
-        self._avg.div_(self.world)
-        avg = self._avg.to(self.flat.param.device)
-        self.optimizer.step(grads=[self.flat.view(avg, i) for i in range(len(self.flat.segments))])
+        self._apply_all()
         st.t_recv = time.perf_counter() - t0
-        st.bytes_sent = (self.world - 1) * msg.numel()
-        st.bytes_recv = (self.world - 1) * msg.numel()
+        st.bytes_sent = st.bytes_recv = (self.world - 1) * self._sent
+        return st
+
+    # ---- backward-overlapped form ---------------------------------------------------------------------
+    def begin_overlap(self, step_idx: int) -> None:
+        if self.residual is not None:
+            raise RuntimeError("--overlap and --error-feedback cannot be combined")
+        self._works, self._sent, self._step = [], 0, step_idx
+
+    def bucket_ready(self, b: int) -> None:
+        self._works.append(self._launch(b, self._step, True, self.flat.grad))
+
+    def finish_overlap(self) -> ExchangeStats:
+        st = ExchangeStats()
+        t0 = time.perf_counter()
+        for w in self._works:
+            if w is not None:
+                w.wait()
+        self._apply_all()
+        st.t_recv = time.perf_counter() - t0
+        st.bytes_sent = st.bytes_recv = (self.world - 1) * self._sent
         return st
 
 

@@ -241,10 +241,11 @@ class _NativeBase(Exchange):
         self._sgd_apply()
         return ExchangeStats()
 
-    def _finish_stats(self, st: ExchangeStats, plan: Optional[ExchangePlan], n_remote_out: int, n_remote_in: int,
+    def _finish_stats(self, st: ExchangeStats, plan, n_remote_out: int, n_remote_in: int,
                       want_stats: bool) -> ExchangeStats:
         if want_stats and plan is not None:
-            self._last_payload = plan.stats()["payload_bytes"]
+            plans = plan if isinstance(plan, (list, tuple)) else [plan]
+            self._last_payload = sum(p.stats()["payload_bytes"] for p in plans)
             self._ev[2].synchronize()
             st.t_send = self._ev[0].elapsed_time(self._ev[1]) * 1e-3
             st.t_recv = self._ev[1].elapsed_time(self._ev[2]) * 1e-3
@@ -254,29 +255,95 @@ class _NativeBase(Exchange):
 
 
 class NativeAllgather(_NativeBase):
+    """Sparse allgather.  ``--bucket-size`` splits the flat buffer into contiguous buckets (one plan + mailbox each);
+    with ``--overlap`` every bucket's K1 + K2 run on a side stream as soon as backward has produced its gradients
+    (:mod:`ewdml.parallel.overlap`), otherwise all sends are enqueued first and all receives after them.  Per-tensor
+    thresholds / norms and the element-indexed Philox counters make the result independent of the bucketing."""
+
     def __init__(self, flat, cfg, optimizer, pg: PeerGroup):
         super().__init__(flat, cfg, optimizer, pg)
+        from .overlap import partition_buckets
         self.codec = make_codec(cfg.resolved_compressor(), cfg.qsgd_levels, cfg.topk_ratio)
-        self.plan = ExchangePlan.for_flat(flat, self.codec)
-        self.mb = Mailbox(pg.alloc("allgather", Mailbox.nbytes(self.world, self.plan.slot_bytes)), self.world,
-                          self.plan.slot_bytes)
+        self.buckets = partition_buckets(flat.segments, cfg.bucket_size)
+        self.plans, self.mbs = [], []
+        for b, (lo, hi) in enumerate(self.buckets):
+            segs = flat.segments[lo:hi]
+            plan = ExchangePlan([s.offset for s in segs], [s.numel for s in segs], self.codec)
+            name = "allgather" if len(self.buckets) == 1 else f"allgather_b{b}"
+            self.plans.append(plan)
+            self.mbs.append(Mailbox(pg.alloc(name, Mailbox.nbytes(self.world, plan.slot_bytes)), self.world, plan.slot_bytes))
+        self.plan, self.mb = self.plans[0], self.mbs[0]
+        self.side: Optional[torch.cuda.Stream] = None
+        # error feedback (optional; the reference has none): what compression dropped is added to the next gradient
+        self.residual = torch.zeros_like(flat.grad) if cfg.error_feedback else None
+        self._own = torch.zeros_like(flat.grad) if cfg.error_feedback else None
+
+    def _send(self, b: int) -> None:
+        me, W, mb = self.rank, self.world, self.mbs[b]
+        src = self.flat.grad if self.residual is None else self.residual
+        self.plans[b].send_state(src, [(mb.slot(r, 0, me), mb.flag(r, 0, me)) for r in range(W)],
+                                 [(mb.slot(r, 1, me), mb.flag(r, 1, me)) for r in range(W)], self.state, self.cfg.seed, me)
+
+    def _recv(self, b: int) -> None:
+        me, W, mb = self.rank, self.world, self.mbs[b]
+        if self.residual is not None:
+            # decode my own payload (already in my mailbox) and keep what it lost: residual = (grad + residual) - sent
+            self.plans[b].recv_apply_state([(mb.slot(me, 0, me), mb.flag(me, 0, me))], [(mb.slot(me, 1, me), mb.flag(me, 1, me))],
+                                           self.state, 1.0, L.OUT_GRAD, out=self._own)
+            lo, hi = self.buckets[b]
+            o0, o1 = self.flat.segments[lo].offset, self.flat.segments[hi - 1].offset + self.flat.segments[hi - 1].numel
+            self.residual[o0:o1].sub_(self._own[o0:o1])
+        self.plans[b].recv_apply_state([(mb.slot(me, 0, r), mb.flag(me, 0, r)) for r in range(W)],
+                                       [(mb.slot(me, 1, r), mb.flag(me, 1, r)) for r in range(W)], self.state, float(W),
+                                       L.OUT_SGD, make_sgd(self.cfg, False), self.flat.param, self.flat.momentum,
+                                       self.flat.param_bf16)
+
+    def _fold_residual(self) -> None:
+        if self.residual is not None:
+            self.residual.add_(self.flat.grad)
 
     def step(self, step_idx: int, is_sync_step: bool = True, want_stats: bool = False) -> ExchangeStats:
         if not is_sync_step:
             return self.local_step()
-        me, W, mb = self.rank, self.world, self.mb
+        W = self.world
         cur = torch.cuda.current_stream()
         self._advance(True)
+        self._fold_residual()
         self._rec(0, cur)
-        self.plan.send_state(self.flat.grad, [(mb.slot(r, 0, me), mb.flag(r, 0, me)) for r in range(W)],
-                             [(mb.slot(r, 1, me), mb.flag(r, 1, me)) for r in range(W)], self.state, self.cfg.seed, me)
+        for b in range(len(self.plans) - 1, -1, -1):
+            self._send(b)
         self._rec(1, cur)
-        self.plan.recv_apply_state([(mb.slot(me, 0, r), mb.flag(me, 0, r)) for r in range(W)],
-                                   [(mb.slot(me, 1, r), mb.flag(me, 1, r)) for r in range(W)], self.state, float(W),
-                                   L.OUT_SGD, make_sgd(self.cfg, False), self.flat.param, self.flat.momentum,
-                                   self.flat.param_bf16)
+        for b in range(len(self.plans) - 1, -1, -1):
+            self._recv(b)
         self._rec(2, cur)
-        return self._finish_stats(ExchangeStats(), self.plan, W - 1, W - 1, want_stats)
+        return self._finish_stats(ExchangeStats(), self.plans, W - 1, W - 1, want_stats)
+
+    # ---- backward-overlapped form: begin_overlap() before forward, bucket_ready(b) from the scheduler, finish after ----
+    def begin_overlap(self) -> None:
+        if self.residual is not None:
+            raise RuntimeError("--overlap and --error-feedback cannot be combined (the residual is folded in after backward)")
+        cur = torch.cuda.current_stream()
+        if self.side is None:
+            self.side = torch.cuda.Stream(device=self.pg.device, priority=-1)
+        self._advance(True)
+        ev = torch.cuda.Event()
+        ev.record(cur)
+        self.side.wait_event(ev)
+
+    def bucket_ready(self, b: int) -> None:
+        ev = torch.cuda.Event()
+        ev.record(torch.cuda.current_stream())
+        self.side.wait_event(ev)
+        with torch.cuda.stream(self.side):
+            self._send(b)
+            self._recv(b)
+
+    def finish_overlap(self, want_stats: bool = False) -> ExchangeStats:
+        torch.cuda.current_stream().wait_stream(self.side)
+        W = self.world
+        if want_stats:      # payload size only: the phases overlap backward, so there is no separate send / receive time
+            self._last_payload = sum(p.stats()["payload_bytes"] for p in self.plans)
+        return self._finish_stats(ExchangeStats(), self.plans, W - 1, W - 1, False)
 
 
 class NativePSWorker(_NativeBase):

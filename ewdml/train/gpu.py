@@ -60,6 +60,11 @@ class GpuTrainer:
         if cfg.compute == "native":
             from ..ops import native
             native.STEP_STATE["tensor"] = self.exchange.state
+        # backward-overlapped bucketed exchange (--overlap): a scheduler fires each bucket's K1+K2 on a side stream
+        self.sched = None
+        if cfg.overlap and role == "worker" and hasattr(self.exchange, "begin_overlap") and self.period == 1:
+            from ..parallel.overlap import BucketScheduler
+            self.sched = BucketScheduler(self.flat.params, self.exchange.buckets, self.exchange.bucket_ready).install()
         self.graph = None
         self.graph_launches = 0          # launches of this repo's kernels inside one captured step
         self.replays = 0
@@ -104,7 +109,17 @@ class GpuTrainer:
             native.end_step()
         return loss, logits
 
+    def _overlapped(self, x, y, want_stats: bool = False):
+        self.exchange.begin_overlap()
+        self.sched.begin_step()
+        loss, logits = self._forward_backward(x, y)
+        self.sched.flush()
+        return loss, logits, self.exchange.finish_overlap(want_stats)
+
     def _step_body(self, x, y):
+        if self.sched is not None:
+            loss, logits, _ = self._overlapped(x, y)
+            return loss.detach(), logits.detach()
         loss, logits = self._forward_backward(x, y)
         self.exchange.step(self.step_idx, is_sync_step=True, want_stats=False)
         return loss.detach(), logits.detach()
@@ -124,8 +139,11 @@ class GpuTrainer:
             self.last_loss, self.last_logits = self.static_loss, self.static_logits
             from ..parallel.host_exchange import ExchangeStats
             return self.static_loss, ExchangeStats()
-        loss, logits = self._forward_backward(x, y)
-        st = self.exchange.step(self.step_idx, is_sync_step=(self.step_idx % self.period == 0), want_stats=want_stats)
+        if self.sched is not None:
+            loss, logits, st = self._overlapped(x, y, want_stats)
+        else:
+            loss, logits = self._forward_backward(x, y)
+            st = self.exchange.step(self.step_idx, is_sync_step=(self.step_idx % self.period == 0), want_stats=want_stats)
         self.step_idx += 1
         self.last_loss, self.last_logits = loss.detach(), logits.detach()
         return self.last_loss, st

@@ -129,6 +129,13 @@ class DistributedWorker(NNTrainer):
         super().build_model(num_classes)
         self.exchange = self._exchange_factory("worker", self.flat, self.cfg, self.optimizer, self.group)
         self.exchange.broadcast_initial_weights(0)
+        # --overlap: fire each bucket's exchange from the backward pass (LeNetSplit's per-layer Isend, lenet.py:111-186,
+        # generalised to every model); only exchanges that expose the overlapped form take part
+        self.sched = None
+        if self.cfg.overlap and hasattr(self.exchange, "begin_overlap") and hasattr(self.exchange, "buckets") \
+                and self.cfg.resolved_sync_period() == 1 and not hasattr(self.exchange, "state"):
+            from ..parallel.overlap import BucketScheduler
+            self.sched = BucketScheduler(self.flat.params, self.exchange.buckets, self.exchange.bucket_ready).install()
         return self
 
     @property
@@ -156,9 +163,17 @@ class DistributedWorker(NNTrainer):
                 t0 = time.perf_counter()
                 x, y = x.to(self.device), y.to(self.device)
                 loss, logits = self._forward(x, y)
-                loss.backward()
-                t_comp = time.perf_counter() - t0
-                st = self.exchange.step(self.cur_step, is_sync_step=(self.cur_step % period == 0))
+                if self.sched is not None:
+                    self.exchange.begin_overlap(self.cur_step)
+                    self.sched.begin_step()
+                    loss.backward()
+                    self.sched.flush()
+                    t_comp = time.perf_counter() - t0
+                    st = self.exchange.finish_overlap()
+                else:
+                    loss.backward()
+                    t_comp = time.perf_counter() - t0
+                    st = self.exchange.step(self.cur_step, is_sync_step=(self.cur_step % period == 0))
                 p1, p5 = accuracy(logits.detach().float(), y, topk=(1, 5))
                 rec = self.log.log(self.cur_step, loss=float(loss.detach()), prec1=float(p1), prec5=float(p5),
                                    bytes_sent=st.bytes_sent, bytes_recv=st.bytes_recv,

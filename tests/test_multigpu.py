@@ -164,9 +164,12 @@ def _trainer(rank, world, port, out_dir, exchange, method):
     dev = torch.device("cuda", rank)
     torch.cuda.set_device(dev)
     pg = PeerGroup.from_env(dev)
+    extra = {}
+    if exchange.endswith("-overlap"):       # bucketed exchange launched from the backward pass on a side stream
+        exchange, extra = exchange[:-len("-overlap")], dict(bucket_size=100000, overlap=True)
     cfg = TrainConfig(network="LeNet", dataset="MNIST", batch_size=32, lr=0.02, momentum=0.9, method=method,
                       exchange=exchange, topk_ratio=0.1, compressor="topk-qsgd" if method == 0 else "",
-                      dtype="fp32", enable_gpu=True).validate()
+                      dtype="fp32", enable_gpu=True, **extra).validate()
     role = "server" if (exchange == "ps" and rank == 0) else "worker"
     tr = GpuTrainer(cfg, dev, pg, role=role)
     g = torch.Generator().manual_seed(5 + rank)
@@ -188,9 +191,12 @@ def _trainer(rank, world, port, out_dir, exchange, method):
     pg.close()
 
 
-@pytest.mark.parametrize("exchange,method", [("allgather", 0), ("allreduce", 3), ("ps", 1), ("ps", 3), ("ps", 5)])
+@pytest.mark.parametrize("exchange,method", [("allgather", 0), ("allgather-overlap", 0), ("allreduce", 3), ("ps", 1), ("ps", 3),
+                                             ("ps", 5)])
 def test_two_gpu_training_replicas_stay_identical(tmp_path, exchange, method):
     world = min(4, torch.cuda.device_count()) if exchange != "ps" else min(5, torch.cuda.device_count())
+    if world < 2:
+        pytest.skip("needs 2 GPUs")
     if exchange == "ps" and world < 2:
         pytest.skip("needs 2 GPUs")
     mp.spawn(_trainer, args=(world, _free_port(), str(tmp_path), exchange, method), nprocs=world, join=True)

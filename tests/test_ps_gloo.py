@@ -26,18 +26,22 @@ def _run(rank, world, port, cfg_kwargs, out_dir):
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
     torch.set_num_threads(1)
     dist.init_process_group("gloo", rank=rank, world_size=world)
+    cfg_kwargs = dict(cfg_kwargs)
+    factory = None
+    if cfg_kwargs.pop("_factory", None) == "library":
+        from ewdml.parallel.nccl_baseline import build_nccl_exchange as factory
     cfg = TrainConfig(**cfg_kwargs).validate()
     ps = cfg.exchange == "ps"
     nw = world - 1 if ps else world
     train_set, _ = build_datasets(cfg)
     total = planned_steps(cfg, len(train_set), nw)
     if ps and rank == 0:
-        m = SyncReplicasMaster_NN(cfg, world).build_model(cfg.num_classes())
+        m = SyncReplicasMaster_NN(cfg, world, exchange_factory=factory).build_model(cfg.num_classes())
         stats = m.start(total_steps=total)
         res = {"role": "server", "steps": len(stats), "bytes_recv": [s.bytes_recv for s in stats]}
     else:
         loader, test_loader = prepare_data(cfg, shard_rank=(rank - 1 if ps else rank), num_shards=nw)
-        w = DistributedWorker(cfg, rank, world).build_model(cfg.num_classes())
+        w = DistributedWorker(cfg, rank, world, exchange_factory=factory).build_model(cfg.num_classes())
         hist = w.train(loader, test_loader, total_steps=total)
         res = {"role": "worker", "loss": [h["loss"] for h in hist],
                "bytes_sent": [h["bytes_sent"] for h in hist],
@@ -108,3 +112,60 @@ def test_cli_entrypoint_under_torchrun(tmp_path):
     out = subprocess.run(cmd, capture_output=True, text=True, timeout=240, cwd=ROOT)
     assert out.returncode == 0, out.stderr[-2000:]
     assert "I am the master" in out.stdout and "I am worker: 1 in all 1 workers" in out.stdout
+
+
+@pytest.mark.parametrize("exchange,method,compressor", [("allgather", 0, "topk"), ("allreduce", 3, ""), ("ps", 1, ""), ("ps", 3, "")])
+def test_library_only_arm_matches_plumbing(tmp_path, exchange, method, compressor):
+    """The torch-ops + collectives classes behind --backend nccl compute the same updates as the packed gloo path
+    (deterministic compressors only; run here on CPU tensors over gloo)."""
+    kw = dict(exchange=exchange, method=method, compressor=compressor, topk_ratio=0.25, max_steps=4)
+    (tmp_path / "a").mkdir(); (tmp_path / "b").mkdir()
+    a = _launch(3, tmp_path / "a", **kw)
+    b = _launch(3, tmp_path / "b", _factory="library", **kw)
+    wa = [r for r in a if r["role"] == "worker"]
+    wb = [r for r in b if r["role"] == "worker"]
+    assert wa[0]["checksum"] == pytest.approx(wb[0]["checksum"], rel=1e-6)
+    assert wb[0]["checksum"] == pytest.approx(wb[1]["checksum"], rel=1e-9)
+    assert wa[0]["loss"] == pytest.approx(wb[0]["loss"], rel=1e-4)
+
+
+def test_bucketed_overlapped_allgather_equals_monolithic(tmp_path):
+    """--bucket-size/--overlap change when the exchange runs, not what it computes (per-tensor norms and top-k,
+    element-indexed random numbers)."""
+    for d in ("a", "b", "c"):
+        (tmp_path / d).mkdir()
+    kw = dict(exchange="allgather", compressor="topk-qsgd", topk_ratio=0.1, max_steps=5)
+    a = _launch(2, tmp_path / "a", **kw)
+    b = _launch(2, tmp_path / "b", bucket_size=100000, **kw)
+    c = _launch(2, tmp_path / "c", bucket_size=100000, overlap=True, **kw)
+    for other in (b, c):
+        assert other[0]["checksum"] == pytest.approx(a[0]["checksum"], rel=1e-12)
+        assert other[0]["loss"] == pytest.approx(a[0]["loss"], rel=1e-9)
+        assert other[0]["bytes_sent"] == a[0]["bytes_sent"]
+    assert c[0]["checksum"] == pytest.approx(c[1]["checksum"], rel=1e-12)
+
+
+def test_error_feedback_conserves_the_gradient_sum():
+    """With error feedback, (everything transmitted so far) + residual == (sum of all gradients so far)."""
+    from ewdml.models import build_model
+    from ewdml.optim import build_optimizer
+    from ewdml.parallel.flat import FlatModel
+    from ewdml.parallel.host_exchange import AllgatherExchange
+    cfg = TrainConfig(network="LeNet", exchange="allgather", compressor="topk-qsgd", topk_ratio=0.05, error_feedback=True,
+                      lr=0.0, momentum=0.0, bucket_size=100000).validate()
+    torch.manual_seed(0)
+    flat = FlatModel(build_model("LeNet", 10))
+    ex = AllgatherExchange(flat, cfg, build_optimizer(cfg, flat.params))
+    assert len(ex.buckets) == 2 and ex.residual is not None
+    total_grad = torch.zeros(flat.total)
+    total_sent = torch.zeros(flat.total)
+    for step in range(6):
+        flat.grad.copy_(torch.randn(flat.total) * 0.01)
+        for seg_a, seg_b in zip(flat.segments[:-1], flat.segments[1:]):       # alignment gaps carry no gradient
+            flat.grad[seg_a.offset + seg_a.numel:seg_b.offset] = 0
+        total_grad += flat.grad
+        ex.step(step)
+        total_sent += ex._avg          # world == 1: the average is exactly what this rank transmitted
+    assert torch.allclose(total_sent + ex.residual, total_grad, atol=1e-5)
+    # without feedback the same compressor loses most of the mass
+    assert (total_sent - total_grad).norm() > 10 * (total_sent + ex.residual - total_grad).norm()
