@@ -90,6 +90,8 @@ class TrainConfig:
     legacy_checkpoint_name: bool = True  # keep "model_step_" (same file every time)
     fault_inject_step: int = -1     # test hook: this rank exits at step k
     fault_inject_rank: int = -1
+    straggler_rank: int = -1        # test hook: this rank sleeps straggler_delay_s before every step
+    straggler_delay_s: float = 0.0
     timeout_s: float = 300.0        # collective timeout for the watchdog
     shard_data: bool = True         # per-rank sharding (reference has none; fix per Appendix A)
     overlap: bool = False           # launch each bucket's exchange from backward (autograd hooks) on a side stream

@@ -178,6 +178,166 @@ class PSServer(Exchange):
 
 
 # --------------------------------------------------------------------------------------
+# Parameter server with backup workers / straggler cut-off
+# --------------------------------------------------------------------------------------
+_PUSH_TAG, _PULL_TAG, _HDR = 11, 12, 16
+
+
+class PSWorkerP2P(PSWorker):
+    """Worker side of the partial-aggregation protocol: point-to-point ``send`` of (step header + payload) and a
+    ``recv`` of the pull message instead of the ``gather`` / ``broadcast`` pair, so the server is free to close a
+    step without this worker."""
+
+    def __init__(self, flat, cfg, optimizer, group=None):
+        super().__init__(flat, cfg, optimizer, group)
+        self._msg = torch.zeros(_HDR + self.push.nbytes, dtype=torch.uint8)
+
+    def step(self, step_idx: int, is_sync_step: bool = True) -> ExchangeStats:
+        if not is_sync_step:
+            return self.local_step()
+        st = ExchangeStats()
+        t0 = time.perf_counter()
+        self._msg[:8].view(torch.int64)[0] = step_idx
+        self.push.encode(self._ef_source(), step_idx, out=self._msg[_HDR:])
+        self._ef_update(self.push, self._msg[_HDR:])
+        dist.send(self._msg, dst=0, group=self.group, tag=_PUSH_TAG)
+        st.t_send = time.perf_counter() - t0
+        st.bytes_sent = self._msg.numel()
+        t0 = time.perf_counter()
+        if self.pull_mode == "weights":
+            dist.recv(self._wbuf, src=0, group=self.group, tag=_PULL_TAG)
+            self.flat.load_flat_params(self._wbuf.to(self.flat.param.device))
+            st.bytes_recv = self._wbuf.numel() * 4
+        else:
+            dist.recv(self._pull_msg, src=0, group=self.group, tag=_PULL_TAG)
+            self.pull.decode(self._pull_msg, out=self._dense)
+            st.bytes_recv = self._pull_msg.numel()
+            dense = self._dense.to(self.flat.param.device)
+            self.optimizer.step(grads=[self.flat.view(dense, i) for i in range(len(self.flat.segments))])
+        st.t_recv = time.perf_counter() - t0
+        return st
+
+
+class PSServerP2P(PSServer):
+    """Aggregates the first ``num_aggregate`` gradients of every step (backup workers, Chen et al. 2016 -- the
+    semantics the reference's ``--num-aggregate`` flag names but never implements, ``distributed_nn.py:50-59``); with
+    ``--mode kill`` it additionally stops waiting ``kill_threshold`` seconds after the first arrival (the dead
+    straggler-kill loop of ``model_ops/lenet.py:188-255``; here the straggler is not interrupted, its late gradient
+    is dropped).  A receiver thread takes pushes from any source in arrival order and queues them by step; gradients
+    of steps that are already closed are counted in ``dropped``.  ``--timeout-s`` bounds the wait for a dead worker."""
+
+    def __init__(self, flat, cfg, optimizer, group=None):
+        import queue
+        import threading
+        super().__init__(flat, cfg, optimizer, group)
+        self.need = max(1, min(cfg.num_aggregate, self.num_workers))
+        self.kill = cfg.mode == "kill"
+        self.threshold = float(cfg.kill_threshold)
+        self.timeout = float(cfg.timeout_s)
+        self.dropped = 0
+        self.used_per_step: List[int] = []
+        self._q: "queue.Queue" = queue.Queue()
+        self._stop = False
+        self._received = 0
+        self._out: list = []
+        self._nbytes = _HDR + self.decoders[0].nbytes
+        self._thread = threading.Thread(target=self._receiver, daemon=True)
+        self._expected: Optional[int] = None        # set by expect(): total number of pushes the job will produce
+        self._started = False
+
+    def expect(self, sync_steps: int) -> None:
+        self._expected = sync_steps * self.num_workers
+
+    def _receiver(self) -> None:
+        while not self._stop and (self._expected is None or self._received < self._expected):
+            buf = torch.empty(self._nbytes, dtype=torch.uint8)
+            try:
+                src = dist.recv(buf, group=self.group, tag=_PUSH_TAG)          # any source, arrival order
+            except Exception as e:                                             # group torn down / peer died
+                self._q.put(("error", e))
+                return
+            self._received += 1
+            self._q.put((int(src), int(buf[:8].view(torch.int64)[0]), buf))
+
+    def step(self, step_idx: int, is_sync_step: bool = True) -> ExchangeStats:
+        import queue
+        if not is_sync_step:
+            return ExchangeStats()
+        if not self._started:
+            self._thread.start()
+            self._started = True
+        st = ExchangeStats()
+        t0 = time.perf_counter()
+        self._out = [(w, b) for (w, b) in self._out if not _done(w)]
+        while len(self._out) > 8 * self.num_workers:        # back-pressure: at most 8 pulls in flight per worker
+            self._out.pop(0)[0].wait()
+        got, first = [], None
+        while len(got) < self.need:
+            now = time.perf_counter()
+            if self.kill and first is not None:
+                wait = self.threshold - (now - first)
+                if wait <= 0:
+                    break
+            else:
+                wait = self.timeout - (now - t0)
+                if wait <= 0:
+                    raise TimeoutError(f"parameter server: {len(got)} of {self.num_workers} gradients after {self.timeout}s "
+                                       f"at step {step_idx} (a worker died?)")
+            try:
+                item = self._q.get(timeout=max(wait, 1e-3))
+            except queue.Empty:
+                continue
+            if item[0] == "error":
+                raise RuntimeError(f"parameter server receiver failed: {item[1]}")
+            src, step, buf = item
+            if step != step_idx:
+                self.dropped += 1                   # a straggler's gradient for a step that is already closed
+                continue
+            got.append((src, buf))
+            first = first or time.perf_counter()
+        self._avg.zero_()
+        for src, buf in sorted(got, key=lambda t: t[0]):
+            self.decoders[src].decode(buf[_HDR:], out=self._avg, accumulate=True)
+        self._avg.div_(len(got))
+        self.used_per_step.append(len(got))
+        st.t_recv = time.perf_counter() - t0
+        st.bytes_recv = len(got) * self._nbytes
+        t0 = time.perf_counter()
+        if self.pull_mode == "weights":
+            avg = self._avg.to(self.flat.param.device)
+            self.optimizer.step(grads=[self.flat.view(avg, i) for i in range(len(self.flat.segments))])
+            msg = self.flat.param.detach().cpu().clone()
+            st.bytes_sent = self.num_workers * msg.numel() * 4
+        else:
+            msg = self.pull.encode(self._avg, step_idx).clone()
+            st.bytes_sent = self.num_workers * msg.numel()
+        for r in range(1, self.world):
+            self._out.append((dist.isend(msg, dst=r, group=self.group, tag=_PULL_TAG), msg))
+        st.t_send = time.perf_counter() - t0
+        return st
+
+    def drain(self) -> None:
+        """End of training: let the receiver take (and drop) what stragglers still owe, finish the outstanding sends."""
+        for w, _ in self._out:
+            w.wait()
+        self._out.clear()
+        if self._started and self._expected is not None:
+            self._thread.join(timeout=self.timeout)
+        self._stop = True
+        while not self._q.empty():
+            item = self._q.get_nowait()
+            if item[0] != "error":
+                self.dropped += 1
+
+
+def _done(work) -> bool:
+    try:
+        return bool(work.is_completed())
+    except Exception:
+        return False
+
+
+# --------------------------------------------------------------------------------------
 # Server-less strategies
 # --------------------------------------------------------------------------------------
 class AllgatherExchange(Exchange):
@@ -278,6 +438,9 @@ class AllreduceExchange(Exchange):
 
 def build_host_exchange(role: str, flat: FlatModel, cfg, optimizer, group=None) -> Exchange:
     if cfg.exchange == "ps":
+        world = dist.get_world_size(group) if dist.is_initialized() else 1
+        if cfg.mode == "kill" or cfg.num_aggregate < world - 1:     # backup workers / straggler cut-off
+            return PSServerP2P(flat, cfg, optimizer, group) if role == "server" else PSWorkerP2P(flat, cfg, optimizer, group)
         return PSServer(flat, cfg, optimizer, group) if role == "server" else PSWorker(flat, cfg, optimizer, group)
     if cfg.exchange == "allgather":
         return AllgatherExchange(flat, cfg, optimizer, group)

@@ -200,6 +200,12 @@ class _NativeBase(Exchange):
         self.state = torch.zeros(4, dtype=torch.int32, device=pg.device)
         self._ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
         self._last_payload = 0
+        from ..config import registry
+        self._nvtx = bool(registry.get("nvtx"))            # NVTX ranges around the exchange phases (EWDML_NVTX=1)
+        self._poison = bool(registry.get("debug_poison"))  # fill consumed receive slots with 0xFF (EWDML_DEBUG_POISON=1)
+        self._host_seq = 0                                 # eager-mode mirror of state[0], for the poison aid only
+        if registry.get("trace"):
+            self.lib.ewdml_set_trace(1)
 
     def broadcast_initial_weights(self, src: int = 0) -> None:
         if self.world == 1:
@@ -223,7 +229,30 @@ class _NativeBase(Exchange):
         if not torch.cuda.is_current_stream_capturing():      # timing events are not recorded into CUDA graphs
             self._ev[i].record(stream)
 
+    def _range(self, name: Optional[str]) -> None:
+        """NVTX range boundary: close the open one, open `name` (None = just close)."""
+        if not self._nvtx:
+            return
+        if getattr(self, "_open_range", False):
+            torch.cuda.nvtx.range_pop()
+            self._open_range = False
+        if name is not None:
+            torch.cuda.nvtx.range_push("ewdml:" + name)
+            self._open_range = True
+
+    def _poison_slots(self, mb: "Mailbox", nsrc: int) -> None:
+        """Debug aid: once a slot has been consumed, overwrite it so that a later kernel which reads
+        bytes its sender did not write this step decodes garbage instead of silently reusing stale data."""
+        if not self._poison:
+            return
+        if torch.cuda.is_current_stream_capturing():
+            raise RuntimeError("EWDML_DEBUG_POISON is an eager-mode aid; it cannot be captured in a CUDA graph")
+        par = self._host_seq & 1
+        for r in range(nsrc):
+            mb.local_slot_bytes(par, r).fill_(0xFF)
+
     def _advance(self, bump_seq: bool) -> None:
+        self._host_seq += int(bump_seq)
         L.check(self.lib.ewdml_state_advance(C.c_void_p(self.state.data_ptr()), int(bump_seq), ExchangePlan._stream()),
                 "state_advance")
 
@@ -310,11 +339,15 @@ class NativeAllgather(_NativeBase):
         self._advance(True)
         self._fold_residual()
         self._rec(0, cur)
+        self._range("select+encode+push")
         for b in range(len(self.plans) - 1, -1, -1):
             self._send(b)
         self._rec(1, cur)
+        self._range("wait+decode+apply")
         for b in range(len(self.plans) - 1, -1, -1):
             self._recv(b)
+            self._poison_slots(self.mbs[b], W)
+        self._range(None)
         self._rec(2, cur)
         return self._finish_stats(ExchangeStats(), self.plans, W - 1, W - 1, want_stats)
 

@@ -159,6 +159,8 @@ class DistributedWorker(NNTrainer):
                 if cfg.fault_inject_step == self.cur_step and cfg.fault_inject_rank == self.rank:
                     logger.error("fault injection: rank %d exits at step %d", self.rank, self.cur_step)
                     os._exit(17)
+                if cfg.straggler_rank == self.rank and cfg.straggler_delay_s > 0:
+                    time.sleep(cfg.straggler_delay_s)
                 self._train_init()
                 t0 = time.perf_counter()
                 x, y = x.to(self.device), y.to(self.device)
@@ -213,6 +215,8 @@ class SyncReplicasMaster_NN(NNTrainer):
         period = cfg.resolved_sync_period()
         total = total_steps if total_steps is not None else cfg.max_steps
         stats = []
+        if hasattr(self.exchange, "expect"):
+            self.exchange.expect(sum(1 for i in range(self.cur_step, total) if i % period == 0))
         for i in range(self.cur_step, total):
             if i % max(1, cfg.log_interval) == 0:
                 logger.info("Master node is entering step: %d", i)
@@ -222,6 +226,8 @@ class SyncReplicasMaster_NN(NNTrainer):
             if cfg.resolved_pull() == "weights" and i % cfg.eval_freq == 0:
                 # the server owns the authoritative weights in this mode
                 ckpt.save_model(self.network, ckpt.model_path(cfg.train_dir, i, False), True)
+        if hasattr(self.exchange, "drain"):
+            self.exchange.drain()
         return stats
 
     start_updated = start

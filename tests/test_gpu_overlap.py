@@ -100,3 +100,24 @@ def test_error_feedback_conserves_the_gradient_sum_on_device():
     assert torch.isfinite(ex.residual).all()
     assert float(ex.residual.norm()) < float(total.norm()) * 2.0
     assert tr.check_device_error() == 0
+
+
+def test_poisoned_receive_slots_and_nvtx_ranges_do_not_change_results():
+    """EWDML_DEBUG_POISON overwrites every consumed slot; if any kernel relied on bytes from an earlier step the
+    parameters would differ from the clean run."""
+    from ewdml.config import registry
+    clean, dev = _setup()
+    registry.set("debug_poison", True); registry.set("nvtx", True)
+    try:
+        dirty, _ = _setup()
+    finally:
+        registry.set("debug_poison", False); registry.set("nvtx", False)
+    assert dirty.exchange._poison and not clean.exchange._poison
+    gen = torch.Generator(device="cpu").manual_seed(11)
+    for step in range(4):
+        g = (torch.randn(clean.flat.total, generator=gen) * 0.01).to(dev)
+        _exchange_once(clean, g, False)
+        _exchange_once(dirty, g, False)
+    torch.cuda.synchronize()
+    assert torch.equal(clean.flat.param, dirty.flat.param)
+    assert clean.check_device_error() == 0

@@ -38,7 +38,8 @@ def _run(rank, world, port, cfg_kwargs, out_dir):
     if ps and rank == 0:
         m = SyncReplicasMaster_NN(cfg, world, exchange_factory=factory).build_model(cfg.num_classes())
         stats = m.start(total_steps=total)
-        res = {"role": "server", "steps": len(stats), "bytes_recv": [s.bytes_recv for s in stats]}
+        res = {"role": "server", "steps": len(stats), "bytes_recv": [s.bytes_recv for s in stats],
+               "used": getattr(m.exchange, "used_per_step", None), "dropped": getattr(m.exchange, "dropped", None)}
     else:
         loader, test_loader = prepare_data(cfg, shard_rank=(rank - 1 if ps else rank), num_shards=nw)
         w = DistributedWorker(cfg, rank, world, exchange_factory=factory).build_model(cfg.num_classes())
@@ -46,7 +47,8 @@ def _run(rank, world, port, cfg_kwargs, out_dir):
         res = {"role": "worker", "loss": [h["loss"] for h in hist],
                "bytes_sent": [h["bytes_sent"] for h in hist],
                "checksum": float(w.flat.param.double().sum()), "dense": w.flat.dense_nbytes(),
-               "codec_bytes": getattr(getattr(w.exchange, "push", None), "nbytes", None)}
+               "codec_bytes": getattr(getattr(w.exchange, "push", None), "nbytes", None),
+               "skipped": getattr(w.exchange, "skipped", None)}
     with open(os.path.join(out_dir, f"r{rank}.json"), "w") as f:
         json.dump(res, f)
     dist.barrier()
@@ -169,3 +171,18 @@ def test_error_feedback_conserves_the_gradient_sum():
     assert torch.allclose(total_sent + ex.residual, total_grad, atol=1e-5)
     # without feedback the same compressor loses most of the mass
     assert (total_sent - total_grad).norm() > 10 * (total_sent + ex.residual - total_grad).norm()
+
+
+@pytest.mark.parametrize("mode,kw", [("normal", dict(num_aggregate=2)), ("kill", dict(num_aggregate=3, kill_threshold=0.05))])
+def test_backup_workers_and_straggler_cutoff(tmp_path, mode, kw):
+    """--num-aggregate < workers: the server closes each step with the first gradients to arrive; --mode kill: it stops
+    waiting kill_threshold seconds after the first arrival.  The straggler's late gradients are dropped, every worker
+    still applies the same pulls, so the replicas stay identical and nobody dead-locks."""
+    res = _launch(4, tmp_path, method=3, mode=mode, straggler_rank=3, straggler_delay_s=0.25, max_steps=6, **kw)
+    server, workers = res[0], res[1:]
+    assert server["steps"] == 6
+    assert all(u == 2 for u in server["used"][1:]), server["used"]      # (step 0 may see all three: start-up skew)
+    assert server["dropped"] >= 4
+    assert all(len(w["loss"]) == 6 for w in workers)
+    assert workers[0]["checksum"] == pytest.approx(workers[1]["checksum"], rel=1e-9)
+    assert workers[0]["checksum"] == pytest.approx(workers[2]["checksum"], rel=1e-9)
