@@ -35,7 +35,13 @@ def _run(a, enable_gpu: bool, steps: int, timeout: float):
     net = {"vgg11": "VGG11", "resnet50": "ResNet50", "lenet": "LeNet", "resnet18": "ResNet18"}[a.model.lower()]
     procs = []
     for r in range(world):
-        env = dict(os.environ, RANK=str(r), WORLD_SIZE=str(world), MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port),
+        # under torchrun this process carries the elastic agent's variables; inherited by the reference's own ranks they
+        # redirect its env:// rendezvous to the agent's store (TORCHELASTIC_USE_AGENT_STORE) and the job never forms
+        base = {k: v for k, v in os.environ.items()
+                if not (k.startswith("TORCHELASTIC_") or k.startswith("TORCH_NCCL_") or k in
+                        ("LOCAL_RANK", "GROUP_RANK", "ROLE_RANK", "ROLE_NAME", "LOCAL_WORLD_SIZE", "GROUP_WORLD_SIZE",
+                         "ROLE_WORLD_SIZE", "TORCHELASTIC_RUN_ID", "NCCL_ASYNC_ERROR_HANDLING"))}
+        env = dict(base, RANK=str(r), WORLD_SIZE=str(world), MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port),
                    EWDML_REF_OUT=out, OMP_NUM_THREADS=str(max(1, (os.cpu_count() or 8) // world)),
                    EWDML_REF_DATASET_SIZE=str(max(1024, a.batch_size * 8)))
         if enable_gpu:

@@ -48,6 +48,9 @@ def parse():
     p.add_argument("--compute", type=str, default=os.environ.get("EWDML_BENCH_COMPUTE", "native"),
                    choices=["torch", "native"])
     p.add_argument("--dtype", type=str, default="bf16")
+    p.add_argument("--bucket-size", type=int, default=0, help="bytes per exchange bucket (0 = one launch for the whole model)")
+    p.add_argument("--overlap", action="store_true", help="launch each bucket's exchange from backward on a side stream")
+    p.add_argument("--error-feedback", action="store_true")
     p.add_argument("--no-e2e", action="store_true")
     p.add_argument("--no-flush", action="store_true")
     p.add_argument("--no-graph", action="store_true", help="do not capture the step in a CUDA graph")
@@ -127,7 +130,8 @@ def run_ewdml(a):
     dataset = "MNIST" if a.model.lower() in ("lenet", "mnistnet") else "Cifar10"
     cfg = TrainConfig(network=a.model, dataset=dataset, batch_size=a.batch_size, lr=0.01, momentum=0.9,
                       compressor=a.compressor, topk_ratio=a.topk_ratio, qsgd_levels=a.qsgd_levels,
-                      exchange=a.exchange, dtype=a.dtype, compute=a.compute, enable_gpu=True, seed=1).validate()
+                      exchange=a.exchange, dtype=a.dtype, compute=a.compute, enable_gpu=True, seed=1,
+                      bucket_size=a.bucket_size, overlap=a.overlap, error_feedback=a.error_feedback).validate()
     pg = PeerGroup.from_env(device)
     role = "server" if (a.exchange == "ps" and rank == 0) else "worker"
     tr = GpuTrainer(cfg, device, pg, role=role)
@@ -236,6 +240,7 @@ def run_ewdml(a):
                    "parallelism": f"dp{world}" + ("(1 server)" if a.exchange == "ps" else ""),
                    "compressor": a.compressor, "topk_ratio": a.topk_ratio, "qsgd_levels": a.qsgd_levels,
                    "exchange": a.exchange, "compute": a.compute, "cuda_graph": tr.graph is not None,
+                   "bucket_size": a.bucket_size, "overlap": tr.sched is not None, "error_feedback": a.error_feedback,
                    "l2": "none" if a.no_flush else "256 MiB buffer overwritten every step inside the timed region"},
         "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "device_ms_total": ms, "wall_ms_total": wall_ms,
         "exchange": None if st is None else {"bytes_sent_per_step": st.bytes_sent, "bytes_recv_per_step": st.bytes_recv,

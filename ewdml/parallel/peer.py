@@ -82,6 +82,20 @@ class PeerGroup:
         if world > 1:
             addr = os.environ.get("MASTER_ADDR", "127.0.0.1")
             port = int(os.environ.get("EWDML_STORE_PORT", int(os.environ.get("MASTER_PORT", "29500")) + 17))
+            if "EWDML_STORE_PORT" not in os.environ:
+                # when torch.distributed is already up, let rank 0 pick a port that is free right now instead of
+                # trusting MASTER_PORT + 17
+                import torch.distributed as dist
+                if dist.is_available() and dist.is_initialized():
+                    obj = [None]
+                    if rank == 0:
+                        import socket
+                        s = socket.socket()
+                        s.bind(("", 0))
+                        obj[0] = s.getsockname()[1]
+                        s.close()
+                    dist.broadcast_object_list(obj, src=0, device=device if dist.get_backend() == "nccl" else None)
+                    port = int(obj[0])
             store = L.Store(addr, port, rank, world, timeout_s=120.0)
         return cls(rank, world, device, store)
 

@@ -45,3 +45,23 @@ def test_env_override_precedence(monkeypatch):
     assert r.register("my_tunable", 3, "x") == 7 and r.dump()["my_tunable"]["source"] == "env"
     r.set("my_tunable", "9"); assert r.get("my_tunable") == 9
     assert "select_tile" in registry.dump()
+
+
+def test_cluster_tool_on_the_local_pseudo_host(tmp_path):
+    """tools/cluster.py (the host-driving half of the reference's pytorch_ec2.py): hosts file, run_command, launch with
+    recorded PIDs, status, PID-based kill_all -- exercised on the `local` pseudo host, no ssh involved."""
+    import os, subprocess, sys, time
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    hosts, pids, log = tmp_path / "hosts", tmp_path / "pids", tmp_path / "job.log"
+    hosts.write_text("# comment\nlocal 2\n")
+    base = [sys.executable, os.path.join(root, "tools", "cluster.py"), "--hosts", str(hosts), "--pids", str(pids)]
+    run = lambda *args: subprocess.run(base + list(args), capture_output=True, text=True, timeout=120, cwd=root)
+    assert run("get_hosts").stdout.strip() == "local slots=2"
+    assert "[local] hello" in run("run_command", "--", "echo", "hello").stdout
+    dry = run("--dry-run", "launch", "--", "python", "x.py")
+    assert "ewdml.cli.launch -np 2" in dry.stdout and not pids.exists()
+    out = run("launch", "--log", str(log), "--master-port", "29761", "--", sys.executable, "-c", "import time; time.sleep(60)")
+    assert out.returncode == 0 and pids.exists(), out.stderr
+    time.sleep(1.0)
+    assert "running" in run("status").stdout
+    assert run("kill_all").returncode == 0 and not pids.exists()

@@ -35,3 +35,24 @@ def test_info_tool_and_adasum_pair():
     a = torch.tensor([1.0, 0.0]); b = torch.tensor([0.0, 1.0])
     assert torch.allclose(_adasum_pair(a, b), a + b)                 # orthogonal -> sum
     assert torch.allclose(_adasum_pair(a, a), a)                     # parallel   -> average
+
+
+def test_keras_style_trainer_with_callbacks(tmp_path):
+    """tensorflow_mnist.py's capability: Adam + DistributedOptimizer, broadcast / metric-average / LR warm-up callbacks,
+    rank-0 checkpoint per epoch."""
+    ck = str(tmp_path / "checkpoint-{epoch}.pt")
+    cmd = [sys.executable, "-m", "ewdml.cli.launch", "-np", "2", "--master-port", "29743", "--",
+           sys.executable, "-m", "ewdml.cli.allreduce_mnist_keras", "--epochs", "2", "--steps-per-epoch", "6", "--no-cuda",
+           "--synthetic-size", "256", "--batch-size", "16", "--warmup-epochs", "1", "--checkpoint-format", ck]
+    out = subprocess.run(cmd, capture_output=True, text=True, timeout=300, cwd=ROOT)
+    assert out.returncode == 0, out.stderr[-1500:]
+    assert "Epoch 2/2 - loss:" in out.stdout and "finished gradual learning rate warmup" in out.stdout
+    assert os.path.isfile(ck.format(epoch=1)) and os.path.isfile(ck.format(epoch=2))
+    sd = torch.load(ck.format(epoch=2))
+    assert sd["fc1.weight"].shape == (128, 64 * 12 * 12)
+
+
+def test_lr_warmup_multiplier_matches_horovod_formula():
+    from ewdml.parallel import hvd_keras as K
+    cb = K.LearningRateWarmupCallback(initial_lr=0.008, warmup_epochs=4)
+    assert cb.multiplier(0.0) == 1.0 and cb.multiplier(10) == 1.0        # size() == 1 here: no scaling to ramp

@@ -16,12 +16,18 @@ pytestmark = [pytest.mark.gpu, pytest.mark.multigpu]
 
 
 def _free_port():
-    s = socket.socket(); s.bind(("127.0.0.1", 0)); p = s.getsockname()[1]; s.close(); return p
+    """(rendezvous port, store port): two distinct ports that are free right now."""
+    a, b = socket.socket(), socket.socket()
+    a.bind(("127.0.0.1", 0)); b.bind(("127.0.0.1", 0))
+    ports = (a.getsockname()[1], b.getsockname()[1])
+    a.close(); b.close()
+    return ports
 
 
 def _worker(rank, world, port, out_dir):
     import ctypes as C
-    os.environ.update(RANK=str(rank), WORLD_SIZE=str(world), MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    os.environ.update(RANK=str(rank), WORLD_SIZE=str(world), MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port[0]),
+                      EWDML_STORE_PORT=str(port[1]))
     from ewdml.parallel.flat import Segment
     from ewdml.parallel.host_codec import HostCodec
     from ewdml.parallel.native_exchange import ExchangePlan, Mailbox, make_codec
@@ -157,7 +163,8 @@ def test_two_gpu_exchange_and_allreduce(tmp_path, world):
 
 
 def _trainer(rank, world, port, out_dir, exchange, method):
-    os.environ.update(RANK=str(rank), WORLD_SIZE=str(world), MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    os.environ.update(RANK=str(rank), WORLD_SIZE=str(world), MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port[0]),
+                      EWDML_STORE_PORT=str(port[1]))
     from ewdml.config import TrainConfig
     from ewdml.parallel.peer import PeerGroup
     from ewdml.train.gpu import GpuTrainer
