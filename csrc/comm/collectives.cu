@@ -81,6 +81,23 @@ __device__ __forceinline__ bool elect_last(uint32_t* counter, int* s_flag) {
     return *s_flag != 0;
 }
 
+// grid-stride copy of n16 16-byte vectors with four loads in flight per thread
+__device__ __forceinline__ void copy16x4(uint8_t* __restrict__ d, const uint8_t* __restrict__ s, int64_t n16, int64_t gtid, int64_t gsize) {
+    for (int64_t i0 = gtid; i0 < n16; i0 += 4 * gsize) {
+        uint4 v[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const int64_t i = i0 + u * gsize;
+            if (i < n16) v[u] = ld_v4(s + (i << 4));
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const int64_t i = i0 + u * gsize;
+            if (i < n16) st_na_v4(d + (i << 4), v[u]);
+        }
+    }
+}
+
 __global__ void __launch_bounds__(512) k_coll(const CollArgs a) {
     __shared__ int s_ok, s_last;
     const int tid = threadIdx.x, W = a.world, me = a.rank;
@@ -97,19 +114,31 @@ __global__ void __launch_bounds__(512) k_coll(const CollArgs a) {
             if (!wait_flag_ge(my_ack + tid, a.ack_need[tid], a.spin_limit, a.err_word, (uint32_t)EWDML_ERR_TIMEOUT)) s_ok = 0;
         __syncthreads();
         if (s_ok) {
+            // four independent 16-byte loads in flight per thread before the first store (the copy is latency bound otherwise)
             if (a.src_stride == 0) {
-                for (int64_t i = gtid; i < n16; i += gsize) {
-                    const uint4 v = ld_v4(a.src + (i << 4));
+                for (int64_t i0 = gtid; i0 < n16; i0 += 4 * gsize) {
+                    uint4 v[4];
 #pragma unroll
-                    for (int p = 0; p < EWDML_MAX_PEERS; ++p)
-                        if (p < W && ((a.put_mask >> p) & 1u)) st_na_v4(slot_ptr(a, p, me) + kHeaderBytes + (i << 4), v);
+                    for (int u = 0; u < 4; ++u) {
+                        const int64_t i = i0 + u * gsize;
+                        if (i < n16) v[u] = ld_v4(a.src + (i << 4));
+                    }
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) {
+                        const int64_t i = i0 + u * gsize;
+                        if (i < n16) {
+#pragma unroll
+                            for (int p = 0; p < EWDML_MAX_PEERS; ++p)
+                                if (p < W && ((a.put_mask >> p) & 1u)) st_na_v4(slot_ptr(a, p, me) + kHeaderBytes + (i << 4), v[u]);
+                        }
+                    }
                 }
             } else {
                 for (int p = 0; p < W; ++p) {
                     if (!((a.put_mask >> p) & 1u)) continue;
                     const uint8_t* s = a.src + (int64_t)p * a.src_stride;
                     uint8_t* d = slot_ptr(a, p, me) + kHeaderBytes;
-                    for (int64_t i = gtid; i < n16; i += gsize) st_na_v4(d + (i << 4), ld_v4(s + (i << 4)));
+                    copy16x4(d, s, n16, gtid, gsize);
                 }
             }
         }
@@ -143,7 +172,7 @@ __global__ void __launch_bounds__(512) k_coll(const CollArgs a) {
                 if (!((a.src_mask >> s) & 1u)) continue;
                 const uint8_t* p = slot_ptr(a, me, s) + kHeaderBytes;
                 uint8_t* d = a.dst + (int64_t)s * a.dst_stride;
-                for (int64_t i = gtid; i < n16; i += gsize) *reinterpret_cast<uint4*>(d + (i << 4)) = ld_v4(p + (i << 4));
+                copy16x4(d, p, n16, gtid, gsize);
             }
         } else if (s_ok && a.consume == CONS_SUM) {
             for (int64_t i = gtid; i < n16; i += gsize) {
@@ -282,7 +311,9 @@ static int run(ewdml_engine* e, int op, int tag, int region, uint32_t seq, uint3
         }
     if (!a.put_mask && !a.src_mask) return 0;
     const int64_t n16 = nbytes >> 4;
-    int grid = (int)std::min<int64_t>(std::max<int64_t>((n16 + 511) / 512, 1), (int64_t)e->sms);
+    // <= 2 CTAs per SM: every CTA of the grid is resident, so CTAs spinning in the wait phase never keep a CTA that still
+    // has to put from being scheduled
+    int grid = (int)std::min<int64_t>(std::max<int64_t>((n16 + 4 * 512 - 1) / (4 * 512), 1), 2 * (int64_t)e->sms);
     k_coll<<<grid, 512, 0, st>>>(a);
     EWDML_LAUNCH_CHECK();
     int64_t out_bytes = 0;

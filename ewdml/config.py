@@ -54,7 +54,7 @@ class TrainConfig:
     seed: int = 1
     log_interval: int = 10
     network: str = "LeNet"
-    mode: str = "normal"
+    mode: str = "normal"            # normal | kill (straggler cut-off) | async (asynchronous parameter server)
     kill_threshold: float = 7.0
     dataset: str = "MNIST"
     comm_type: str = "Bcast"
@@ -134,6 +134,8 @@ class TrainConfig:
             raise ValueError(f"--compressor must be one of {COMPRESSORS}")
         if self.exchange not in EXCHANGES:
             raise ValueError(f"--exchange must be one of {EXCHANGES}")
+        if self.mode not in ("normal", "kill", "async"):
+            raise ValueError("--mode must be normal, kill or async")
         if self.method not in METHODS:
             raise ValueError(f"--method must be in {METHODS}")
         if not (1 <= self.qsgd_levels <= 32768):

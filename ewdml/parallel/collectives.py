@@ -77,11 +77,19 @@ class CollectiveEngine:
         return slot_payload, int(lib.ewdml_engine_window_bytes(world, slot_payload)), int(lib.ewdml_engine_flag_bytes())
 
     @classmethod
-    def create(cls, pg: PeerGroup, slot_payload: int = 4 << 20, name: str = "coll") -> "CollectiveEngine":
-        """Collective over the whole peer group (every rank calls this at the same point)."""
+    def create(cls, pg: PeerGroup, slot_payload: int = 4 << 20, name: str = "coll", heap=None) -> "CollectiveEngine":
+        """Collective over the whole peer group (every rank calls this at the same point).  With ``heap`` (a
+        :class:`ewdml.parallel.peer.SymmetricHeap`) the window and flags are carved out of the already-mapped region,
+        so creating an engine costs no IPC exchange."""
         sp, wbytes, fbytes = cls._sizes(pg.world, slot_payload)
-        win = pg.alloc(name + "_win", wbytes)
-        flags = pg.alloc(name + "_flags", fbytes)
+        if heap is not None:
+            win, flags = heap.alloc(name + "_win", wbytes), heap.alloc(name + "_flags", fbytes)
+            flags.local.zero_()                       # recycled heap memory: flags must start at zero on every rank
+            torch.cuda.synchronize(pg.device)
+            pg.host_barrier(name + "_ready")
+        else:
+            win = pg.alloc(name + "_win", wbytes)
+            flags = pg.alloc(name + "_flags", fbytes)
         return cls(pg.rank, pg.world, win, flags, sp, pg.device)
 
     @classmethod

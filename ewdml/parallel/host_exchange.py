@@ -330,6 +330,60 @@ class PSServerP2P(PSServer):
                 self.dropped += 1
 
 
+class PSServerAsync(PSServerP2P):
+    """Asynchronous parameter server (``--mode async``): the variant the report describes next to the synchronous one
+    (``Report.zip!main.tex:58-59``) but the reference never implements.  Each gradient is applied the moment it
+    arrives and the fresh weights go back to that worker only; workers never wait for each other, so a slow worker
+    costs nobody else anything -- at the price of stale gradients.  One call of ``step`` serves one arrival; the
+    training loop calls it ``workers x steps`` times."""
+
+    def __init__(self, flat, cfg, optimizer, group=None):
+        super().__init__(flat, cfg, optimizer, group)
+        self.staleness: List[int] = []
+        self._version = 0
+        self._seen = {r: 0 for r in range(1, self.world)}
+
+    def step(self, step_idx: int, is_sync_step: bool = True) -> ExchangeStats:
+        import queue
+        if not self._started:
+            self._thread.start()
+            self._started = True
+        st = ExchangeStats()
+        t0 = time.perf_counter()
+        try:
+            item = self._q.get(timeout=self.timeout)
+        except queue.Empty:
+            raise TimeoutError(f"asynchronous parameter server: no gradient for {self.timeout}s (workers died?)")
+        if item[0] == "error":
+            raise RuntimeError(f"parameter server receiver failed: {item[1]}")
+        src, wstep, buf = item
+        self.decoders[src].decode(buf[_HDR:], out=self._avg, accumulate=False)
+        st.t_recv = time.perf_counter() - t0
+        st.bytes_recv = self._nbytes
+        t0 = time.perf_counter()
+        avg = self._avg.to(self.flat.param.device)
+        self.optimizer.step(grads=[self.flat.view(avg, i) for i in range(len(self.flat.segments))])
+        self.staleness.append(self._version - self._seen[src])      # updates applied since this worker last pulled
+        self._version += 1
+        self._seen[src] = self._version
+        msg = self.flat.param.detach().cpu().clone()
+        self._out.append((dist.isend(msg, dst=src, group=self.group, tag=_PULL_TAG), msg))
+        while len(self._out) > 8 * self.num_workers:
+            self._out.pop(0)[0].wait()
+        st.bytes_sent = msg.numel() * 4
+        st.t_send = time.perf_counter() - t0
+        self.used_per_step.append(1)
+        return st
+
+
+class PSWorkerAsync(PSWorkerP2P):
+    """Pushes its gradient, pulls whatever the weights are by then (always a weights pull)."""
+
+    def __init__(self, flat, cfg, optimizer, group=None):
+        super().__init__(flat, cfg, optimizer, group)
+        self.pull_mode = "weights"
+
+
 def _done(work) -> bool:
     try:
         return bool(work.is_completed())
@@ -439,6 +493,8 @@ class AllreduceExchange(Exchange):
 def build_host_exchange(role: str, flat: FlatModel, cfg, optimizer, group=None) -> Exchange:
     if cfg.exchange == "ps":
         world = dist.get_world_size(group) if dist.is_initialized() else 1
+        if cfg.mode == "async":
+            return PSServerAsync(flat, cfg, optimizer, group) if role == "server" else PSWorkerAsync(flat, cfg, optimizer, group)
         if cfg.mode == "kill" or cfg.num_aggregate < world - 1:     # backup workers / straggler cut-off
             return PSServerP2P(flat, cfg, optimizer, group) if role == "server" else PSWorkerP2P(flat, cfg, optimizer, group)
         return PSServer(flat, cfg, optimizer, group) if role == "server" else PSWorker(flat, cfg, optimizer, group)

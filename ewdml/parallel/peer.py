@@ -151,6 +151,55 @@ class PeerGroup:
             self.store = None
 
 
+class SymmetricHeap:
+    """One peer-mapped region + the native deterministic sub-allocator (``ewdml_symheap_*``): after the single IPC
+    exchange that maps the region, ``alloc`` is a purely local call -- every rank performs the same sequence of
+    allocations, so an object sits at the same offset in every rank's region (OSHMEM ``shmalloc`` semantics,
+    ``oshmem/mca/memheap``)."""
+
+    def __init__(self, pg, nbytes: int, name: str = "symheap", align: int = 256):
+        self.pg, self.lib = pg, L.load()
+        self.region = pg.alloc(name, nbytes)          # PeerGroup: one SymmetricBuffer; LocalPeerGroup: one per rank
+        self._regions = self.region if isinstance(self.region, list) else [self.region]
+        self._h = C.c_void_p()
+        L.check(self.lib.ewdml_symheap_create(C.byref(self._h), self._regions[0].nbytes, align), "symheap_create")
+        self._live = {}
+
+    def alloc(self, name: str, nbytes: int):
+        off = int(self.lib.ewdml_symheap_alloc(self._h, int(nbytes)))
+        if off < 0:
+            raise L.NativeError(self.lib.ewdml_last_error().decode(errors="replace"))
+        bufs = []
+        for reg in self._regions:
+            b = SymmetricBuffer.__new__(SymmetricBuffer)
+            b.name, b.nbytes, b.rank = name, (nbytes + 255) // 256 * 256, reg.rank
+            b.ptrs = [p + off for p in reg.ptrs]
+            b.local = reg.local[off:off + b.nbytes]
+            b.heap_offset = off
+            bufs.append(b)
+        out = bufs if isinstance(self.region, list) else bufs[0]
+        self._live[off] = out
+        return out
+
+    def free(self, buf) -> None:
+        b = buf[0] if isinstance(buf, list) else buf
+        L.check(self.lib.ewdml_symheap_free(self._h, b.heap_offset), "symheap_free")
+        self._live.pop(b.heap_offset, None)
+
+    @property
+    def used(self) -> int:
+        return int(self.lib.ewdml_symheap_used(self._h))
+
+    @property
+    def largest_free(self) -> int:
+        return int(self.lib.ewdml_symheap_largest_free(self._h))
+
+    def close(self) -> None:
+        if self._h:
+            self.lib.ewdml_symheap_destroy(self._h)
+            self._h = C.c_void_p()
+
+
 class LocalPeerGroup:
     """``world`` emulated ranks in one process on one GPU; ``alloc`` returns one buffer per rank."""
 

@@ -114,6 +114,13 @@ def load() -> C.CDLL:
         "ewdml_peer_matrix_add": (None, [i32, i64]),
         "ewdml_peer_matrix_get": (i32, [P(i64)]),
         "ewdml_set_trace": (None, [i32]),
+        "ewdml_symheap_create": (i32, [P(vp), i64, i64]),
+        "ewdml_symheap_alloc": (i64, [vp, i64]),
+        "ewdml_symheap_free": (i32, [vp, i64]),
+        "ewdml_symheap_used": (i64, [vp]),
+        "ewdml_symheap_peak": (i64, [vp]),
+        "ewdml_symheap_largest_free": (i64, [vp]),
+        "ewdml_symheap_destroy": (i32, [vp]),
         "ewdml_engine_window_bytes": (i64, [i32, i64]),
         "ewdml_engine_flag_bytes": (i64, []),
         "ewdml_engine_create": (i32, [P(vp), i32, i32, P(vp), P(vp), i64]),

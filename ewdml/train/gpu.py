@@ -153,6 +153,42 @@ class GpuTrainer:
         self.step_idx += 1
         return st
 
+    # -- checkpoint / resume: reference-format state_dict + sidecar with everything a bit-exact resume needs --
+    def save_checkpoint(self, path: str, is_writer: bool = True) -> None:
+        """``path``: plain ``torch.save(state_dict)`` the reference evaluator loads; ``path + ".state"``: step counter,
+        flat momentum buffer, device step state (sequence number / RNG position), error-feedback residual."""
+        from ..utils import checkpoint as ckpt
+        torch.cuda.synchronize(self.device)
+        ckpt.save_model(self.model, path, is_writer)
+        extra = {"momentum": self.flat.momentum.detach().cpu() if self.flat.momentum is not None else None,
+                 "device_state": self.exchange.state.detach().cpu(),
+                 "residual": self.exchange.residual.detach().cpu() if getattr(self.exchange, "residual", None) is not None else None}
+        ckpt.save_sidecar(path, step=self.step_idx, optimizer_state=None, extra=extra, is_writer=is_writer)
+
+    def load_checkpoint(self, path: str) -> int:
+        """Restore weights (+ sidecar when present); returns the step to continue from.  A captured graph stays valid:
+        every buffer is updated in place."""
+        from ..utils import checkpoint as ckpt
+        ckpt.load_model(self.model, path)                 # parameters are views of the flat buffer: copied in place
+        if self.flat.param_bf16 is not None:
+            self.flat.param_bf16.copy_(self.flat.param)
+        side = ckpt.load_sidecar(path)
+        if side is not None:
+            self.step_idx = int(side["step"])
+            ex = side.get("extra") or {}
+            if ex.get("momentum") is not None and self.flat.momentum is not None:
+                self.flat.momentum.copy_(ex["momentum"])
+            if ex.get("device_state") is not None:
+                st = ex["device_state"].to(self.exchange.state.device)
+                if self.world > 1:
+                    # the flag sequence number must stay in step with the peers' mailboxes of THIS job: keep seq, restore the rest
+                    st[0] = self.exchange.state[0]
+                self.exchange.state.copy_(st)
+            if ex.get("residual") is not None and getattr(self.exchange, "residual", None) is not None:
+                self.exchange.residual.copy_(ex["residual"])
+        torch.cuda.synchronize(self.device)
+        return self.step_idx
+
     def input_spec(self):
         c, h, w = input_shape(self.cfg.network)
         return (self.cfg.batch_size, c, h, w)

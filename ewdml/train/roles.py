@@ -215,6 +215,15 @@ class SyncReplicasMaster_NN(NNTrainer):
         period = cfg.resolved_sync_period()
         total = total_steps if total_steps is not None else cfg.max_steps
         stats = []
+        if cfg.mode == "async":
+            # one exchange.step per arriving gradient; every worker pushes once per step of its own
+            n = (total - self.cur_step) * self._num_workers
+            self.exchange.expect(total - self.cur_step)
+            for i in range(n):
+                stats.append(self.exchange.step(i))
+            self.cur_step = total
+            self.exchange.drain()
+            return stats
         if hasattr(self.exchange, "expect"):
             self.exchange.expect(sum(1 for i in range(self.cur_step, total) if i % period == 0))
         for i in range(self.cur_step, total):

@@ -202,6 +202,16 @@ int ewdml_heap_export(void* base, uint8_t handle[64]);           /* cudaIpcMemHa
 int ewdml_heap_import(const uint8_t handle[64], void** mapped);  /* enables peer access lazily  */
 int ewdml_heap_unmap(void* mapped);
 int ewdml_can_access_peer(int dev, int peer, int* out);
+/* Deterministic offset allocator inside one peer-mapped region (OSHMEM memheap analogue): the same alloc/free sequence
+ * gives the same offsets on every rank, so symmetric objects need no rendezvous after the region was exchanged.      */
+typedef struct ewdml_symheap ewdml_symheap;
+int ewdml_symheap_create(ewdml_symheap** out, int64_t bytes, int64_t align);
+int64_t ewdml_symheap_alloc(ewdml_symheap* h, int64_t bytes);      /* offset, or -1 when it does not fit */
+int ewdml_symheap_free(ewdml_symheap* h, int64_t offset);
+int64_t ewdml_symheap_used(const ewdml_symheap* h);
+int64_t ewdml_symheap_peak(const ewdml_symheap* h);
+int64_t ewdml_symheap_largest_free(const ewdml_symheap* h);
+int ewdml_symheap_destroy(ewdml_symheap* h);
 
 /* N1: rendezvous key-value store over TCP (replaces the PMIx modex / ORTE oob,
  * ompi:ompi/runtime/ompi_mpi_init.c:657-724).  Rank 0 hosts the server thread.                  */

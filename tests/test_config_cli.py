@@ -65,3 +65,27 @@ def test_cluster_tool_on_the_local_pseudo_host(tmp_path):
     time.sleep(1.0)
     assert "running" in run("status").stdout
     assert run("kill_all").returncode == 0 and not pids.exists()
+
+
+def test_symmetric_heap_allocator_is_deterministic_and_coalesces():
+    """ewdml_symheap_*: offsets only (no GPU needed); two heaps fed the same sequence agree, frees coalesce."""
+    import ctypes as C
+    from ewdml.runtime import lib as L
+    lib = L.load()
+
+    def run():
+        h = C.c_void_p()
+        L.check(lib.ewdml_symheap_create(C.byref(h), 1 << 20, 256))
+        offs = [lib.ewdml_symheap_alloc(h, n) for n in (1000, 5000, 300)]
+        L.check(lib.ewdml_symheap_free(h, offs[1]))
+        offs += [lib.ewdml_symheap_alloc(h, 2000), lib.ewdml_symheap_alloc(h, 4000)]
+        return h, offs
+
+    (h1, o1), (h2, o2) = run(), run()
+    assert o1 == o2 == [0, 1024, 6144, 1024, 6656]               # first fit reuses the hole, the rest goes behind
+    assert lib.ewdml_symheap_alloc(h1, 1 << 21) == -1 and b"do not fit" in lib.ewdml_last_error()
+    for off in (0, 6144, 1024, 6656):
+        L.check(lib.ewdml_symheap_free(h1, off))
+    assert lib.ewdml_symheap_used(h1) == 0 and lib.ewdml_symheap_largest_free(h1) == 1 << 20   # fully coalesced again
+    assert lib.ewdml_symheap_free(h1, 12345) != 0                 # not a live allocation
+    lib.ewdml_symheap_destroy(h1); lib.ewdml_symheap_destroy(h2)

@@ -176,3 +176,26 @@ def test_argument_errors_are_reported(dev):
         engs[0].all_reduce(torch.zeros(16, dtype=torch.float16, device=dev))
     with pytest.raises(ValueError):
         engs[0].all_gather(torch.zeros(3, device=dev), torch.zeros(6, device=dev))
+
+
+def test_engine_on_symmetric_heap(dev):
+    """Window and flags carved out of one pre-mapped region by the deterministic sub-allocator."""
+    from ewdml.parallel.collectives import CollectiveEngine
+    from ewdml.parallel.peer import PeerGroup, SymmetricHeap
+    pg = PeerGroup(0, 1, dev)
+    heap = SymmetricHeap(pg, 8 << 20)
+    scratch = heap.alloc("scratch", 1 << 20)
+    eng = CollectiveEngine.create(pg, slot_payload=1 << 16, heap=heap)
+    used = heap.used
+    heap.free(scratch)
+    assert heap.used == used - (1 << 20)
+    x = torch.randn(40000, device=dev)
+    y = x.clone()
+    eng.all_reduce(y, scale=3.0)
+    z = torch.zeros_like(x)
+    eng.all_gather(x, z)
+    torch.cuda.synchronize()
+    assert torch.equal(y, 3.0 * x) and torch.equal(z, x)
+    again = heap.alloc("again", 1 << 19)
+    assert again.heap_offset == 0 and again.local.numel() == 1 << 19      # first fit: the freed block is reused
+    assert _device_error() == 0

@@ -121,3 +121,27 @@ def test_poisoned_receive_slots_and_nvtx_ranges_do_not_change_results():
     torch.cuda.synchronize()
     assert torch.equal(clean.flat.param, dirty.flat.param)
     assert clean.check_device_error() == 0
+
+
+def test_gpu_trainer_checkpoint_resume_is_exact(tmp_path):
+    """save_checkpoint / load_checkpoint: a fresh trainer restored from the files continues with exactly the parameters,
+    momentum and random-number position of the original (exchange-only steps on fixed gradients: deterministic)."""
+    a, dev = _setup()
+    gen = torch.Generator(device="cpu").manual_seed(21)
+    gs = [(torch.randn(a.flat.total, generator=gen) * 0.01).to(dev) for _ in range(5)]
+    for g in gs[:3]:
+        _exchange_once(a, g, False)
+        a.step_idx += 1
+    path = str(tmp_path / "model_step_")
+    a.save_checkpoint(path)
+    for g in gs[3:]:
+        _exchange_once(a, g, False)
+    b, _ = _setup()
+    assert b.load_checkpoint(path) == 3
+    assert torch.equal(b.exchange.state.cpu()[1:], torch.tensor([3, 0, 3], dtype=torch.int32))
+    for g in gs[3:]:
+        _exchange_once(b, g, False)
+    torch.cuda.synchronize()
+    assert torch.equal(a.flat.param, b.flat.param) and torch.equal(a.flat.momentum, b.flat.momentum)
+    sd = torch.load(path, map_location="cpu", weights_only=True)       # reference-format file
+    assert "conv1.weight" in sd and sd["conv1.weight"].shape == (64, 3, 3, 3)

@@ -39,7 +39,8 @@ def _run(rank, world, port, cfg_kwargs, out_dir):
         m = SyncReplicasMaster_NN(cfg, world, exchange_factory=factory).build_model(cfg.num_classes())
         stats = m.start(total_steps=total)
         res = {"role": "server", "steps": len(stats), "bytes_recv": [s.bytes_recv for s in stats],
-               "used": getattr(m.exchange, "used_per_step", None), "dropped": getattr(m.exchange, "dropped", None)}
+               "used": getattr(m.exchange, "used_per_step", None), "dropped": getattr(m.exchange, "dropped", None),
+               "staleness": getattr(m.exchange, "staleness", None), "checksum": float(m.flat.param.double().sum())}
     else:
         loader, test_loader = prepare_data(cfg, shard_rank=(rank - 1 if ps else rank), num_shards=nw)
         w = DistributedWorker(cfg, rank, world, exchange_factory=factory).build_model(cfg.num_classes())
@@ -186,3 +187,14 @@ def test_backup_workers_and_straggler_cutoff(tmp_path, mode, kw):
     assert all(len(w["loss"]) == 6 for w in workers)
     assert workers[0]["checksum"] == pytest.approx(workers[1]["checksum"], rel=1e-9)
     assert workers[0]["checksum"] == pytest.approx(workers[2]["checksum"], rel=1e-9)
+
+
+def test_asynchronous_parameter_server(tmp_path):
+    """--mode async: gradients are applied as they arrive, each worker gets fresh weights back; a slow worker does not
+    hold the others up (they finish long before it) and its gradients arrive stale."""
+    res = _launch(4, tmp_path, method=1, mode="async", straggler_rank=3, straggler_delay_s=0.15, max_steps=8)
+    server, workers = res[0], res[1:]
+    assert server["steps"] == 24                                   # 3 workers x 8 steps, one server step per arrival
+    assert max(server["staleness"]) >= 1 and min(server["staleness"]) == 0
+    assert all(len(w["loss"]) == 8 and all(l == l for l in w["loss"]) for w in workers)
+    assert workers[0]["loss"][-1] < workers[0]["loss"][0]
