@@ -21,6 +21,14 @@ def _setup(compute="torch", **kw):
     return GpuTrainer(cfg, dev), dev
 
 
+def _grad(total, gen, dev):
+    """Random gradient whose magnitudes are all distinct (a permutation of 1..n times 2^-28, random signs): exact top-k
+    then has no ties at the threshold, whose resolution by atomic ticket is the one order-dependent step of the kernels."""
+    mag = (torch.randperm(total, generator=gen) + 1).float() * 2.0 ** -28
+    sign = torch.randint(0, 2, (total,), generator=gen).float() * 2 - 1
+    return (mag * sign).to(dev)
+
+
 def _exchange_once(tr, g, overlapped):
     tr.flat.grad.copy_(g)
     ex = tr.exchange
@@ -40,7 +48,7 @@ def test_bucketed_and_overlapped_exchange_is_bit_identical_to_monolithic():
     assert len(mono.exchange.buckets) == 1 and len(buck.exchange.buckets) >= 3
     gen = torch.Generator(device="cpu").manual_seed(3)
     for step in range(3):
-        g = (torch.randn(mono.flat.total, generator=gen) * 0.01).to(dev)
+        g = _grad(mono.flat.total, gen, dev)
         _exchange_once(mono, g, False)
         _exchange_once(buck, g, False)
         _exchange_once(over, g, True)
@@ -115,7 +123,7 @@ def test_poisoned_receive_slots_and_nvtx_ranges_do_not_change_results():
     assert dirty.exchange._poison and not clean.exchange._poison
     gen = torch.Generator(device="cpu").manual_seed(11)
     for step in range(4):
-        g = (torch.randn(clean.flat.total, generator=gen) * 0.01).to(dev)
+        g = _grad(clean.flat.total, gen, dev)
         _exchange_once(clean, g, False)
         _exchange_once(dirty, g, False)
     torch.cuda.synchronize()
@@ -128,7 +136,7 @@ def test_gpu_trainer_checkpoint_resume_is_exact(tmp_path):
     momentum and random-number position of the original (exchange-only steps on fixed gradients: deterministic)."""
     a, dev = _setup()
     gen = torch.Generator(device="cpu").manual_seed(21)
-    gs = [(torch.randn(a.flat.total, generator=gen) * 0.01).to(dev) for _ in range(5)]
+    gs = [_grad(a.flat.total, gen, dev) for _ in range(5)]
     for g in gs[:3]:
         _exchange_once(a, g, False)
         a.step_idx += 1
