@@ -175,7 +175,12 @@ class DistributedWorker(NNTrainer):
                 else:
                     loss.backward()
                     t_comp = time.perf_counter() - t0
-                    st = self.exchange.step(self.cur_step, is_sync_step=(self.cur_step % period == 0))
+                    sync = self.cur_step % period == 0
+                    if hasattr(self.exchange, "state"):     # native kernels: payload size / phase times cost a device sync,
+                        st = self.exchange.step(self.cur_step, is_sync_step=sync,      # so only on the steps that get logged
+                                                want_stats=self.cur_step % max(1, cfg.log_interval) == 0)
+                    else:
+                        st = self.exchange.step(self.cur_step, is_sync_step=sync)
                 p1, p5 = accuracy(logits.detach().float(), y, topk=(1, 5))
                 rec = self.log.log(self.cur_step, loss=float(loss.detach()), prec1=float(p1), prec5=float(p5),
                                    bytes_sent=st.bytes_sent, bytes_recv=st.bytes_recv,
