@@ -71,6 +71,18 @@ def main(argv=None):
     total = planned_steps(cfg, len(train_set), n_workers)
 
     t0 = time.time()
+    if backend == "native" and cfg.graphs:
+        # fast path: GpuTrainer + DeviceFeeder, the whole step replayed from one CUDA graph
+        from ..train.gpu import run_training
+        res = run_training(cfg, rank, world_size, device, total_steps=total)
+        if ps_mode and rank == 0:
+            print("Done sending messages to workers! , total time takken by master " + str(time.time() - t0))
+        else:
+            print("Now the next step is: {}".format(total))
+            print("totla time by worker: {} is {} ".format(rank, time.time() - t0))
+        dist.barrier()
+        dist.destroy_process_group()
+        return res
     if ps_mode and rank == 0:
         master = SyncReplicasMaster_NN(cfg, world_size, device, exchange_factory=exchange_factory)
         master.build_model(num_classes=cfg.num_classes())

@@ -95,7 +95,7 @@ class TrainConfig:
     timeout_s: float = 300.0        # collective timeout for the watchdog
     shard_data: bool = True         # per-rank sharding (reference has none; fix per Appendix A)
     overlap: bool = False           # launch each bucket's exchange from backward (autograd hooks) on a side stream
-    graphs: bool = False            # capture the step in a CUDA graph
+    graphs: bool = False            # --backend native: GpuTrainer fast path, whole step replayed from one CUDA graph
 
     # ------------------------------------------------------------------
     def resolved_compressor(self) -> str:

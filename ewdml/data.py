@@ -116,6 +116,43 @@ def build_datasets(cfg):
                                   seed=1234))
 
 
+def dataset_tensors(ds, name: str) -> Tuple[torch.Tensor, torch.Tensor]:
+    """(normalised fp32 NCHW images, int64 labels) of a whole dataset, for :class:`DeviceFeeder`.  Synthetic sets are stored
+    that way already; torchvision sets are converted from their raw uint8 arrays with the reference's constants
+    (``util.py:22-104``) -- augmentation then happens on the device (:func:`gpu_augment`)."""
+    if isinstance(ds, SyntheticImageDataset):
+        return ds.data, ds.targets
+    import numpy as np
+    raw = np.asarray(ds.data)
+    x = torch.from_numpy(raw)
+    if x.dim() == 3:                       # MNIST [N, H, W]
+        x = x.unsqueeze(1)
+    elif x.shape[-1] in (1, 3):            # CIFAR [N, H, W, C]; SVHN is already [N, C, H, W]
+        x = x.permute(0, 3, 1, 2)
+    _, _, _, _, mean, std = _SHAPES[name]
+    x = x.float().div_(255.0)
+    x = (x - torch.tensor(mean).view(1, -1, 1, 1)) / torch.tensor(std).view(1, -1, 1, 1)
+    labels = getattr(ds, "targets", None)
+    if labels is None:
+        labels = ds.labels
+    return x.contiguous(), torch.as_tensor(np.asarray(labels), dtype=torch.int64)
+
+
+def gpu_augment(x: torch.Tensor, pad: int = 4) -> torch.Tensor:
+    """The reference's CIFAR training augmentation (reflect-pad 4, random 32x32 crop, random horizontal flip,
+    ``util.py:36-47``) applied to a whole device batch: one crop offset and one flip decision per image."""
+    n, c, h, w = x.shape
+    xp = torch.nn.functional.pad(x, (pad, pad, pad, pad), mode="reflect")
+    dy = torch.randint(0, 2 * pad + 1, (n,), device=x.device)
+    dx = torch.randint(0, 2 * pad + 1, (n,), device=x.device)
+    flip = torch.rand(n, device=x.device) < 0.5
+    rows = (dy.view(n, 1) + torch.arange(h, device=x.device).view(1, h))                     # [n, h]
+    cols = (dx.view(n, 1) + torch.arange(w, device=x.device).view(1, w))                     # [n, w]
+    cols = torch.where(flip.view(n, 1), cols.flip(1), cols)
+    idx = (rows.view(n, h, 1) * (w + 2 * pad) + cols.view(n, 1, w)).view(n, 1, h * w).expand(n, c, h * w)
+    return xp.reshape(n, c, -1).gather(2, idx).view(n, c, h, w).contiguous(memory_format=torch.channels_last)
+
+
 def prepare_data(cfg, shard_rank: int = 0, num_shards: int = 1):
     """(train_loader, test_loader) — the ``prepare_data(args)`` entry point of util.py:20.
 
@@ -145,9 +182,10 @@ class _Slot:
 class DeviceFeeder:
     """Pinned-host -> device batch pipeline for the GPU path (double-buffered, copy stream).
 
-    Holds the (sharded) dataset in host memory in NHWC order; every ``next()`` gathers the
-    *following* shuffled batch into a pinned staging buffer, enqueues its H2D copy on a side stream
-    and returns the batch copied one call earlier, so the copy overlaps the previous step's compute.
+    Holds the (sharded) dataset in host memory in NHWC order.  ``next()`` returns the batch whose H2D copy was
+    enqueued earlier; ``mark_consumed()`` -- called right after the step has been launched -- gathers the
+    FOLLOWING shuffled batch into a pinned staging buffer and enqueues its copy on a side stream, so both
+    the host-side gather and the copy overlap the GPU work of the current step.
     Batches are returned as NCHW-shaped channels-last views.  ``h2d_bytes_per_step`` is what
     bench.py reports.
     """

@@ -198,3 +198,63 @@ class GpuTrainer:
         err = C.c_uint32(0)
         L.check(L.load().ewdml_get_device_error(C.byref(err), C.c_void_p(torch.cuda.current_stream().cuda_stream)))
         return err.value
+
+
+def run_training(cfg: TrainConfig, rank: int, world: int, device: torch.device, pg: Optional[PeerGroup] = None,
+                 total_steps: Optional[int] = None):
+    """The command-line trainer's fast path (``distributed_nn.py --enable-gpu --backend native --graphs``): the loop of
+    ``DistributedWorker.train_updated`` / ``SyncReplicasMaster_NN.start_updated`` (``distributed_worker.py:162-239``,
+    ``sync_replicas_master_nn.py:158-177``) on :class:`GpuTrainer` -- device-resident batches from :class:`DeviceFeeder`,
+    the whole step replayed from one CUDA graph, the loss / accuracy read back only on the steps that are logged,
+    reference-format checkpoints every ``eval_freq`` steps.  Returns the list of logged records (workers) or the number of
+    served steps (server)."""
+    from ..data import DeviceFeeder, build_datasets, dataset_tensors, gpu_augment
+    from ..utils.metrics import StepLogger, accuracy, logger
+    from ..utils import checkpoint as ckpt
+    pg = pg or PeerGroup.from_env(device)
+    ps = cfg.exchange == "ps"
+    role = "server" if (ps and rank == 0) else "worker"
+    tr = GpuTrainer(cfg, device, pg, role=role)
+    if cfg.resume:
+        tr.load_checkpoint(cfg.resume)
+    tr.exchange.broadcast_initial_weights(0)
+    n_workers = world - 1 if ps else world
+    total = total_steps if total_steps is not None else cfg.max_steps
+    will_capture = bool(cfg.graphs) and tr.period == 1 and total - tr.step_idx > 3
+    if role == "server":
+        # the workers' capture() runs 3 extra (real) warm-up exchanges the step counter does not see
+        for _ in range(tr.step_idx, total + (3 if will_capture else 0)):
+            tr.server_step()
+        torch.cuda.synchronize(device)
+        return tr.step_idx
+    train_set, _ = build_datasets(cfg)
+    data, targets = dataset_tensors(train_set, cfg.dataset)
+    shard = (rank - 1) if ps else rank
+    feeder = DeviceFeeder(data, targets, cfg.batch_size, device, channels_last=True, seed=cfg.seed,
+                          shard_rank=shard if cfg.shard_data else 0, num_shards=n_workers if cfg.shard_data else 1)
+    augment = gpu_augment if (cfg.dataset in ("Cifar10", "Cifar100") and not hasattr(train_set, "num_classes")) else None
+    log = StepLogger(rank, cfg.metrics_file, cfg.log_interval)
+    writer = rank == (1 if ps else 0)
+    history = []
+    capture_at = tr.step_idx + 3 if will_capture else -1                         # a few eager steps first, then replay
+    for step in range(tr.step_idx, total):
+        x, y = feeder.next()
+        if augment is not None:
+            x = augment(x)
+        if step == capture_at:
+            tr.capture(x, y)                    # runs its own 3 warm-up steps: peers capture at the same step
+        loss, st = tr.step(x, y, want_stats=(tr.graph is None and step % max(1, cfg.log_interval) == 0))
+        feeder.mark_consumed()
+        if step % max(1, cfg.log_interval) == 0:
+            p1, p5 = accuracy(tr.last_logits.float(), y, topk=(1, 5))
+            history.append(log.log(step, loss=float(loss), prec1=float(p1), prec5=float(p5), bytes_sent=st.bytes_sent,
+                                   bytes_recv=st.bytes_recv, dense_bytes=tr.flat.dense_nbytes(), t_send=st.t_send, t_recv=st.t_recv,
+                                   images=int(y.shape[0])))
+        if step % cfg.eval_freq == 0:
+            tr.save_checkpoint(ckpt.model_path(cfg.train_dir, step, cfg.legacy_checkpoint_name), writer)
+    torch.cuda.synchronize(device)
+    err = tr.check_device_error()
+    if err:
+        raise RuntimeError(f"device error word {err:#x} (a peer timed out?)")
+    log.close()
+    return history

@@ -15,6 +15,8 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     ["--network=LeNet", "--dataset=MNIST", "--backend=native", "--exchange=allgather", "--compressor=topk-qsgd", "--topk-ratio=0.1"],
     ["--network=VGG11", "--dataset=Cifar10", "--backend=native", "--exchange=allgather", "--compressor=topk-qsgd",
      "--topk-ratio=0.01", "--compute=native", "--dtype=bf16"],
+    ["--network=VGG11", "--dataset=Cifar10", "--backend=native", "--exchange=allgather", "--compressor=topk-qsgd",
+     "--topk-ratio=0.01", "--compute=native", "--dtype=bf16", "--graphs", "--max-steps=12"],
     ["--network=LeNet", "--dataset=MNIST", "--backend=nccl", "--exchange=allgather", "--compressor=topk-qsgd", "--topk-ratio=0.1"],
 ])
 def test_cli_trainer_on_gpu(tmp_path, extra):
@@ -26,7 +28,7 @@ def test_cli_trainer_on_gpu(tmp_path, extra):
            f"--train-dir={tmp_path}/", f"--metrics-file={tmp_path}/metrics.jsonl"] + extra
     out = subprocess.run(cmd, capture_output=True, text=True, timeout=240, cwd=ROOT, env=env)
     assert out.returncode == 0, (out.stdout[-800:], out.stderr[-1500:])
-    assert "Now the next step is: 6" in out.stdout
+    assert ("Now the next step is: 12" if "--graphs" in extra else "Now the next step is: 6") in out.stdout
     assert os.path.isfile(tmp_path / "model_step_")
     sd = torch.load(tmp_path / "model_step_", map_location="cpu", weights_only=True)
     assert all(torch.isfinite(v).all() for v in sd.values() if v.is_floating_point())
