@@ -1,14 +1,17 @@
 // K1: fused select + QSGD quantise + bit-pack + peer store ("sparse allgather send").
 //
-// One CTA per 8192-element tile (full read #2 of the gradient).  Each thread keeps its 32 elements in
-// registers (eight coalesced 16-byte loads); warp ballots turn the per-element selection into the
-// tile's bitmap in a bit-sliced order, a block scan of the word popcounts gives ordered output
-// positions, and the tile's chunk
+// Persistent CTAs (2 per SM) walk the 8192-element tiles (full read #2 of the gradient), prefetching the next tile
+// into registers.  Thread t owns the 16-byte vectors t, t+256, ... of a tile (eight coalesced loads), so the
+// selection test on its registers IS bitmap word t (bit 4j+q <-> element (t+256j)*4+q; the decoder uses the same
+// "thread-major" mapping).  A block scan of the word popcounts gives ordered output positions.  Dense-ish tiles
+// (BITMAP mode) pack their codes behind the bitmap; IDX16 tiles under top-k (about 1 % of the elements) take a
+// sparse path that gathers (index, value) pairs in shared memory with shared-memory atomics instead of running
+// 32 predicated pack blocks per warp.  The tile's chunk
 //     [u16 local index x cnt]  (IDX16 mode only)   [bit-packed codes x cnt]
-// is assembled in shared memory, given a byte range of the payload by ONE atomicAdd, and written
-// with 16-byte stores straight into the receive slot of every destination over NVLink (or local
-// memory for the own slot).  The last CTA to finish publishes header + per-destination flag with
-// release semantics; there is no separate pack buffer, copy kernel or collective call.
+// goes to a FIXED slot (tile * chunk_stride, worst-case sized: no global allocator atomic; only the bytes produced
+// are written or read) with 16-byte stores straight into the receive slot of every destination over NVLink (or
+// local memory for the own slot).  The last CTA to finish publishes header + per-destination flag with release
+// semantics; there is no separate pack buffer, copy kernel or collective call.
 //
 // Replaces: Compresssor/qsgd.py:12-32 (8 elementwise kernels + RNG), Compresssor/TopK.py:5-10
 // (topk + gather), the D2H copy and dist.gather per tensor (distributed_worker.py:317-351), and on
