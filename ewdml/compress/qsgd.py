@@ -43,7 +43,9 @@ def qsgd_quantize(t: torch.Tensor, s: int, u: torch.Tensor, norm: Optional[torch
         norm = t.norm()
     norm = norm.reshape(()).to(torch.float32)
     if float(norm) == 0.0 or not math.isfinite(float(norm)):
-        return torch.zeros_like(t), norm.reshape(1)
+        # zero tensor, or a sum of squares that overflows fp32: nothing is sent and the receiver reconstructs zeros
+        # (the reference divides by the norm unguarded, qsgd.py:21; a non-finite norm would decode to NaN)
+        return torch.zeros_like(t), torch.zeros(1, dtype=torch.float32)
     scale = torch.tensor(float(s), dtype=torch.float32) / norm      # s / norm first, as the reference
     lf = scale * t.abs()
     prev = lf.floor()
