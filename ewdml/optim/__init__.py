@@ -1,5 +1,5 @@
 from .sgd import SGD
-from .adam import Adam
+from .adam import Adam, FlatAdam
 
 
 def build_optimizer(cfg, params):

@@ -51,3 +51,39 @@ class Adam(Optimizer):
                 p.addcdiv_(st["exp_avg"], denom, value=-group["lr"] * math.sqrt(bc2) / bc1)
             offset += len(group["params"])
         return loss
+
+
+class FlatAdam:
+    """Adam on the flat parameter buffer of :class:`ewdml.parallel.flat.FlatModel` (one fused sequence of whole-model
+    tensor ops instead of a Python loop over parameters).  The step counter lives in a device tensor and every operation
+    is a tensor op, so the update can be captured in a CUDA graph together with the exchange that produced the gradient.
+    Same arithmetic as :class:`Adam` (bias-corrected, optional L2 weight decay); used by the native exchanges when
+    ``--optimizer adam`` is selected (their fused epilogue implements momentum-SGD only)."""
+
+    def __init__(self, param: torch.Tensor, lr: float = 1e-3, betas=(0.9, 0.999), eps: float = 1e-8,
+                 weight_decay: float = 0.0, param_bf16: Optional[torch.Tensor] = None):
+        self.param, self.param_bf16 = param, param_bf16
+        self.lr, self.betas, self.eps, self.weight_decay = lr, betas, eps, weight_decay
+        self.exp_avg = torch.zeros_like(param)
+        self.exp_avg_sq = torch.zeros_like(param)
+        self.t = torch.zeros((), dtype=torch.float64, device=param.device)
+
+    @torch.no_grad()
+    def step(self, grad: torch.Tensor) -> None:
+        b1, b2 = self.betas
+        self.t.add_(1.0)
+        g = grad if self.weight_decay == 0 else grad.add(self.param, alpha=self.weight_decay)
+        self.exp_avg.mul_(b1).add_(g, alpha=1 - b1)
+        self.exp_avg_sq.mul_(b2).addcmul_(g, g, value=1 - b2)
+        bc1 = 1.0 - torch.pow(torch.tensor(b1, dtype=torch.float64, device=self.t.device), self.t)
+        bc2 = 1.0 - torch.pow(torch.tensor(b2, dtype=torch.float64, device=self.t.device), self.t)
+        step_size = (self.lr * torch.sqrt(bc2) / bc1).to(torch.float32)
+        self.param.sub_(self.exp_avg / self.exp_avg_sq.sqrt().add_(self.eps) * step_size)
+        if self.param_bf16 is not None:
+            self.param_bf16.copy_(self.param)
+
+    def state_dict(self):
+        return {"exp_avg": self.exp_avg, "exp_avg_sq": self.exp_avg_sq, "t": self.t}
+
+    def load_state_dict(self, sd) -> None:
+        self.exp_avg.copy_(sd["exp_avg"]); self.exp_avg_sq.copy_(sd["exp_avg_sq"]); self.t.copy_(sd["t"])

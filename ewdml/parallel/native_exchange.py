@@ -206,6 +206,13 @@ class _NativeBase(Exchange):
         self._host_seq = 0                                 # eager-mode mirror of state[0], for the poison aid only
         if registry.get("trace"):
             self.lib.ewdml_set_trace(1)
+        # the fused receive epilogue implements momentum-SGD; with --optimizer adam the kernels deliver the dense averaged
+        # gradient instead and a flat whole-model Adam update (tensor ops, graph-capturable) follows
+        self.adam = None
+        if getattr(cfg, "optimizer", "sgd") == "adam":
+            from ..optim.adam import FlatAdam
+            self.adam = FlatAdam(flat.param, lr=cfg.lr, weight_decay=cfg.weight_decay, param_bf16=flat.param_bf16)
+            self._dense = torch.zeros_like(flat.param)
 
     def broadcast_initial_weights(self, src: int = 0) -> None:
         if self.world == 1:
@@ -257,6 +264,9 @@ class _NativeBase(Exchange):
                 "state_advance")
 
     def _sgd_apply(self) -> None:
+        if self.adam is not None:
+            self.adam.step(self.flat.grad)
+            return
         sgd = make_sgd(self.cfg, False)
         f = self.flat
         L.check(self.lib.ewdml_sgd_apply_state(C.c_void_p(f.grad.data_ptr()), C.c_void_p(f.param.data_ptr()),
@@ -322,8 +332,11 @@ class NativeAllgather(_NativeBase):
             lo, hi = self.buckets[b]
             o0, o1 = self.flat.segments[lo].offset, self.flat.segments[hi - 1].offset + self.flat.segments[hi - 1].numel
             self.residual[o0:o1].sub_(self._own[o0:o1])
-        self.plans[b].recv_apply_state([(mb.slot(me, 0, r), mb.flag(me, 0, r)) for r in range(W)],
-                                       [(mb.slot(me, 1, r), mb.flag(me, 1, r)) for r in range(W)], self.state, float(W),
+        srcs = ([(mb.slot(me, 0, r), mb.flag(me, 0, r)) for r in range(W)], [(mb.slot(me, 1, r), mb.flag(me, 1, r)) for r in range(W)])
+        if self.adam is not None:       # dense average of this bucket's tensors; Adam runs once after the last bucket
+            self.plans[b].recv_apply_state(srcs[0], srcs[1], self.state, float(W), L.OUT_GRAD, out=self._dense)
+            return
+        self.plans[b].recv_apply_state(srcs[0], srcs[1], self.state, float(W),
                                        L.OUT_SGD, make_sgd(self.cfg, False), self.flat.param, self.flat.momentum,
                                        self.flat.param_bf16)
 
@@ -347,6 +360,8 @@ class NativeAllgather(_NativeBase):
         for b in range(len(self.plans) - 1, -1, -1):
             self._recv(b)
             self._poison_slots(self.mbs[b], W)
+        if self.adam is not None:
+            self.adam.step(self._dense)
         self._range(None)
         self._rec(2, cur)
         return self._finish_stats(ExchangeStats(), self.plans, W - 1, W - 1, want_stats)
@@ -373,6 +388,8 @@ class NativeAllgather(_NativeBase):
 
     def finish_overlap(self, want_stats: bool = False) -> ExchangeStats:
         torch.cuda.current_stream().wait_stream(self.side)
+        if self.adam is not None:
+            self.adam.step(self._dense)
         W = self.world
         if want_stats:      # payload size only: the phases overlap backward, so there is no separate send / receive time
             self._last_payload = sum(p.stats()["payload_bytes"] for p in self.plans)
@@ -413,6 +430,9 @@ class NativePSWorker(_NativeBase):
             if self.pull_mode == "weights":
                 self.pull.recv_apply_state(src[0], src[1], self.state, 1.0, L.OUT_ASSIGN, param=self.flat.param,
                                            param_bf16=self.flat.param_bf16)
+            elif self.adam is not None:
+                self.pull.recv_apply_state(src[0], src[1], self.state, 1.0, L.OUT_GRAD, out=self._dense)
+                self.adam.step(self._dense)
             else:
                 self.pull.recv_apply_state(src[0], src[1], self.state, 1.0, L.OUT_SGD, sgd, self.flat.param,
                                            self.flat.momentum, self.flat.param_bf16)
@@ -422,8 +442,12 @@ class NativePSWorker(_NativeBase):
         srcs = [[(push.slot(0, par, r), push.flag(0, par, r)) for r in range(1, W)] for par in (0, 1)]
         dests = [[(pull.slot(r, par, 0), pull.flag(r, par, 0)) for r in range(1, W)] for par in (0, 1)]
         if self.pull_mode == "weights":
-            self.push.recv_apply_state(srcs[0], srcs[1], self.state, float(self.num_workers), L.OUT_SGD, sgd,
-                                       self.flat.param, self.flat.momentum, self.flat.param_bf16)
+            if self.adam is not None:
+                self.push.recv_apply_state(srcs[0], srcs[1], self.state, float(self.num_workers), L.OUT_GRAD, out=self._dense)
+                self.adam.step(self._dense)
+            else:
+                self.push.recv_apply_state(srcs[0], srcs[1], self.state, float(self.num_workers), L.OUT_SGD, sgd,
+                                           self.flat.param, self.flat.momentum, self.flat.param_bf16)
             self._rec(1, cur)
             self.pull.send_state(self.flat.param, dests[0], dests[1], self.state, self.cfg.seed, 0)
         else:

@@ -162,7 +162,9 @@ class GpuTrainer:
         ckpt.save_model(self.model, path, is_writer)
         extra = {"momentum": self.flat.momentum.detach().cpu() if self.flat.momentum is not None else None,
                  "device_state": self.exchange.state.detach().cpu(),
-                 "residual": self.exchange.residual.detach().cpu() if getattr(self.exchange, "residual", None) is not None else None}
+                 "residual": self.exchange.residual.detach().cpu() if getattr(self.exchange, "residual", None) is not None else None,
+                 "adam": {k: v.detach().cpu() for k, v in self.exchange.adam.state_dict().items()}
+                 if getattr(self.exchange, "adam", None) is not None else None}
         ckpt.save_sidecar(path, step=self.step_idx, optimizer_state=None, extra=extra, is_writer=is_writer)
 
     def load_checkpoint(self, path: str) -> int:
@@ -186,6 +188,8 @@ class GpuTrainer:
                 self.exchange.state.copy_(st)
             if ex.get("residual") is not None and getattr(self.exchange, "residual", None) is not None:
                 self.exchange.residual.copy_(ex["residual"])
+            if ex.get("adam") is not None and getattr(self.exchange, "adam", None) is not None:
+                self.exchange.adam.load_state_dict(ex["adam"])
         torch.cuda.synchronize(self.device)
         return self.step_idx
 

@@ -153,3 +153,22 @@ def test_gpu_trainer_checkpoint_resume_is_exact(tmp_path):
     assert torch.equal(a.flat.param, b.flat.param) and torch.equal(a.flat.momentum, b.flat.momentum)
     sd = torch.load(path, map_location="cpu", weights_only=True)       # reference-format file
     assert "conv1.weight" in sd and sd["conv1.weight"].shape == (64, 3, 3, 3)
+
+
+def test_adam_on_the_native_exchange_matches_flat_adam_on_the_decoded_gradient():
+    """--optimizer adam: the receive kernel delivers the dense averaged gradient and FlatAdam applies it."""
+    from ewdml.optim import FlatAdam
+    tr, dev = _setup(optimizer="adam", bucket_size=4 << 20)
+    ex = tr.exchange
+    assert ex.adam is not None
+    ref = FlatAdam(tr.flat.param.detach().clone(), lr=tr.cfg.lr)
+    gen = torch.Generator(device="cpu").manual_seed(8)
+    for step in range(3):
+        _exchange_once(tr, _grad(tr.flat.total, gen, dev), False)
+        torch.cuda.synchronize()
+        k = sum(max(1, int(s.numel * 0.01)) for s in tr.flat.segments)
+        assert 0 < int((ex._dense != 0).sum()) <= k
+        ref.step(ex._dense)
+    assert torch.allclose(ref.param, tr.flat.param, atol=1e-6)
+    assert torch.equal(tr.flat.param_bf16.float(), tr.flat.param.to(torch.bfloat16).float()) if tr.flat.param_bf16 is not None else True
+    assert tr.check_device_error() == 0

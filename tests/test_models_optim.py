@@ -103,3 +103,28 @@ def test_adam_external_numpy_grads_matches_torch():
         p2[0].grad = g.clone()
         o1.step(grads=[g.numpy()]); o2.step()
     assert torch.allclose(p1[0], p2[0], atol=1e-6)
+
+
+def test_flat_adam_matches_per_parameter_adam():
+    """FlatAdam (whole-model tensor ops on the flat buffer, used by the native exchanges with --optimizer adam) computes
+    what the external-gradient Adam computes parameter by parameter."""
+    import torch
+    from ewdml.models import build_model
+    from ewdml.optim import Adam, FlatAdam
+    from ewdml.parallel.flat import FlatModel
+    torch.manual_seed(0)
+    f = FlatModel(build_model("LeNet", 10))
+    ref = [torch.nn.Parameter(p.detach().clone()) for p in f.params]
+    opt, fa = Adam(ref, lr=0.01, weight_decay=0.001), FlatAdam(f.param, lr=0.01, weight_decay=0.001)
+    for _ in range(5):
+        g = torch.randn(f.total) * 0.1
+        for a, b in zip(f.segments[:-1], f.segments[1:]):
+            g[a.offset + a.numel:b.offset] = 0
+        opt.step(grads=[f.view(g, i).clone() for i in range(len(f.segments))])
+        fa.step(g)
+    for p, q in zip(ref, f.params):
+        assert torch.allclose(p.detach(), q.detach(), atol=1e-6)
+    sd = {k: v.clone() for k, v in fa.state_dict().items()}
+    fb = FlatAdam(f.param.clone())
+    fb.load_state_dict(sd)
+    assert float(fb.t) == 5.0 and torch.equal(fb.exp_avg, fa.exp_avg)
