@@ -187,10 +187,12 @@ class DistributedWorker(NNTrainer):
                                    dense_bytes=self.flat.dense_nbytes(), t_send=st.t_send,
                                    t_recv=st.t_recv, t_compute=t_comp, images=int(y.shape[0]))
                 self.history.append(rec)
-                if self.cur_step % cfg.eval_freq == 0:
-                    self._save_model(self._generate_model_path(), self.is_checkpoint_writer)
-                self.cur_step += 1
+                finished = self.cur_step
+                self.cur_step += 1                      # from here on: the NEXT step to run (what the sidecar records)
                 self.next_step = self.cur_step
+                if finished % cfg.eval_freq == 0:
+                    self._save_model(ckpt.model_path(cfg.train_dir, finished, cfg.legacy_checkpoint_name),
+                                     self.is_checkpoint_writer)
             if done:
                 break
         self.log.close()

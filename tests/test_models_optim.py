@@ -128,3 +128,36 @@ def test_flat_adam_matches_per_parameter_adam():
     fb = FlatAdam(f.param.clone())
     fb.load_state_dict(sd)
     assert float(fb.t) == 5.0 and torch.equal(fb.exp_avg, fa.exp_avg)
+
+
+def test_single_process_trainer_and_resume(tmp_path):
+    """NNTrainer (nn_ops.py) trains; DistributedWorker writes model_step_ + sidecar; --resume restores the weights, the
+    momentum buffers and the step counter, and training continues from the NEXT step."""
+    import torch
+    from ewdml.config import TrainConfig
+    from ewdml.data import prepare_data
+    from ewdml.train.roles import DistributedWorker, NNTrainer
+    from ewdml.utils import checkpoint as ckpt
+    base = dict(network="LeNet", dataset="MNIST", batch_size=16, lr=0.05, momentum=0.9, data="synthetic", synthetic_size=128,
+                exchange="allgather", compressor="none", eval_freq=3, train_dir=str(tmp_path) + "/", log_interval=100)
+    cfg = TrainConfig(max_steps=3, epochs=1, **base).validate()
+    loader, test = prepare_data(cfg)
+    t = NNTrainer(cfg).build_model(10)
+    before = t.flat.param.clone()
+    t.train_and_validate(loader, test)
+    assert t.cur_step == 3 and not torch.equal(before, t.flat.param)
+
+    w = DistributedWorker(TrainConfig(max_steps=5, epochs=2, **base).validate(), 0, 1).build_model(10)
+    w.train(loader, test, total_steps=5)                      # checkpoints after steps 0 and 3
+    path = ckpt.model_path(cfg.train_dir)
+    side = ckpt.load_sidecar(path)
+    assert side["step"] == 4 and side["optimizer"]["state"]
+    r = DistributedWorker(TrainConfig(max_steps=6, epochs=2, resume=path, **base).validate(), 0, 1).build_model(10)
+    assert r.cur_step == 4
+    sd = torch.load(path, weights_only=True)
+    assert all(torch.equal(sd[k], v.detach()) for k, v in r.network.state_dict().items())
+    mom_saved = side["optimizer"]["state"][0]["momentum_buffer"]
+    mom_now = r.optimizer.state_dict()["state"][0]["momentum_buffer"]
+    assert torch.equal(mom_saved, mom_now)
+    hist = r.train(loader, test, total_steps=6)
+    assert [h["step"] for h in hist] == [4, 5]
