@@ -8,9 +8,9 @@ from _cfg import config_from_kwargs
 
 def update_params_dist_version(param, avg_grad, learning_rate):
     """Plain SGD on one layer (``sync_replicas_master_nn.py:24-30``)."""
-    assert param.shape == avg_grad.shape
-    param -= learning_rate * avg_grad
-    return param
+    if tuple(param.shape) != tuple(avg_grad.shape):
+        raise ValueError(f"shape mismatch: {tuple(param.shape)} vs {tuple(avg_grad.shape)}")
+    return param.sub_(avg_grad, alpha=float(learning_rate))
 
 
 class GradientAccumulator(object):
@@ -29,16 +29,17 @@ class GradientAccumulator(object):
             self.model_index_range.append(i)
             off += p.numel()
 
-    def meset_everything(self):
-        self._meset_grad_counter()
-        self._meset_grad_aggregator()
-
+    # (method names, including the reference's spelling, kept for callers)
     def _meset_grad_counter(self):
-        self.gradient_aggregate_counter = [0 for _ in self.gradient_aggregate_counter]
+        self.gradient_aggregate_counter = [0] * len(self.gradient_aggregator)
 
     def _meset_grad_aggregator(self):
-        if self._mode != "compress":
+        if self._mode != "compress":          # one memset of the single backing allocation clears every slot
             self._flat.zero_()
+
+    def meset_everything(self):
+        self._meset_grad_aggregator()
+        self._meset_grad_counter()
 
 
 class SyncReplicasMaster_NN(_Master):
