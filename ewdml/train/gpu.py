@@ -65,6 +65,14 @@ class GpuTrainer:
         if cfg.overlap and role == "worker" and hasattr(self.exchange, "begin_overlap") and self.period == 1:
             from ..parallel.overlap import BucketScheduler
             self.sched = BucketScheduler(self.flat.params, self.exchange.buckets, self.exchange.bucket_ready).install()
+        if role == "worker":
+            from ..utils.metrics import logger
+            if cfg.overlap and self.sched is None:
+                logger.warning("--overlap is implemented for --exchange allgather with sync_period 1; running %s without it",
+                               cfg.exchange)
+            if cfg.error_feedback and getattr(self.exchange, "residual", None) is None and cfg.resolved_compressor() != "none":
+                logger.warning("--error-feedback is implemented for --exchange allgather on the native backend; ignored for %s",
+                               cfg.exchange)
         self.graph = None
         self.graph_launches = 0          # launches of this repo's kernels inside one captured step
         self.replays = 0
