@@ -409,7 +409,12 @@ int gemm_dispatch(const void* A, const void* B, void* C, int M, int N, int K, in
     EWDML_CHECK_ARG(A && B && C && M > 0 && N > 0 && K > 0);
     EWDML_CHECK_ARG(lda % 8 == 0 && ldb % 8 == 0 && ((uintptr_t)A % 16) == 0 && ((uintptr_t)B % 16) == 0);
     EWDML_CHECK_ARG(out_mode >= 0 && out_mode <= 2);
-    const int bn = bn_force ? bn_force : (N <= 64 ? 64 : 128);
+    int bn = bn_force ? bn_force : (N <= 64 ? 64 : 128);
+    // EXPERIMENTAL, off unless EWDML_GEMM_BN=256: 128x256 tiles (N = 256 UMMA, 256 TMEM columns, 4 x 48 KB stages, one CTA
+    // per SM) halve the A-operand traffic of layers with >= 256 output channels -- the L2 -> smem traffic is what ncu shows
+    // these GEMMs waiting on (profiles/ncu_prof_gemm.txt).  Compiled and resource-checked, NOT yet validated on a GPU.
+    static const int bn_env = getenv("EWDML_GEMM_BN") ? atoi(getenv("EWDML_GEMM_BN")) : 0;
+    if (!bn_force && bn_env == 256 && !A_MN && N % 256 == 0) bn = 256;
     GemmArgs g;
     memset(&g, 0, sizeof(g));
     if (cm) g.cm = *cm;
@@ -447,6 +452,9 @@ int gemm_dispatch(const void* A, const void* B, void* C, int M, int N, int K, in
     // there is no second resident CTA to hide that latency, so use the whole shared memory for a deep ring instead.
     const int ctas = tiles * split;
     const bool deep = ctas <= 160;
+    if constexpr (!A_MN) {
+        if (bn == 256) return launch<256, 4, A_MN, B_MN>(tA, tB, g, split, st);
+    }
     if (bn == 64) return deep ? launch<64, 8, A_MN, B_MN>(tA, tB, g, split, st) : launch<64, 4, A_MN, B_MN>(tA, tB, g, split, st);
     return deep ? launch<128, 6, A_MN, B_MN>(tA, tB, g, split, st) : launch<128, 3, A_MN, B_MN>(tA, tB, g, split, st);
 }

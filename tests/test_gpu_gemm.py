@@ -82,3 +82,11 @@ def test_gemm_mn_major_operands(M, N, K, a_mn, b_mn):
     torch.cuda.synchronize()
     tol = 2e-3 * ref.abs().max().item() + 1e-3
     assert (out - ref).abs().max().item() <= tol
+
+
+@pytest.mark.skipif(__import__("os").environ.get("EWDML_GEMM_BN") != "256",
+                    reason="experimental 128x256 tiles: run the file with EWDML_GEMM_BN=256 (the variable is read once per process)")
+@pytest.mark.parametrize("M,N,K", [(2048, 512, 4608), (8192, 256, 1152), (512, 512, 4608), (12800, 256, 2304)])
+def test_gemm_bn256_experimental(M, N, K):
+    """EWDML_GEMM_BN=256 python -m pytest tests/test_gpu_gemm.py -k bn256 : same oracle as the default tiles."""
+    test_gemm_bf16_out(M, N, K)
