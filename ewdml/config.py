@@ -192,11 +192,11 @@ class Registry:
 
 
 registry = Registry()
-registry.register("select_tile", 8192, "elements per tile in the select/encode kernels")
-registry.register("exchange_ctas", 0, "CTAs for the exchange kernels (0 = 2 x SM count)")
-registry.register("spin_limit", 1 << 24, "device-side flag spin iteration cap before the error word is set")
-registry.register("allreduce_algo", "auto", "dense allreduce algorithm: auto | oneshot | twoshot")
-registry.register("oneshot_max_bytes", 1 << 20, "auto: use one-shot allreduce at or below this size")
+registry.register("spin_limit", 1 << 24, "device-side flag spin iteration cap before the error word is set (read by the library)")
+registry.register("allreduce_algo", "auto", "fused dense allreduce (K4): auto | oneshot | twoshot")
+registry.register("coll_allreduce_algo", "auto", "collective engine allreduce: auto | oneshot | twoshot (read by the library)")
+registry.register("coll_oneshot_max_bytes", 1 << 18, "collective engine: one-shot allreduce at or below this size (read by the library)")
+registry.register("gemm_bn", 0, "experimental GEMM tile width: 256 = 128x256 tiles where N % 256 == 0 (read by the library)")
 registry.register("trace", False, "print one line per native collective call (libompitrace analogue)")
 registry.register("nvtx", False, "emit NVTX ranges around exchange phases")
 registry.register("debug_poison", False, "poison receive slots after consumption (debug build aid)")

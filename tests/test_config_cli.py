@@ -44,7 +44,7 @@ def test_env_override_precedence(monkeypatch):
     r = Registry()
     assert r.register("my_tunable", 3, "x") == 7 and r.dump()["my_tunable"]["source"] == "env"
     r.set("my_tunable", "9"); assert r.get("my_tunable") == 9
-    assert "select_tile" in registry.dump()
+    assert "spin_limit" in registry.dump()
 
 
 def test_cluster_tool_on_the_local_pseudo_host(tmp_path):

@@ -30,7 +30,7 @@ def test_launcher_tears_job_down_on_failure():
 def test_info_tool_and_adasum_pair():
     out = subprocess.run([sys.executable, "-m", "ewdml.cli.info"], capture_output=True, text=True, timeout=120, cwd=ROOT)
     info = json.loads(out.stdout)
-    assert "select_tile" in info["tunables"] and info["flags"]["network"] == "LeNet"
+    assert "spin_limit" in info["tunables"] and "coll_allreduce_algo" in info["tunables"] and info["flags"]["network"] == "LeNet"
     from ewdml.parallel.hvd import _adasum_pair
     a = torch.tensor([1.0, 0.0]); b = torch.tensor([0.0, 1.0])
     assert torch.allclose(_adasum_pair(a, b), a + b)                 # orthogonal -> sum
