@@ -11,9 +11,15 @@ compressor  per-segment message
 =========== ==================================================================================
 none        ``numel`` fp32
 qsgd        norm fp32 + ``numel`` packed signed levels            (``qsgd.py:12-32``)
-topk        ``k`` fp32 values + ``k`` int32 indices               (``TopK.py:5-10``)
-topk-qsgd   norm fp32 + ``k`` packed signed levels + ``k`` int32  (``qsgd.py:14-15`` enabled)
+topk        ``k`` fp32 values + index block                       (``TopK.py:5-10``)
+topk-qsgd   norm fp32 + ``k`` packed signed levels + index block  (``qsgd.py:14-15`` enabled)
 =========== ==================================================================================
+
+The index block is whichever is smaller for the segment's (numel, k): a bitmap of ``numel`` bits, or a list of
+``k`` indices (uint16 when ``numel <= 65536``, else int32); values / levels are stored in ascending index order.
+Both sizes depend only on (numel, k), so messages stay fixed-size.  This mirrors the two sparse wire modes of the
+GPU kernels (BITMAP above 1/16 density, 16-bit tile-local indices below) and is what makes the plumbing path's
+byte counts comparable with the reference's accounting (value and index "1 byte each", ``Report.zip!Comm Cost.png``).
 
 Signed levels in ``[-s, s]`` are stored as int8 when ``s <= 127``, as uint8 magnitude plus a
 bit-packed sign plane when ``s <= 255`` (the reference default s = 128), else int16.
@@ -42,6 +48,37 @@ def _levels_nbytes(n: int, s: int) -> int:
     if s <= 255:
         return _r4(n + (n + 7) // 8)
     return _r4(2 * n)
+
+
+def _index_nbytes(n: int, k: int) -> int:
+    return min(_r4((n + 7) // 8), _r4(k * (2 if n <= 65536 else 4)))
+
+
+def _index_is_bitmap(n: int, k: int) -> bool:
+    return _r4((n + 7) // 8) <= _r4(k * (2 if n <= 65536 else 4))
+
+
+def _pack_index(idx_sorted: torch.Tensor, n: int, k: int) -> torch.Tensor:
+    out = torch.zeros(_index_nbytes(n, k), dtype=torch.uint8)
+    if _index_is_bitmap(n, k):
+        bits = np.zeros(n, dtype=np.uint8)
+        bits[idx_sorted.numpy()] = 1
+        raw = torch.from_numpy(np.packbits(bits, bitorder="little"))
+    elif n <= 65536:
+        raw = torch.from_numpy(idx_sorted.numpy().astype(np.uint16)).view(torch.uint8)
+    else:
+        raw = idx_sorted.to(torch.int32).view(torch.uint8)
+    out[:raw.numel()] = raw
+    return out
+
+
+def _unpack_index(buf: torch.Tensor, n: int, k: int) -> torch.Tensor:
+    if _index_is_bitmap(n, k):
+        bits = np.unpackbits(buf[:(n + 7) // 8].numpy(), bitorder="little")[:n]
+        return torch.from_numpy(np.flatnonzero(bits).astype(np.int64))
+    if n <= 65536:
+        return torch.from_numpy(buf[:2 * k].numpy().view(np.uint16).astype(np.int64))
+    return buf[:4 * k].clone().view(torch.int32).long()
 
 
 def _pack_levels(q: torch.Tensor, s: int) -> torch.Tensor:
@@ -100,10 +137,11 @@ class HostCodec:
         if c == "qsgd":
             return 4 + _levels_nbytes(n, self.s)
         if c == "topk":
-            return 8 * self._k(seg)
+            k = self._k(seg)
+            return 4 * k + _index_nbytes(n, k)
         if c == "topk-qsgd":
             k = self._k(seg)
-            return 4 + _levels_nbytes(k, self.s) + 4 * k
+            return 4 + _levels_nbytes(k, self.s) + _index_nbytes(n, k)
         raise ValueError(c)
 
     def _norm(self, t: torch.Tensor):
@@ -130,16 +168,21 @@ class HostCodec:
             elif c == "topk":
                 vals, idx = sparsify(g, self.ratio)
                 k = vals.numel()
-                dst[:4 * k].copy_(vals.contiguous().view(torch.uint8))
-                dst[4 * k:].copy_(idx.to(torch.int32).view(torch.uint8))
+                idx, order = torch.sort(idx)
+                dst[:4 * k].copy_(vals[order].contiguous().view(torch.uint8))
+                dst[4 * k:].copy_(_pack_index(idx, seg.numel, k))
             else:  # topk-qsgd
                 vals, idx = sparsify(g, self.ratio)
                 k = vals.numel()
-                q, norm = qsgd_quantize(vals, self.s, self._uniform(idx + seg.offset, step), norm=self._norm(vals))
+                norm = self._norm(vals)
+                if norm is None:
+                    norm = vals.norm()                  # before sorting: the same summation order as the unsorted oracle
+                idx, order = torch.sort(idx)
+                q, norm = qsgd_quantize(vals[order], self.s, self._uniform(idx + seg.offset, step), norm=norm)
                 lb = _levels_nbytes(k, self.s)
                 dst[:4].copy_(norm.view(torch.uint8))
                 dst[4:4 + lb].copy_(_pack_levels(q, self.s))
-                dst[4 + lb:].copy_(idx.to(torch.int32).view(torch.uint8))
+                dst[4 + lb:].copy_(_pack_index(idx, seg.numel, k))
         return msg
 
     def decode(self, msg: torch.Tensor, out: Optional[torch.Tensor] = None, accumulate: bool = False,
@@ -165,13 +208,13 @@ class HostCodec:
             elif c == "topk":
                 k = self._k(seg)
                 vals = src[:4 * k].view(torch.float32)
-                idx = src[4 * k:].view(torch.int32).long()
+                idx = _unpack_index(src[4 * k:], seg.numel, k)
                 tgt.index_add_(0, idx, vals)
             else:
                 k = self._k(seg)
                 lb = _levels_nbytes(k, self.s)
                 norm = src[:4].view(torch.float32)
                 q = _unpack_levels(src[4:4 + lb], k, self.s)
-                idx = src[4 + lb:].view(torch.int32).long()
+                idx = _unpack_index(src[4 + lb:], seg.numel, k)
                 tgt.index_add_(0, idx, qsgd_dequantize(q, norm, self.s))
         return dense
