@@ -29,14 +29,21 @@ extern "C" int ewdml_launch(int nproc, const char* master_addr, int master_port,
     if (nproc < 1 || !argv || !argv[0]) { ewdml_set_error("launch: bad args"); return EWDML_ERR_ARG; }
     if (failed_rank) *failed_rank = -1;
     std::vector<pid_t> pids(nproc, -1);
+    // multi-node: NODE_RANK / NNODES in the launcher's environment (set by `ewdml.cli.launch --node-rank/--nnodes` or
+    // tools/cluster.py) place this node's ranks at node_rank * nproc + local_rank in a world of nnodes * nproc
+    const char* nr = getenv("NODE_RANK");
+    const char* nn = getenv("NNODES");
+    const int node_rank = nr ? atoi(nr) : 0, nnodes = (nn && atoi(nn) > 0) ? atoi(nn) : 1;
+    if (node_rank < 0 || node_rank >= nnodes) { ewdml_set_error("launch: NODE_RANK %d outside NNODES %d", node_rank, nnodes); return EWDML_ERR_ARG; }
     for (int r = 0; r < nproc; ++r) {
         pid_t pid = fork();
         if (pid < 0) { ewdml_set_error("launch: fork failed: %s", strerror(errno)); return EWDML_ERR_STATE; }
         if (pid == 0) {
             setpgid(0, 0);
-            setenv("RANK", std::to_string(r).c_str(), 1);
+            setenv("RANK", std::to_string(node_rank * nproc + r).c_str(), 1);
             setenv("LOCAL_RANK", std::to_string(r).c_str(), 1);
-            setenv("WORLD_SIZE", std::to_string(nproc).c_str(), 1);
+            setenv("WORLD_SIZE", std::to_string(nnodes * nproc).c_str(), 1);
+            setenv("GROUP_RANK", std::to_string(node_rank).c_str(), 1);
             setenv("LOCAL_WORLD_SIZE", std::to_string(nproc).c_str(), 1);
             setenv("MASTER_ADDR", master_addr ? master_addr : "127.0.0.1", 1);
             setenv("MASTER_PORT", std::to_string(master_port).c_str(), 1);

@@ -56,3 +56,15 @@ def test_lr_warmup_multiplier_matches_horovod_formula():
     from ewdml.parallel import hvd_keras as K
     cb = K.LearningRateWarmupCallback(initial_lr=0.008, warmup_epochs=4)
     assert cb.multiplier(0.0) == 1.0 and cb.multiplier(10) == 1.0        # size() == 1 here: no scaling to ramp
+
+
+def test_launcher_multi_node_rank_numbering():
+    """One launcher per node: --nnodes 2 --node-rank 1 -np 2 starts global ranks 2 and 3 of a world of 4."""
+    code = "import os; print('R', os.environ['RANK'], os.environ['LOCAL_RANK'], os.environ['WORLD_SIZE'], os.environ['GROUP_RANK'])"
+    out = subprocess.run([sys.executable, "-m", "ewdml.cli.launch", "-np", "2", "--nnodes", "2", "--node-rank", "1", "--",
+                          sys.executable, "-c", code], capture_output=True, text=True, timeout=60, cwd=ROOT)
+    assert out.returncode == 0, out.stderr
+    assert sorted(l for l in out.stdout.splitlines() if l.startswith("R")) == ["R 2 0 4 1", "R 3 1 4 1"]
+    bad = subprocess.run([sys.executable, "-m", "ewdml.cli.launch", "-np", "1", "--nnodes", "2", "--node-rank", "5", "--",
+                          sys.executable, "-c", "pass"], capture_output=True, text=True, timeout=60, cwd=ROOT)
+    assert bad.returncode != 0
