@@ -89,3 +89,20 @@ def test_symmetric_heap_allocator_is_deterministic_and_coalesces():
     assert lib.ewdml_symheap_used(h1) == 0 and lib.ewdml_symheap_largest_free(h1) == 1 << 20   # fully coalesced again
     assert lib.ewdml_symheap_free(h1, 12345) != 0                 # not a live allocation
     lib.ewdml_symheap_destroy(h1); lib.ewdml_symheap_destroy(h2)
+
+
+def test_c_abi_header_is_c99_and_links_from_c(tmp_path):
+    """include/ewdml.h compiles as pedantic C99 and a plain C program links and runs against libewdml.so (no GPU needed for
+    the host-side entry points)."""
+    import os, shutil, subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    if shutil.which("gcc") is None or not os.path.isfile(os.path.join(root, "ewdml", "_C", "libewdml.so")):
+        import pytest
+        pytest.skip("needs gcc and the built library")
+    exe = str(tmp_path / "c_abi_demo")
+    cc = subprocess.run(["gcc", "-std=c99", "-Wall", "-Wextra", "-pedantic", "-Werror", "-I" + os.path.join(root, "include"),
+                         os.path.join(root, "examples", "c_abi_demo.c"), "-o", exe, "-L" + os.path.join(root, "ewdml", "_C"), "-lewdml",
+                         "-Wl,-rpath," + os.path.join(root, "ewdml", "_C")], capture_output=True, text=True)
+    assert cc.returncode == 0, cc.stderr
+    out = subprocess.run([exe], capture_output=True, text=True, timeout=60)
+    assert out.returncode == 0 and "offsets 0 1024 used 71168" in out.stdout and "counter 3" in out.stdout
