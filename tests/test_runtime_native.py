@@ -1,0 +1,100 @@
+"""Native TCP rendezvous store (csrc/runtime/store.cpp, the PMIx-modex analogue): set / blocking get / barrier / all_gather
+across processes, on CPU."""
+import json
+import os
+import socket
+import time
+
+import torch.multiprocessing as mp
+
+
+def _free_port():
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); p = s.getsockname()[1]; s.close(); return p
+
+
+def _proc(rank, world, port, out_dir):
+    from ewdml.runtime import lib as L
+    if rank == 2:
+        time.sleep(0.3)                           # a late joiner: the others block in get / barrier until it arrives
+    st = L.Store("127.0.0.1", port, rank, world, timeout_s=30.0)
+    st.set(f"key/{rank}", bytes([rank]) * (100 + rank))
+    got = {r: st.get(f"key/{r}") for r in range(world)}          # blocks until every key exists
+    st.barrier("phase1")
+    handles = st.all_gather("handles", f"ipc-handle-of-{rank}".encode().ljust(64, b"\0"))
+    big = os.urandom(40000) if rank == 0 else b""
+    if rank == 0:
+        st.set("big", big)
+    blob = st.get("big", cap=1 << 17)
+    st.barrier("phase2")
+    json.dump({"lens": {str(r): len(v) for r, v in got.items()}, "first": {str(r): v[0] for r, v in got.items()},
+               "handles": [h.rstrip(b"\0").decode() for h in handles], "big": len(blob)},
+              open(os.path.join(out_dir, f"r{rank}.json"), "w"))
+    st.close()
+
+
+def test_store_set_get_barrier_all_gather(tmp_path):
+    world = 3
+    mp.spawn(_proc, args=(world, _free_port(), str(tmp_path)), nprocs=world, join=True)
+    for r in range(world):
+        res = json.load(open(tmp_path / f"r{r}.json"))
+        assert res["lens"] == {"0": 100, "1": 101, "2": 102} and res["first"] == {"0": 0, "1": 1, "2": 2}
+        assert res["handles"] == [f"ipc-handle-of-{i}" for i in range(world)]
+        assert res["big"] == 40000
+
+
+def test_counters_and_peer_matrix():
+    import ctypes as C
+    from ewdml.runtime import lib as L
+    lib = L.load()
+    lib.ewdml_counters_reset()
+    lib.ewdml_counter_add(L.CTR_BYTES_SENT, 1234)
+    lib.ewdml_counter_add(L.CTR_SEND_CALLS, 2)
+    lib.ewdml_peer_matrix_add(3, 1000); lib.ewdml_peer_matrix_add(3, 24); lib.ewdml_peer_matrix_add(0, 7)
+    row = (C.c_int64 * L.MAX_PEERS)()
+    L.check(lib.ewdml_peer_matrix_get(row))
+    assert lib.ewdml_counter_get(L.CTR_BYTES_SENT) == 1234 and lib.ewdml_counter_get(L.CTR_SEND_CALLS) == 2
+    assert row[3] == 1024 and row[0] == 7 and row[1] == 0
+    lib.ewdml_counters_reset()
+    assert lib.ewdml_counter_get(L.CTR_BYTES_SENT) == 0
+
+
+def _engine(world, rank=0):
+    import ctypes as C
+    from ewdml.runtime import lib as L
+    lib = L.load()
+    fake = (C.c_void_p * world)(*[0x1000 * (i + 1) for i in range(world)])     # never dereferenced: no launch happens here
+    h = C.c_void_p()
+    L.check(lib.ewdml_engine_create(C.byref(h), rank, world, fake, fake, 1 << 20))
+    return lib, h
+
+
+def test_collective_engine_decision_table():
+    """coll/tuned analogue: allreduce is one-shot at W <= 2 or at most 256 KiB, two-shot above; forced algorithm wins;
+    every other operation has one algorithm."""
+    from ewdml.runtime import lib as L
+    lib, h2 = _engine(2)
+    lib, h8 = _engine(8)
+    sel = lambda h, op, n: lib.ewdml_engine_select_algo(h, op, n)
+    assert sel(h2, L.COLL_ALLREDUCE, 1 << 30) == L.ALGO_ONESHOT
+    assert sel(h8, L.COLL_ALLREDUCE, 1 << 18) == L.ALGO_ONESHOT and sel(h8, L.COLL_ALLREDUCE, (1 << 18) + 16) == L.ALGO_TWOSHOT
+    assert sel(h8, L.COLL_ALLGATHER, 1 << 30) == L.ALGO_ONESHOT and sel(h8, L.COLL_BCAST, 16) == L.ALGO_ONESHOT
+    L.check(lib.ewdml_engine_set_algo(h8, L.COLL_ALLREDUCE, L.ALGO_ONESHOT))
+    assert sel(h8, L.COLL_ALLREDUCE, 1 << 30) == L.ALGO_ONESHOT
+    assert lib.ewdml_engine_set_algo(h8, 99, 0) != 0 and lib.ewdml_engine_slot_payload(h8) == 1 << 20
+    assert lib.ewdml_engine_window_bytes(8, 1 << 20) == 2 * 2 * 8 * ((1 << 20) + 256)
+    assert lib.ewdml_coll_op_name(L.COLL_REDUCE_SCATTER) == b"reduce_scatter"
+    lib.ewdml_engine_destroy(h2); lib.ewdml_engine_destroy(h8)
+
+
+def test_collective_engine_environment_override():
+    import subprocess, sys
+    code = ("import sys, ctypes as C; sys.path.insert(0, %r); from ewdml.runtime import lib as L; lib = L.load(); "
+            "fake = (C.c_void_p * 8)(*[4096 * (i + 1) for i in range(8)]); h = C.c_void_p(); "
+            "L.check(lib.ewdml_engine_create(C.byref(h), 0, 8, fake, fake, 1 << 20)); "
+            "print(lib.ewdml_engine_select_algo(h, L.COLL_ALLREDUCE, 64), lib.ewdml_engine_select_algo(h, L.COLL_ALLREDUCE, 1 << 30))")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    run = lambda env: subprocess.run([sys.executable, "-c", code % root], capture_output=True, text=True, timeout=120, cwd=root,
+                                     env=dict(os.environ, **env)).stdout.split()
+    assert run({"EWDML_COLL_ALLREDUCE_ALGO": "twoshot"}) == ["2", "2"]
+    assert run({"EWDML_COLL_ONESHOT_MAX_BYTES": "32"}) == ["2", "2"]
+    assert run({"EWDML_COLL_ONESHOT_MAX_BYTES": str(1 << 31)}) == ["1", "1"]
