@@ -68,3 +68,46 @@ def test_launcher_multi_node_rank_numbering():
     bad = subprocess.run([sys.executable, "-m", "ewdml.cli.launch", "-np", "1", "--nnodes", "2", "--node-rank", "5", "--",
                           sys.executable, "-c", "pass"], capture_output=True, text=True, timeout=60, cwd=ROOT)
     assert bad.returncode != 0
+
+
+def _hvd_rank(rank, world, port, out_dir):
+    import torch.distributed as dist
+    from ewdml.compress import Compression
+    from ewdml.parallel import hvd
+    os.environ.update(RANK=str(rank), WORLD_SIZE=str(world), MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    torch.set_num_threads(1)
+    hvd.init("gloo")
+    res = {"rank": hvd.rank(), "size": hvd.size()}
+    t = torch.full((5,), float(rank + 1))
+    res["avg"] = hvd.allreduce(t).tolist()
+    res["sum"] = hvd.allreduce(t, op=hvd.Sum).tolist()
+    res["adasum"] = hvd.allreduce(torch.eye(2)[rank % 2], op=hvd.Adasum).tolist()       # orthogonal vectors add up
+    torch.manual_seed(rank)                                                            # different initial weights per rank
+    model = torch.nn.Linear(4, 3)
+    opt = torch.optim.SGD(model.parameters(), lr=0.1 * (rank + 1), momentum=0.9)
+    hvd.broadcast_parameters(model.state_dict(), root_rank=0)
+    hvd.broadcast_optimizer_state(opt, root_rank=0)
+    res["lr"] = opt.param_groups[0]["lr"]
+    dopt = hvd.DistributedOptimizer(opt, named_parameters=model.named_parameters(), compression=Compression.none)
+    x = torch.full((2, 4), float(rank + 1))
+    model(x).sum().backward()
+    local = model.weight.grad.clone()
+    dopt.synchronize()
+    res["grad_is_average"] = bool(torch.allclose(model.weight.grad, hvd.allreduce(local)))
+    dopt.step()
+    res["weight_sum"] = float(model.weight.double().sum())
+    json.dump(res, open(os.path.join(out_dir, f"r{rank}.json"), "w"))
+    hvd.shutdown()
+
+
+def test_hvd_collectives_and_distributed_optimizer(tmp_path):
+    import socket
+    import torch.multiprocessing as mp
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
+    mp.spawn(_hvd_rank, args=(2, port, str(tmp_path)), nprocs=2, join=True)
+    r0, r1 = (json.load(open(tmp_path / f"r{r}.json")) for r in (0, 1))
+    assert (r0["rank"], r1["rank"], r0["size"]) == (0, 1, 2)
+    assert r0["avg"] == [1.5] * 5 and r1["sum"] == [3.0] * 5 and r0["adasum"] == [1.0, 1.0]
+    assert r1["lr"] == 0.1                                   # optimizer state came from rank 0
+    assert r0["grad_is_average"] and r1["grad_is_average"]
+    assert r0["weight_sum"] == r1["weight_sum"]              # same start, same averaged gradient: replicas stay identical
