@@ -347,6 +347,252 @@ __global__ void __launch_bounds__(192) k_gemm_tcgen05(const __grid_constant__ CU
     if (warp == 1) tcgen05_dealloc(tmem_base, BN);
 }
 
+// ---- EXPERIMENTAL persistent variant (EWDML_GEMM_PERSIST=1; compiled and resource-checked, not yet validated on a GPU) -------
+// ncu shows the one-tile-per-CTA kernel above spending most of its time in per-tile fixed costs (TMEM allocation, barrier and
+// descriptor set-up, TMEM -> register -> global epilogue) around K loops of only 9-72 k-blocks.  Here one CTA per SM walks a list
+// of work items (m fastest, so neighbouring CTAs share the B tile in L2), the shared-memory ring runs across tile boundaries, and
+// TMEM holds TWO accumulators so that the epilogue of item i overlaps the main loop of item i+1.  All waits are bounded (trap).
+__device__ __forceinline__ uint32_t mbar_try(uint32_t bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+        "selp.u32 %0, 1, 0, p;\n"
+        "}\n"
+        : "=r"(ok)
+        : "r"(bar), "r"(parity)
+        : "memory");
+    return ok;
+}
+__device__ __forceinline__ void mbar_wait_bounded(uint32_t bar, uint32_t parity) {
+    for (uint32_t it = 0; !mbar_try(bar, parity); ++it)
+        if (it > (1u << 26)) __trap();
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+
+template <int BN, int STAGES>
+struct SmemP {
+    static constexpr int A_BYTES = BM * BK * 2;
+    static constexpr int B_BYTES = BN * BK * 2;
+    static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+    static constexpr int BAR_OFF = STAGES * STAGE_BYTES;
+    static constexpr int NBARS = 2 * STAGES + 4;                               // full, empty, tmem_full[2], tmem_empty[2]
+    static constexpr int BIAS_OFF = BAR_OFF + 8 * (NBARS + 1) + 16;
+    static constexpr int TOTAL = BIAS_OFF + 2 * BN * 4 + 1024;
+};
+
+struct WorkDims { int m_tiles, n_tiles, total; };
+
+template <int BN, int STAGES, bool A_MN, bool B_MN>
+__global__ void __launch_bounds__(192) k_gemm_persist(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                                                         const GemmArgs g, const WorkDims wd) {
+    using S = SmemP<BN, STAGES>;
+    static_assert(2 * BN <= 512, "two accumulators must fit the 512 TMEM columns");
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    const uint32_t smem_base = smem_u32(smem);
+    const uint32_t bar_base = smem_base + S::BAR_OFF;
+    auto full_bar = [&](int s) { return bar_base + 8 * s; };
+    auto empty_bar = [&](int s) { return bar_base + 8 * (STAGES + s); };
+    auto tfull_bar = [&](int a) { return bar_base + 8 * (2 * STAGES + a); };
+    auto tempty_bar = [&](int a) { return bar_base + 8 * (2 * STAGES + 2 + a); };
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + S::BAR_OFF + 8 * S::NBARS);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < STAGES; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
+        for (int a = 0; a < 2; ++a) { mbar_init(tfull_bar(a), 1); mbar_init(tempty_bar(a), 4); }      // 4 epilogue warps arrive
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    }
+    if (warp == 1) tcgen05_alloc(smem_u32(tmem_slot), 2 * BN);
+    tcgen05_fence_before();
+    __syncthreads();
+    tcgen05_fence_after();
+    const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(tmem_slot);
+
+    // work item w -> (m_tile, n_tile, split z); every split is non-empty by construction
+    auto decode = [&](int w, int& m_tile, int& n_tile, int& kb0, int& nkb, int& z) {
+        m_tile = w % wd.m_tiles;
+        const int rest = w / wd.m_tiles;
+        n_tile = rest % wd.n_tiles;
+        z = rest / wd.n_tiles;
+        kb0 = z * g.kb_per_split;
+        nkb = min(g.kb_total, kb0 + g.kb_per_split) - kb0;
+    };
+
+    if (warp == 0) {
+        if (lane == 0) {
+            uint32_t it = 0;                                     // k-blocks issued so far: ring position across items
+            for (int w = blockIdx.x; w < wd.total; w += gridDim.x) {
+                int m_tile, n_tile, kb0, nkb, z;
+                decode(w, m_tile, n_tile, kb0, nkb, z);
+                for (int i = 0; i < nkb; ++i, ++it) {
+                    const int s = it % STAGES;
+                    const uint32_t ph = (it / STAGES) & 1;
+                    mbar_wait_bounded(empty_bar(s), ph ^ 1);
+                    mbar_expect_tx(full_bar(s), S::STAGE_BYTES);
+                    const uint32_t a_dst = smem_base + s * S::STAGE_BYTES;
+                    const int kb = kb0 + i;
+                    const int k0 = kb * BK;
+                    int a_row = m_tile * BM, a_col = k0, b_row = n_tile * BN, b_col = k0;
+                    if (g.cm.mode == CONV_FPROP) {
+                        const int tap = kb / g.cm.cblocks;
+                        a_row += g.cm.off[tap];
+                        a_col = (kb - tap * g.cm.cblocks) * BK;
+                    } else if (g.cm.mode == CONV_DGRAD) {
+                        const int tap = kb / g.cm.cblocks;
+                        a_row -= g.cm.off[tap];
+                        a_col = (kb - tap * g.cm.cblocks) * BK;
+                        b_col = a_col;
+                        b_row = tap * g.cm.cin + n_tile * BN;
+                    } else if (g.cm.mode == CONV_WGRAD) {
+                        const int tap = (n_tile * BN) / g.cm.cin;
+                        b_row = n_tile * BN - tap * g.cm.cin;
+                        b_col = k0 + g.cm.off[tap];
+                    }
+                    if constexpr (A_MN) {
+#pragma unroll
+                        for (int h = 0; h < BM / 64; ++h) tma_load_2d(a_dst + h * (BK * 128), &tmA, full_bar(s), a_row + h * 64, a_col);
+                    } else {
+                        tma_load_2d(a_dst, &tmA, full_bar(s), a_col, a_row);
+                    }
+                    if constexpr (B_MN) {
+#pragma unroll
+                        for (int h = 0; h < BN / 64; ++h)
+                            tma_load_2d(a_dst + S::A_BYTES + h * (BK * 128), &tmB, full_bar(s), b_row + h * 64, b_col);
+                    } else {
+                        tma_load_2d(a_dst + S::A_BYTES, &tmB, full_bar(s), b_col, b_row);
+                    }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            constexpr uint32_t idesc = make_idesc(BN, A_MN, B_MN);
+            constexpr uint64_t a_step = A_MN ? 128 : 2, b_step = B_MN ? 128 : 2;
+            uint32_t it = 0;
+            int item = 0;
+            for (int w = blockIdx.x; w < wd.total; w += gridDim.x, ++item) {
+                int m_tile, n_tile, kb0, nkb, z;
+                decode(w, m_tile, n_tile, kb0, nkb, z);
+                const int acc = item & 1;
+                mbar_wait_bounded(tempty_bar(acc), ((item >> 1) & 1) ^ 1);      // the epilogue has drained this accumulator
+                tcgen05_fence_after();
+                const uint32_t d_tmem = tmem_base + (uint32_t)(acc * BN);
+                for (int i = 0; i < nkb; ++i, ++it) {
+                    const int s = it % STAGES;
+                    const uint32_t ph = (it / STAGES) & 1;
+                    mbar_wait_bounded(full_bar(s), ph);
+                    tcgen05_fence_after();
+                    const uint32_t a_addr = smem_base + s * S::STAGE_BYTES;
+                    const uint64_t a_desc = A_MN ? make_smem_desc_mn(a_addr) : make_smem_desc(a_addr);
+                    const uint64_t b_desc = B_MN ? make_smem_desc_mn(a_addr + S::A_BYTES) : make_smem_desc(a_addr + S::A_BYTES);
+#pragma unroll
+                    for (int k = 0; k < BK / UMMA_K; ++k)
+                        tcgen05_mma_f16(d_tmem, a_desc + a_step * k, b_desc + b_step * k, idesc, (i > 0 || k > 0) ? 1u : 0u);
+                    tcgen05_commit(empty_bar(s));
+                }
+                tcgen05_commit(tfull_bar(acc));
+            }
+        }
+    } else {
+        const int quad = warp & 3;
+        float* s_bias_all = reinterpret_cast<float*>(smem + S::BIAS_OFF);
+        int item = 0;
+        for (int w = blockIdx.x; w < wd.total; w += gridDim.x, ++item) {
+            int m_tile, n_tile, kb0, nkb, z;
+            decode(w, m_tile, n_tile, kb0, nkb, z);
+            const int acc = item & 1;
+            float* s_bias = s_bias_all + acc * BN;
+            const bool use_bias = g.bias != nullptr && z == 0;
+            if (use_bias) {
+                for (int j = threadIdx.x - 64; j < BN; j += 128) {
+                    const int c = n_tile * BN + j;
+                    s_bias[j] = c < g.N ? g.bias[c] : 0.f;
+                }
+            }
+            // every item: also orders the reuse of s_bias[acc] two items later behind the slowest epilogue warp of this one
+            asm volatile("bar.sync 1, 128;" ::: "memory");
+            int row = m_tile * BM + quad * 32 + lane;
+            if (g.cm.remap) {
+                const int WP = g.cm.W + 2, HP = g.cm.H + 2;
+                const int wp = row % WP, t = row / WP, hp = t % HP, n = t / HP;
+                const bool interior = hp >= 1 && hp <= g.cm.H && wp >= 1 && wp <= g.cm.W;
+                row = interior ? (n * g.cm.H + hp - 1) * g.cm.W + (wp - 1) : g.m_store;
+            }
+            mbar_wait_bounded(tfull_bar(acc), (item >> 1) & 1);
+            tcgen05_fence_after();
+#pragma unroll 1
+            for (int c = 0; c < BN / 32; ++c) {
+                uint32_t v[32];
+                tcgen05_ld_32x32(tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(acc * BN + c * 32), v);
+                const int col0 = n_tile * BN + c * 32;
+                if (row >= g.m_store || col0 >= g.N) continue;
+                float f[32];
+#pragma unroll
+                for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]) * g.alpha;
+                if (use_bias) {
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) f[j] += s_bias[c * 32 + j];
+                }
+                const bool full = col0 + 32 <= g.N;
+                if (g.out_mode == 0) {
+                    __nv_bfloat16* out = reinterpret_cast<__nv_bfloat16*>(g.C) + (size_t)row * g.ldc + col0;
+                    if (full && (g.ldc % 8 == 0)) {
+#pragma unroll
+                        for (int j = 0; j < 32; j += 8) {
+                            uint4 pk;
+                            __nv_bfloat162 p0 = __floats2bfloat162_rn(f[j], f[j + 1]), p1 = __floats2bfloat162_rn(f[j + 2], f[j + 3]);
+                            __nv_bfloat162 p2 = __floats2bfloat162_rn(f[j + 4], f[j + 5]), p3 = __floats2bfloat162_rn(f[j + 6], f[j + 7]);
+                            pk.x = *reinterpret_cast<uint32_t*>(&p0); pk.y = *reinterpret_cast<uint32_t*>(&p1);
+                            pk.z = *reinterpret_cast<uint32_t*>(&p2); pk.w = *reinterpret_cast<uint32_t*>(&p3);
+                            *reinterpret_cast<uint4*>(out + j) = pk;
+                        }
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < 32; ++j)
+                            if (col0 + j < g.N) out[j] = __float2bfloat16_rn(f[j]);
+                    }
+                } else if (g.out_mode == 1) {
+                    float* out = reinterpret_cast<float*>(g.C) + (size_t)row * g.ldc + col0;
+                    if (full && (g.ldc % 4 == 0)) {
+#pragma unroll
+                        for (int j = 0; j < 32; j += 4) *reinterpret_cast<float4*>(out + j) = make_float4(f[j], f[j + 1], f[j + 2], f[j + 3]);
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < 32; ++j)
+                            if (col0 + j < g.N) out[j] = f[j];
+                    }
+                } else {
+                    float* out = reinterpret_cast<float*>(g.C) + (size_t)row * g.ldc + col0;
+                    if (full && (g.ldc % 4 == 0) && ((reinterpret_cast<uintptr_t>(g.C) & 15) == 0)) {
+#pragma unroll
+                        for (int j = 0; j < 32; j += 4)
+                            asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(out + j), "f"(f[j]), "f"(f[j + 1]), "f"(f[j + 2]),
+                                         "f"(f[j + 3])
+                                         : "memory");
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < 32; ++j)
+                            if (col0 + j < g.N) atomicAdd(out + j, f[j]);
+                    }
+                }
+            }
+            // this warp's reads of the accumulator are complete (tcgen05.wait::ld inside the load): hand it back to the MMA thread
+            tcgen05_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(tempty_bar(acc));
+        }
+    }
+    tcgen05_fence_before();
+    __syncthreads();
+    if (warp == 1) tcgen05_dealloc(tmem_base, 2 * BN);
+}
+
 // ---- host side ----------------------------------------------------------------------------------
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
                                   const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
@@ -396,6 +642,27 @@ int launch(const CUtensorMap& tA, const CUtensorMap& tB, const GemmArgs& g, int 
     k_gemm_tcgen05<BN, STAGES, A_MN, B_MN><<<grid, 192, S::TOTAL, st>>>(tA, tB, g);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) { ewdml_set_error("gemm launch failed: %s", cudaGetErrorString(e)); return (int)e; }
+    ewdml_counter_add(EWDML_CTR_COMPUTE_LAUNCHES, 1);
+    return 0;
+}
+
+template <int BN, int STAGES, bool A_MN, bool B_MN>
+int launch_persist(const CUtensorMap& tA, const CUtensorMap& tB, const GemmArgs& g, int split, cudaStream_t st) {
+    using S = SmemP<BN, STAGES>;
+    static bool attr = false;
+    if (!attr) {
+        EWDML_CUDA(cudaFuncSetAttribute(k_gemm_persist<BN, STAGES, A_MN, B_MN>, cudaFuncAttributeMaxDynamicSharedMemorySize, S::TOTAL));
+        attr = true;
+    }
+    WorkDims wd;
+    wd.m_tiles = (g.M + BM - 1) / BM; wd.n_tiles = (g.N + BN - 1) / BN; wd.total = wd.m_tiles * wd.n_tiles * split;
+    int dev = 0, sms = 148;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    const int grid = wd.total < sms ? wd.total : sms;             // one CTA per SM (the ring takes most of the shared memory)
+    k_gemm_persist<BN, STAGES, A_MN, B_MN><<<grid, 192, S::TOTAL, st>>>(tA, tB, g, wd);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) { ewdml_set_error("persistent gemm launch failed: %s", cudaGetErrorString(e)); return (int)e; }
     ewdml_counter_add(EWDML_CTR_COMPUTE_LAUNCHES, 1);
     return 0;
 }
@@ -455,6 +722,10 @@ int gemm_dispatch(const void* A, const void* B, void* C, int M, int N, int K, in
     if constexpr (!A_MN) {
         if (bn == 256) return launch<256, 4, A_MN, B_MN>(tA, tB, g, split, st);
     }
+    // EXPERIMENTAL, off unless EWDML_GEMM_PERSIST=1 (see k_gemm_persist)
+    static const int persist_env = getenv("EWDML_GEMM_PERSIST") ? atoi(getenv("EWDML_GEMM_PERSIST")) : 0;
+    if (persist_env == 1)
+        return bn == 64 ? launch_persist<64, 8, A_MN, B_MN>(tA, tB, g, split, st) : launch_persist<128, 6, A_MN, B_MN>(tA, tB, g, split, st);
     if (bn == 64) return deep ? launch<64, 8, A_MN, B_MN>(tA, tB, g, split, st) : launch<64, 4, A_MN, B_MN>(tA, tB, g, split, st);
     return deep ? launch<128, 6, A_MN, B_MN>(tA, tB, g, split, st) : launch<128, 3, A_MN, B_MN>(tA, tB, g, split, st);
 }

@@ -197,6 +197,7 @@ registry.register("allreduce_algo", "auto", "fused dense allreduce (K4): auto | 
 registry.register("coll_allreduce_algo", "auto", "collective engine allreduce: auto | oneshot | twoshot (read by the library)")
 registry.register("coll_oneshot_max_bytes", 1 << 18, "collective engine: one-shot allreduce at or below this size (read by the library)")
 registry.register("gemm_bn", 0, "experimental GEMM tile width: 256 = 128x256 tiles where N % 256 == 0 (read by the library)")
+registry.register("gemm_persist", 0, "experimental persistent GEMM kernel with two TMEM accumulators: 1 = on (read by the library)")
 registry.register("trace", False, "print one line per native collective call (libompitrace analogue)")
 registry.register("nvtx", False, "emit NVTX ranges around exchange phases")
 registry.register("debug_poison", False, "poison receive slots after consumption (debug build aid)")

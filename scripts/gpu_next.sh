@@ -8,6 +8,12 @@ timeout 100 python bench.py --steps 100 --warmup 3 --no-e2e > gpurun_out/bench_b
 EWDML_GEMM_BN=256 timeout 100 python bench.py --steps 100 --warmup 3 --no-e2e > gpurun_out/bench_bn256.json 2>/dev/null; echo "bn256 rc=$?"; cut -c1-140 gpurun_out/bench_bn256.json
 EWDML_GEMM_BN=256 timeout 100 python bench.py --steps 50 --warmup 3 --no-e2e --model ResNet50 > gpurun_out/bench_r50_bn256.json 2>/dev/null; cut -c1-140 gpurun_out/bench_r50_bn256.json
 timeout 100 python bench.py --steps 50 --warmup 3 --no-e2e --model ResNet50 > gpurun_out/bench_r50_bn128.json 2>/dev/null; cut -c1-140 gpurun_out/bench_r50_bn128.json
+# 1b. experimental persistent GEMM (two TMEM accumulators, one CTA per SM): numerics under a short timeout first, then the step time
+EWDML_GEMM_PERSIST=1 timeout 90 python -m pytest tests/test_gpu_gemm.py -x -q -k "persistent" > gpurun_out/persist_test.log 2>&1; rc=$?; echo "persist test rc=$rc"; tail -2 gpurun_out/persist_test.log
+if [ $rc -eq 0 ]; then
+  EWDML_GEMM_PERSIST=1 timeout 200 python -m pytest tests/test_gpu_gemm.py tests/test_gpu_native_ops.py -x -q > gpurun_out/persist_suite.log 2>&1; echo "persist suite rc=$?"; tail -2 gpurun_out/persist_suite.log
+  EWDML_GEMM_PERSIST=1 timeout 100 python bench.py --steps 100 --warmup 3 --no-e2e > gpurun_out/bench_persist.json 2>/dev/null; echo "persist bench rc=$?"; cut -c1-140 gpurun_out/bench_persist.json
+fi
 # 2. Adam and error feedback through the public bench (native exchange), overlap on ResNet-50
 timeout 100 python bench.py --steps 50 --warmup 3 --no-e2e --model ResNet50 --bucket-size 16777216 --overlap > gpurun_out/bench_r50_overlap.json 2>/dev/null; cut -c1-140 gpurun_out/bench_r50_overlap.json
 # 3. the whole suite once more

@@ -90,3 +90,15 @@ def test_gemm_mn_major_operands(M, N, K, a_mn, b_mn):
 def test_gemm_bn256_experimental(M, N, K):
     """EWDML_GEMM_BN=256 python -m pytest tests/test_gpu_gemm.py -k bn256 : same oracle as the default tiles."""
     test_gemm_bf16_out(M, N, K)
+
+
+@pytest.mark.skipif(__import__("os").environ.get("EWDML_GEMM_PERSIST") != "1",
+                    reason="experimental persistent GEMM: run the file with EWDML_GEMM_PERSIST=1 (read once per process)")
+def test_gemm_persistent_experimental():
+    """EWDML_GEMM_PERSIST=1 python -m pytest tests/test_gpu_gemm.py tests/test_gpu_native_ops.py : every GEMM and convolution
+    pass then goes through k_gemm_persist; this test runs the plain-GEMM oracle checks on all shapes and modes."""
+    for M, N, K in SHAPES:
+        test_gemm_bf16_out(M, N, K)
+    for M, N, K in SHAPES[:7]:
+        test_gemm_f32_and_accumulate_splitk(M, N, K)
+    test_gemm_strided_operands()
