@@ -52,6 +52,9 @@ def parse():
     p.add_argument("--overlap", action="store_true", help="launch each bucket's exchange from backward on a side stream")
     p.add_argument("--error-feedback", action="store_true")
     p.add_argument("--no-e2e", action="store_true")
+    p.add_argument("--e2e-lag", type=int, default=0, choices=[0, 1],
+                   help="end-to-end loop: 1 = read step i-1's loss while step i runs (every step's loss is still read inside the "
+                        "timed region; experimental, default 0 = blocking read of step i's loss)")
     p.add_argument("--no-flush", action="store_true")
     p.add_argument("--no-graph", action="store_true", help="do not capture the step in a CUDA graph")
     return p.parse_args()
@@ -162,6 +165,8 @@ def run_ewdml(a):
     def timed(nsteps, e2e):
         ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         host_loss = torch.zeros(1, dtype=torch.float32).pin_memory()
+        lag_buf = [torch.zeros(1, dtype=torch.float32).pin_memory() for _ in range(2)]
+        lag_ev = [torch.cuda.Event() for _ in range(2)]
         barrier()
         t0 = time.perf_counter()
         ev0.record()
@@ -171,11 +176,21 @@ def run_ewdml(a):
                 x, y = feeder.next()
                 loss = one_step(x, y)
                 feeder.mark_consumed()
-                if loss is not None:
+                if loss is not None and not a.e2e_lag:
                     host_loss.copy_(loss.reshape(1), non_blocking=False)   # D2H read of the step's result
                     last = float(host_loss[0])
+                elif loss is not None:
+                    k = _ & 1                                              # enqueue this step's read, consume the previous step's
+                    lag_buf[k].copy_(loss.reshape(1), non_blocking=True)
+                    lag_ev[k].record()
+                    if _ > 0:
+                        lag_ev[k ^ 1].synchronize()
+                        last = float(lag_buf[k ^ 1][0])
             else:
                 one_step(x0, y0)
+        if e2e and a.e2e_lag and nsteps > 0 and role == "worker":
+            lag_ev[(nsteps - 1) & 1].synchronize()                         # the last step's loss, still inside the timed region
+            last = float(lag_buf[(nsteps - 1) & 1][0])
         ev1.record()
         barrier()
         wall = (time.perf_counter() - t0) * 1e3
@@ -217,7 +232,7 @@ def run_ewdml(a):
         ms_e, wall_e, last_loss = timed(a.steps, e2e=True)
         e2e = {"value": a.batch_size * n_workers * a.steps / (wall_e / 1e3), "unit": "images/s",
                "h2d_bytes_per_step": feeder.h2d_bytes_per_step, "d2h_bytes_per_step": 4,
-               "ms_per_step": wall_e / a.steps, "timed_with": "host wall clock around barrier+synchronize, max over ranks",
+               "ms_per_step": wall_e / a.steps, "timed_with": "host wall clock around barrier+synchronize, max over ranks", "loss_read_lag_steps": a.e2e_lag,
                "last_loss": last_loss}
     # exchange statistics (one extra step with stats collection, outside the timed regions)
     st = None

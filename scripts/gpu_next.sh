@@ -16,5 +16,7 @@ if [ $rc -eq 0 ]; then
 fi
 # 2. Adam and error feedback through the public bench (native exchange), overlap on ResNet-50
 timeout 100 python bench.py --steps 50 --warmup 3 --no-e2e --model ResNet50 --bucket-size 16777216 --overlap > gpurun_out/bench_r50_overlap.json 2>/dev/null; cut -c1-140 gpurun_out/bench_r50_overlap.json
+# 2b. end-to-end loop with the loss read lagging one step (every step's loss is still read inside the timed region)
+timeout 100 python bench.py --steps 100 --warmup 3 --e2e-lag 1 > gpurun_out/bench_e2e_lag.json 2>/dev/null; python -c "import json;d=json.load(open('gpurun_out/bench_e2e_lag.json'));print('e2e lag1', d['e2e']['value'], 'device', d['value'])"
 # 3. the whole suite once more
 timeout 300 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?"; tail -3 gpurun_out/pytest_gpu.log
