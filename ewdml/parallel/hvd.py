@@ -128,6 +128,22 @@ def broadcast_parameters(params, root_rank: int = 0) -> None:
 def broadcast_optimizer_state(optimizer: torch.optim.Optimizer, root_rank: int = 0) -> None:
     if size() == 1:
         return
+    if _state.get("engine") is not None:
+        # native runtime: no torch.distributed group exists; the (small, host-side) state travels through the rendezvous store
+        import io
+        import pickle
+        pg = _state["pg"]
+        _state["bcast_n"] = _state.get("bcast_n", 0) + 1
+        key = f"hvd/optstate/{_state['bcast_n']}"
+        if rank() == root_rank:
+            buf = io.BytesIO()
+            torch.save(optimizer.state_dict(), buf)
+            pg.store.set(key, buf.getvalue())
+        blob = pg.store.get(key, cap=1 << 28)
+        if rank() != root_rank:
+            optimizer.load_state_dict(torch.load(io.BytesIO(blob), map_location="cpu", weights_only=False))
+        pg.host_barrier(key + "/done")
+        return
     obj = [optimizer.state_dict() if rank() == root_rank else None]
     dist.broadcast_object_list(obj, src=root_rank)
     if rank() != root_rank:
