@@ -131,7 +131,6 @@ def broadcast_optimizer_state(optimizer: torch.optim.Optimizer, root_rank: int =
     if _state.get("engine") is not None:
         # native runtime: no torch.distributed group exists; the (small, host-side) state travels through the rendezvous store
         import io
-        import pickle
         pg = _state["pg"]
         _state["bcast_n"] = _state.get("bcast_n", 0) + 1
         key = f"hvd/optstate/{_state['bcast_n']}"
