@@ -30,7 +30,6 @@ import time
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
-REFERENCE_CPU_IMG_S_PER_WORKER = 104.0     # derived VGG11 M1 throughput of the reference (CPU)
 
 
 def parse():
@@ -60,54 +59,21 @@ def parse():
     return p.parse_args()
 
 
-class ClockSampler:
-    """nvidia-smi sampler running during the timed region (B200_PROFILING.md clocks line)."""
-    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
-         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
-         "clocks_event_reasons.sw_power_cap")
+def _load_clock_sampler():
+    # bench/clocks.py by path: `import bench` would resolve to this very file, and the reference arm must not import ewdml
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("ewdml_bench_clocks", os.path.join(ROOT, "bench", "clocks.py"))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    return mod.ClockSampler
 
-    def __init__(self, gpu_index: int):
-        self.gpu_index, self.proc, self.path = gpu_index, None, f"/tmp/ewdml_clocks_{os.getpid()}.csv"
 
-    def start(self):
-        try:
-            self.f = open(self.path, "w")
-            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                                          "-lms", "50", "-i", str(self.gpu_index)], stdout=self.f,
-                                         stderr=subprocess.DEVNULL)
-        except Exception:
-            self.proc = None
+ClockSampler = _load_clock_sampler()       # NVML poller in a child process, ~2 ms period, started before warm-up
 
-    def stop(self):
-        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
-        if self.proc is None:
-            return out
-        self.proc.terminate()
-        try:
-            self.proc.wait(timeout=5)
-        except Exception:
-            self.proc.kill()
-        self.f.close()
-        sm, mx, reasons = [], [], set()
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        try:
-            for line in open(self.path):
-                parts = [x.strip() for x in line.split(",")]
-                if len(parts) < 9:
-                    continue
-                try:
-                    sm.append(float(parts[1])); mx.append(float(parts[2]))
-                except ValueError:
-                    continue
-                for nm, v in zip(names, parts[5:9]):
-                    if v.lower().startswith("active"):
-                        reasons.add(nm)
-            os.remove(self.path)
-        except Exception:
-            pass
-        if sm:
-            out.update(sm_mhz=statistics.median(sm), sm_max_mhz=max(mx), reasons=sorted(reasons), samples=len(sm))
-        return out
+
+def metric_name(a) -> str:
+    """One metric string for every arm (ewdml / reference / nccl); what differs between arms lives in ``config``."""
+    return f"{a.model} images/sec"
 
 
 def run_ewdml(a):
@@ -201,6 +167,8 @@ def run_ewdml(a):
         return float(t[0]), float(t[1]), last
 
     # ---- warm-up (eager), then optional CUDA-graph capture of the whole step, then graph warm-up -----
+    sampler = ClockSampler(local_rank).start() if rank == 0 else None      # running from before warm-up on
+    pg.host_barrier("bench_start")          # every rank has built its trainer: nobody spins through a peer's set-up
     for _ in range(max(3, a.warmup)):
         one_step(x0, y0)
     barrier()
@@ -217,19 +185,22 @@ def run_ewdml(a):
     if err:
         raise SystemExit(f"device error word {err:#x} after warm-up")
 
-    sampler = ClockSampler(local_rank) if rank == 0 else None
-    if sampler:
-        sampler.start()
     l0 = tr.own_launches()
+    tw0 = time.time()
     ms, wall_ms, _ = timed(a.steps, e2e=False)
+    tw1 = time.time()
     launches = tr.own_launches() - l0
-    clocks = sampler.stop() if sampler else None
+    if sampler:
+        sampler.window("device_timed", tw0, tw1)
     stats = tr.exchange.step  # noqa: F841 (keep reference alive)
     e2e = None
     if not a.no_e2e:
         for _ in range(3):
             x, y = feeder.next(); one_step(x, y); feeder.mark_consumed()
+        te0 = time.time()
         ms_e, wall_e, last_loss = timed(a.steps, e2e=True)
+        if sampler:
+            sampler.window("e2e", te0, time.time())
         e2e = {"value": a.batch_size * n_workers * a.steps / (wall_e / 1e3), "unit": "images/s",
                "h2d_bytes_per_step": feeder.h2d_bytes_per_step, "d2h_bytes_per_step": 4,
                "ms_per_step": wall_e / a.steps, "timed_with": "host wall clock around barrier+synchronize, max over ranks", "loss_read_lag_steps": a.e2e_lag,
@@ -241,14 +212,14 @@ def run_ewdml(a):
     else:
         st = tr.server_step(want_stats=True)
     barrier()
+    clocks = sampler.stop() if sampler else None
     err = tr.check_device_error()
     value = a.batch_size * n_workers * a.steps / (ms / 1e3)
     out = {
-        "metric": f"{a.model} images/sec ({a.compressor} k={a.topk_ratio} s={a.qsgd_levels} {a.exchange})",
+        "metric": metric_name(a),
         "value": value, "unit": "images/s", "n_gpus": a.gpus, "steps": a.steps, "warmup": max(3, a.warmup),
         "ms_per_step": ms / a.steps, "higher_is_better": True, "scaling": "weak",
-        "vs_baseline": value / (REFERENCE_CPU_IMG_S_PER_WORKER * max(1, n_workers)),
-        "vs_baseline_note": "BASELINE.md publishes no GPU throughput; denominator is its derived 104 images/s per worker (VGG11 M1, Colab CPU)",
+        "vs_baseline": None,      # BASELINE.md publishes no images/s figure (CPU-only Colab minutes and MB/iteration)
         "dtype": a.dtype, "data": "synthetic (CIFAR-10 shape, random-init weights)", "impl": "ewdml",
         "config": {"model": a.model, "global_batch": a.batch_size * n_workers, "per_gpu_batch": a.batch_size,
                    "seq_len": None, "image": list(tr.input_spec()[1:]),
@@ -275,10 +246,10 @@ def main():
     a = parse()
     if a.impl == "reference":
         from baseline.run_reference import main as ref_main
-        return ref_main(a)
+        return ref_main(a, ClockSampler, metric_name)
     if a.impl == "nccl":
         from baseline.nccl_same_algorithm import main as nccl_main
-        return nccl_main(a)
+        return nccl_main(a, ClockSampler, metric_name)
     return run_ewdml(a)
 
 

@@ -83,6 +83,13 @@ __device__ __forceinline__ uint4 ld_v4(const void* p) {
 }
 
 // Spin until *flag >= seq (sequence numbers only grow).  Returns false on timeout and records it.
+// The first EWDML_FAST_POLLS polls are back to back (a local acquire load is ~0.2 us, so that is the first
+// millisecond, where every exchange of a healthy job completes); after that each poll sleeps ~1 us, which turns
+// `limit` into a time budget (2^26 polls = about a minute) that does not depend on how fast an L2 hit is, and
+// keeps hundreds of spinning CTAs from hammering the memory system while a peer is slow (first step, graph
+// capture, checkpoint).  Round 1 counted raw polls: 2^24 of them lasted ~4 s, not the documented 20 s, and an
+// 8-rank ResNet-50 parameter-server job tripped it while the workers were still capturing their graphs.
+#define EWDML_FAST_POLLS 4096
 __device__ __forceinline__ bool wait_flag_ge(const uint32_t* flag, uint32_t seq, uint64_t limit,
                                              uint32_t* err_word, uint32_t err_code) {
     uint64_t it = 0;
@@ -91,7 +98,8 @@ __device__ __forceinline__ bool wait_flag_ge(const uint32_t* flag, uint32_t seq,
             atomicExch(err_word, err_code);
             return false;
         }
-        if ((it & 63) == 0) __nanosleep(64);
+        if (it > EWDML_FAST_POLLS) __nanosleep(1000);
+        else if ((it & 63) == 0) __nanosleep(64);
     }
     return true;
 }

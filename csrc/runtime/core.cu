@@ -55,8 +55,8 @@ extern "C" uint64_t ewdml_spin_limit() {
     uint64_t v = g_spin_limit.load();
     if (v == 0) {
         const char* e = getenv("EWDML_SPIN_LIMIT");
-        v = e ? strtoull(e, nullptr, 10) : (1ull << 24);
-        if (v == 0) v = 1ull << 24;
+        v = e ? strtoull(e, nullptr, 10) : (1ull << 26);
+        if (v == 0) v = 1ull << 26;
         g_spin_limit.store(v);
         if (g_trace.load() < 0) {
             const char* t = getenv("EWDML_TRACE");
@@ -66,7 +66,7 @@ extern "C" uint64_t ewdml_spin_limit() {
     return v;
 }
 extern "C" int ewdml_set_spin_limit(uint64_t iters) {
-    g_spin_limit.store(iters ? iters : (1ull << 24));
+    g_spin_limit.store(iters ? iters : (1ull << 26));
     return 0;
 }
 

@@ -192,7 +192,7 @@ class Registry:
 
 
 registry = Registry()
-registry.register("spin_limit", 1 << 24, "device-side flag spin iteration cap before the error word is set (read by the library)")
+registry.register("spin_limit", 1 << 26, "device-side flag poll cap before the error word is set: 4096 back-to-back polls, then ~1 us per poll (2^26 = about a minute)")
 registry.register("allreduce_algo", "auto", "fused dense allreduce (K4): auto | oneshot | twoshot")
 registry.register("coll_allreduce_algo", "auto", "collective engine allreduce: auto | oneshot | twoshot (read by the library)")
 registry.register("coll_oneshot_max_bytes", 1 << 18, "collective engine: one-shot allreduce at or below this size (read by the library)")

@@ -147,6 +147,7 @@ int ewdml_allreduce_state(const ewdml_comm* comm, int64_t n, float scale, int al
 int ewdml_barrier(const ewdml_comm* comm, uint32_t seq, void* stream);
 /* device error word (0 = ok) set by kernels whose flag spin exceeded the limit                  */
 int ewdml_get_device_error(uint32_t* out, void* stream);
+/* poll cap of every flag wait: 4096 back-to-back polls, then ~1 us per poll; 0 = default 2^26 (about a minute) */
 int ewdml_set_spin_limit(uint64_t iters);
 
 /* ------------------------------------------------------------------------------------------
