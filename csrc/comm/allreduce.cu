@@ -102,6 +102,40 @@ __global__ void __launch_bounds__(512) k_allreduce_twoshot(const ArArgs a) {
     exit_barrier(a);
 }
 
+// NVLS: the same ownership rule as two-shot (only rank r touches shard r, so in place and no middle barrier), but the W-way
+// sum happens inside the NVSwitch (multimem.ld_reduce: one reduced vector comes back over the link instead of W-1 peer
+// copies) and the result leaves as ONE multicast store instead of W unicast stores: link traffic per rank drops from
+// 2(W-1)/W * N to about N in each direction, and the SM issues 2 memory operations per vector instead of 2W.
+__global__ void __launch_bounds__(512) k_allreduce_nvls(const ArArgs a) {
+    __shared__ int s_ok;
+    entry_barrier(a, &s_ok);
+    if (s_ok) {
+        const int W = a.comm.world, me = a.comm.rank;
+        const int64_t per = (a.n4 + W - 1) / W;
+        const int64_t lo = per * me, hi = min(a.n4, lo + per);
+        float4* mc = reinterpret_cast<float4*>(a.comm.mc_buf);
+        const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+        int64_t i = lo + (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+        for (; i + 3 * stride < hi; i += 4 * stride) {          // four reduce-loads in flight per thread
+            float4 v[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) v[u] = mc_ld_reduce_add_v4(mc + i + u * stride);
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const float4 s = v[u];
+                mc_st_v4(mc + i + u * stride, make_uint4(__float_as_uint(s.x * a.scale), __float_as_uint(s.y * a.scale),
+                                                         __float_as_uint(s.z * a.scale), __float_as_uint(s.w * a.scale)));
+            }
+        }
+        for (; i < hi; i += stride) {
+            const float4 s = mc_ld_reduce_add_v4(mc + i);
+            mc_st_v4(mc + i, make_uint4(__float_as_uint(s.x * a.scale), __float_as_uint(s.y * a.scale),
+                                        __float_as_uint(s.z * a.scale), __float_as_uint(s.w * a.scale)));
+        }
+    }
+    exit_barrier(a);
+}
+
 // one-shot: result is accumulated into registers from all peers and written to the local buffer
 // only AFTER every rank has finished reading it (exit barrier inside), via a staging buffer that
 // lives right behind the data in the same symmetric allocation (bufs[me] + n4*4 floats).
@@ -167,9 +201,20 @@ extern "C" int ewdml_allreduce_state(const ewdml_comm* comm, int64_t n, float sc
     if (fill_args(a, comm, n, scale, seq, work_counter)) return EWDML_ERR_CUDA;
     a.state = state;
     cudaStream_t st = (cudaStream_t)stream;
-    if (algo == EWDML_AR_AUTO) algo = (n * 4 <= (1 << 18)) ? EWDML_AR_ONESHOT : EWDML_AR_TWOSHOT;
+    if (algo == EWDML_AR_AUTO)
+        algo = (n * 4 <= (1 << 18)) ? EWDML_AR_ONESHOT : (comm->mc_buf && comm->world > 1 ? EWDML_AR_NVLS : EWDML_AR_TWOSHOT);
+    if (algo == EWDML_AR_NVLS && !comm->mc_buf) {
+        ewdml_set_error("ewdml_allreduce: NVLS requested but the buffer has no multicast mapping");
+        return EWDML_ERR_ARG;
+    }
     const int sms = sm_count();
-    if (algo == EWDML_AR_TWOSHOT) {
+    if (algo == EWDML_AR_NVLS) {
+        int64_t per = (a.n4 + comm->world - 1) / comm->world;
+        int grid = (int)std::min<int64_t>((per + 511) / 512, (int64_t)sms);
+        if (grid < 1) grid = 1;
+        k_allreduce_nvls<<<grid, 512, 0, st>>>(a);
+        EWDML_LAUNCH_CHECK();
+    } else if (algo == EWDML_AR_TWOSHOT) {
         int64_t per = (a.n4 + comm->world - 1) / comm->world;
         int grid = (int)std::min<int64_t>((per + 511) / 512, (int64_t)sms);
         if (grid < 1) grid = 1;

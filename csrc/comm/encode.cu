@@ -59,15 +59,23 @@ __global__ void __launch_bounds__(256, 2) k_encode_push(const EncodeArgs a) {
     const uint32_t seq = a.state ? a.state[0] : a.seq;
     const uint32_t step = a.state ? a.state[1] : a.step;
     const ewdml_dests& D = a.dests[a.state ? (seq & 1u) : 0u];
+    const bool mc = D.mc_slot != nullptr;          // NVLS: payload goes out once through the multicast mapping
+    const int npush = mc ? 1 : D.n;
 
     if constexpr (MODE == EWDML_MODE_DENSE) {
         // plain tile copy into every destination (uncompressed push / allgather)
         const float* src = a.grad + td.start;
         const uint32_t n4 = (td.len + 3) >> 2;
-        for (int d = 0; d < D.n; ++d) {
-            char* dst = (char*)D.slot[d] + a.layout.data + (size_t)td.start * 4;
+        if (mc) {           // one multicast store per vector: the switch replicates it into every rank's slot
+            char* dst = (char*)D.mc_slot + a.layout.data + (size_t)td.start * 4;
             for (uint32_t i = tid; i < n4; i += 256)
-                st_na_v4(dst + (size_t)i * 16, *reinterpret_cast<const uint4*>(src + i * 4));
+                mc_st_v4(dst + (size_t)i * 16, ld_nc_v4(src + i * 4));
+        } else {
+            for (int d = 0; d < D.n; ++d) {
+                char* dst = (char*)D.slot[d] + a.layout.data + (size_t)td.start * 4;
+                for (uint32_t i = tid; i < n4; i += 256)
+                    st_na_v4(dst + (size_t)i * 16, *reinterpret_cast<const uint4*>(src + i * 4));
+            }
         }
     } else {
         // Thread t holds elements (t + 256 j) * 4 + q, j = 0..7, q = 0..3 (eight coalesced 16-byte loads) and builds its own
@@ -249,21 +257,21 @@ __global__ void __launch_bounds__(256, 2) k_encode_push(const EncodeArgs a) {
         const uint32_t off = (uint32_t)tile * a.layout.chunk_stride;
         const bool overflow = false;
         // ---- push to every destination ------------------------------------------------------
-        for (int d = 0; d < D.n; ++d) {
-            char* slot = (char*)D.slot[d];
+        for (int d = 0; d < npush; ++d) {
+            char* slot = mc ? (char*)D.mc_slot : (char*)D.slot[d];
             if (tid == 0) {
                 uint2 de = make_uint2(off, overflow ? 0u : total);
-                *reinterpret_cast<uint2*>(slot + a.layout.dir + (size_t)tile * 8) = de;
+                push_b64(slot + a.layout.dir + (size_t)tile * 8, de, mc);
             }
             if (MODE == EWDML_MODE_BITMAP)
-                reinterpret_cast<uint32_t*>(slot + a.layout.bitmap)[(size_t)tile * 256 + tid] = myword;
+                push_b32(reinterpret_cast<uint32_t*>(slot + a.layout.bitmap) + (size_t)tile * 256 + tid, myword, mc);
             if (!overflow) {
                 char* dst = slot + a.layout.data + off;
                 const uint4* si4 = reinterpret_cast<const uint4*>(s_idx);
-                for (uint32_t i = tid; i < (idx_bytes >> 4); i += 256) st_na_v4(dst + (size_t)i * 16, si4[i]);
+                for (uint32_t i = tid; i < (idx_bytes >> 4); i += 256) push_v4(dst + (size_t)i * 16, si4[i], mc);
                 const uint4* sc4 = reinterpret_cast<const uint4*>(s_code);
                 for (uint32_t i = tid; i < (code_bytes >> 4); i += 256)
-                    st_na_v4(dst + idx_bytes + (size_t)i * 16, sc4[i]);
+                    push_v4(dst + idx_bytes + (size_t)i * 16, sc4[i], mc);
             }
         }
         if (next >= a.ntiles) break;
@@ -292,17 +300,18 @@ __global__ void __launch_bounds__(256, 2) k_encode_push(const EncodeArgs a) {
         const uint32_t entries = a.ctr->entries;
         const uint32_t data_bytes = (uint32_t)a.ctr->data_used;
         const uint32_t overflow = a.ctr->overflow;
-        for (int d = 0; d < D.n; ++d) {
-            char* slot = (char*)D.slot[d];
+        for (int d = 0; d < npush; ++d) {
+            char* slot = mc ? (char*)D.mc_slot : (char*)D.slot[d];
             float* norms = reinterpret_cast<float*>(slot + a.layout.norms);
             if (MODE != EWDML_MODE_DENSE)
-                for (int s = tid; s < a.nseg; s += 256) norms[s] = a.info[s].norm;
+                for (int s = tid; s < a.nseg; s += 256) push_b32(norms + s, __float_as_uint(a.info[s].norm), mc);
             if (tid == 0) {
-                uint32_t* hdr = reinterpret_cast<uint32_t*>(slot);
-                hdr[HDR_ENTRIES] = entries;
-                hdr[HDR_DATA_BYTES] = data_bytes;
-                hdr[HDR_MODE] = (uint32_t)MODE | ((uint32_t)a.code_bits << 8) | (overflow << 31);
-                hdr[HDR_SEQ] = seq;
+                uint32_t h[4];
+                h[HDR_ENTRIES] = entries;
+                h[HDR_DATA_BYTES] = data_bytes;
+                h[HDR_MODE] = (uint32_t)MODE | ((uint32_t)a.code_bits << 8) | (overflow << 31);
+                h[HDR_SEQ] = seq;
+                push_v4(slot, make_uint4(h[0], h[1], h[2], h[3]), mc);
             }
         }
         __syncthreads();

@@ -82,6 +82,36 @@ __device__ __forceinline__ uint4 ld_v4(const void* p) {
     return v;
 }
 
+// ---------------------------------------------------------------------------------------------
+// NVLS multicast (multimem) primitives.  `p` is an address inside a mapped multicast object (runtime/vmm.cu): a store is
+// replicated by the NVSwitch into the same offset of every bound GPU's buffer, a reduce-load returns the in-switch sum
+// of all GPUs' copies.  multimem.st moves bits unchanged, so raw payload words travel through the .f32 vector form.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ void mc_st_v4(void* p, uint4 v) {
+    asm volatile("multimem.st.weak.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(__uint_as_float(v.x)),
+                 "f"(__uint_as_float(v.y)), "f"(__uint_as_float(v.z)), "f"(__uint_as_float(v.w))
+                 : "memory");
+}
+__device__ __forceinline__ void mc_st_b64(void* p, uint2 v) {
+    const unsigned long long x = ((unsigned long long)v.y << 32) | v.x;
+    asm volatile("multimem.st.weak.global.b64 [%0], %1;" ::"l"(p), "l"(x) : "memory");
+}
+__device__ __forceinline__ void mc_st_b32(void* p, uint32_t v) {
+    asm volatile("multimem.st.weak.global.b32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ float4 mc_ld_reduce_add_v4(const void* p) {
+    float4 r;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+                 : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w)
+                 : "l"(p)
+                 : "memory");
+    return r;
+}
+// unicast or multicast store of one 16-byte / 8-byte / 4-byte unit (the branch is warp-uniform)
+__device__ __forceinline__ void push_v4(void* p, uint4 v, bool mc) { if (mc) mc_st_v4(p, v); else st_na_v4(p, v); }
+__device__ __forceinline__ void push_b64(void* p, uint2 v, bool mc) { if (mc) mc_st_b64(p, v); else *reinterpret_cast<uint2*>(p) = v; }
+__device__ __forceinline__ void push_b32(void* p, uint32_t v, bool mc) { if (mc) mc_st_b32(p, v); else *reinterpret_cast<uint32_t*>(p) = v; }
+
 // Spin until *flag >= seq (sequence numbers only grow).  Returns false on timeout and records it.
 // The first EWDML_FAST_POLLS polls are back to back (a local acquire load is ~0.2 us, so that is the first
 // millisecond, where every exchange of a healthy job completes); after that each poll sleeps ~1 us, which turns

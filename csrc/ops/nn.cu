@@ -769,9 +769,280 @@ __global__ void __launch_bounds__(256) k_xent(const __nv_bfloat16* __restrict__ 
     }
 }
 
+// ---------------------------------------------------------------------------------------------
+// Streaming forms of the four BatchNorm passes (un-pooled, C % 8 == 0, C/8 a power of two <= 256).
+//
+// Round 1's kernels re-derived the channel group of every 16-byte vector (`t % c8n`) and re-loaded up to 48 per-channel
+// floats for it on every iteration, one vector in flight per thread: 16-25 % of the HBM roofline on ResNet-50, where they
+// were 55 % of the step (profiles/launch_list_resnet50_r2.txt).  Here the activation is walked as a flat array of 16-byte
+// vectors with a grid-wide stride that is a multiple of C/8, so a thread keeps ONE channel group for its whole life: the
+// per-channel constants are loaded once into registers and the loop body is four independent vector loads (eight or
+// twelve with dout / residual), the arithmetic, and the stores.  Accesses stay perfectly coalesced (consecutive threads =
+// consecutive vectors).  Statistics use a per-channel shift K (row 0 of the tensor): sums of (y - K) and (y - K)^2, so the
+// variance S2/M - (S1/M)^2 does not cancel when |mean| >> std.
+// ---------------------------------------------------------------------------------------------
+#define BN_UNROLL 4
+
+__device__ __forceinline__ void load_ch8(const float* __restrict__ p, int c8, float (&o)[8]) {
+    const float4 a = reinterpret_cast<const float4*>(p)[c8 * 2], b = reinterpret_cast<const float4*>(p)[c8 * 2 + 1];
+    o[0] = a.x; o[1] = a.y; o[2] = a.z; o[3] = a.w; o[4] = b.x; o[5] = b.y; o[6] = b.z; o[7] = b.w;
+}
+
+// CTA-level fold of per-thread partials (threads with equal tid % c8n hold the same channels) + one global atomic per
+// channel and quantity per CTA.  red: c8n * 16 floats of shared memory, zeroed by the caller before use.
+__device__ __forceinline__ void fold16_to_global(float (&s)[8], float (&q)[8], float* red, int c8n, int C, float* __restrict__ sums) {
+    const int lane = threadIdx.x & (c8n - 1);
+    fold_partials<8>(s, red, c8n < 256 ? c8n : 256, lane, 0);
+    fold_partials<8>(q, red, c8n < 256 ? c8n : 256, lane, 8);
+    __syncthreads();
+    const int c8base = (blockIdx.x * 256) & (c8n - 1);      // = 0 when c8n <= 256 (it is): kept for clarity
+    for (int i = threadIdx.x; i < c8n * 16; i += 256) {
+        const int l = i >> 4, j = i & 15, c = ((c8base + l) & (c8n - 1)) * 8 + (j & 7);
+        atomicAdd(&sums[(j < 8 ? 0 : C) + c], red[i]);
+    }
+}
+
+// sums[c] += sum(y - K), sums[C + c] += sum((y - K)^2) with K = shift_row[c] (or 0 when shift_row == NULL)
+__global__ void __launch_bounds__(256) k_colstats_stream(const __nv_bfloat16* __restrict__ y, float* __restrict__ sums, int64_t V, int c8n, int C,
+                                                         const __nv_bfloat16* __restrict__ shift_row) {
+    __shared__ float red[256 * 16];
+    for (int i = threadIdx.x; i < c8n * 16; i += 256) red[i] = 0.f;
+    __syncthreads();
+    const int64_t T = (int64_t)gridDim.x * 256;
+    int64_t v = (int64_t)blockIdx.x * 256 + threadIdx.x;
+    const int c8 = (int)(v & (c8n - 1));
+    float K[8], s[8], q[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) { K[i] = 0.f; s[i] = 0.f; q[i] = 0.f; }
+    if (shift_row) unpack8(*reinterpret_cast<const uint4*>(shift_row + c8 * 8), K);
+    const uint4* yv = reinterpret_cast<const uint4*>(y);
+    for (; v + (BN_UNROLL - 1) * T < V; v += BN_UNROLL * T) {
+        uint4 a[BN_UNROLL];
+#pragma unroll
+        for (int u = 0; u < BN_UNROLL; ++u) a[u] = yv[v + u * T];
+#pragma unroll
+        for (int u = 0; u < BN_UNROLL; ++u) {
+            float f[8];
+            unpack8(a[u], f);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) { const float d = f[i] - K[i]; s[i] += d; q[i] = fmaf(d, d, q[i]); }
+        }
+    }
+    for (; v < V; v += T) {
+        float f[8];
+        unpack8(yv[v], f);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) { const float d = f[i] - K[i]; s[i] += d; q[i] = fmaf(d, d, q[i]); }
+    }
+    fold16_to_global(s, q, red, c8n, C, sums);
+}
+
+// as k_bn_finalize, for sums taken relative to K = shift_row (bf16 [C], may be NULL = no shift)
+__global__ void k_bn_finalize_shifted(const float* __restrict__ sums, const __nv_bfloat16* __restrict__ shift_row, const float* __restrict__ gamma,
+                                      const float* __restrict__ beta, float* __restrict__ running_mean, float* __restrict__ running_var,
+                                      float* __restrict__ stats, int C, float inv_m, float unbias, float momentum, float eps,
+                                      long long* __restrict__ num_batches) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c == 0 && num_batches) *num_batches += 1;
+    if (c >= C) return;
+    const float K = shift_row ? __bfloat162float(shift_row[c]) : 0.f;
+    const float m1 = sums[c] * inv_m;
+    const float mean = K + m1;
+    float var = fmaf(-m1, m1, sums[C + c] * inv_m);
+    var = var > 0.f ? var : 0.f;
+    const float rstd = rsqrtf(var + eps);
+    const float sc = gamma[c] * rstd;
+    stats[c] = mean; stats[C + c] = rstd; stats[2 * C + c] = sc; stats[3 * C + c] = fmaf(-mean, sc, beta[c]);
+    if (running_mean) {
+        running_mean[c] = fmaf(momentum, mean - running_mean[c], running_mean[c]);
+        running_var[c] = fmaf(momentum, var * unbias - running_var[c], running_var[c]);
+    }
+}
+
+// out = act(scale*y + shift (+res))
+template <bool RES>
+__global__ void __launch_bounds__(256) k_bn_act_fwd_stream(const __nv_bfloat16* __restrict__ y, const float* __restrict__ stats,
+                                                           const __nv_bfloat16* __restrict__ res, __nv_bfloat16* __restrict__ out, int64_t V, int c8n,
+                                                           int C, int relu, int has_affine) {
+    const int64_t T = (int64_t)gridDim.x * 256;
+    int64_t v = (int64_t)blockIdx.x * 256 + threadIdx.x;
+    const int c8 = (int)(v & (c8n - 1));
+    float sc[8], sh[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) { sc[i] = 1.f; sh[i] = 0.f; }
+    if (has_affine) { load_ch8(stats + 2 * C, c8, sc); load_ch8(stats + 3 * C, c8, sh); }
+    const uint4* yv = reinterpret_cast<const uint4*>(y);
+    const uint4* rv = reinterpret_cast<const uint4*>(res);
+    uint4* ov = reinterpret_cast<uint4*>(out);
+    const float lo = relu ? 0.f : -INFINITY;
+    for (; v + (BN_UNROLL - 1) * T < V; v += BN_UNROLL * T) {
+        uint4 a[BN_UNROLL], r[BN_UNROLL];
+#pragma unroll
+        for (int u = 0; u < BN_UNROLL; ++u) { a[u] = yv[v + u * T]; if (RES) r[u] = rv[v + u * T]; }
+#pragma unroll
+        for (int u = 0; u < BN_UNROLL; ++u) {
+            float f[8], g[8], o[8];
+            unpack8(a[u], f);
+            if (RES) unpack8(r[u], g);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) o[i] = fmaxf(pre_act(f[i], sc[i], sh[i], RES ? g[i] : 0.f), lo);
+            ov[v + u * T] = pack8(o);
+        }
+    }
+    for (; v < V; v += T) {
+        float f[8], g[8], o[8];
+        unpack8(yv[v], f);
+        if (RES) unpack8(rv[v], g);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) o[i] = fmaxf(pre_act(f[i], sc[i], sh[i], RES ? g[i] : 0.f), lo);
+        ov[v] = pack8(o);
+    }
+}
+
+// sums[c] += sum(dz), sums[C + c] += sum(dz * xhat), dz = dout masked by the recomputed ReLU
+template <bool RES>
+__global__ void __launch_bounds__(256) k_bn_bwd_reduce_stream(const __nv_bfloat16* __restrict__ y, const __nv_bfloat16* __restrict__ res,
+                                                              const __nv_bfloat16* __restrict__ dout, const float* __restrict__ stats,
+                                                              float* __restrict__ sums, int64_t V, int c8n, int C, int relu) {
+    __shared__ float red[256 * 16];
+    for (int i = threadIdx.x; i < c8n * 16; i += 256) red[i] = 0.f;
+    __syncthreads();
+    const int64_t T = (int64_t)gridDim.x * 256;
+    int64_t v = (int64_t)blockIdx.x * 256 + threadIdx.x;
+    const int c8 = (int)(v & (c8n - 1));
+    float rstd[8], nm[8], sc[8], sh[8], s[8], sx[8];
+    load_ch8(stats, c8, nm); load_ch8(stats + C, c8, rstd); load_ch8(stats + 2 * C, c8, sc); load_ch8(stats + 3 * C, c8, sh);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) { nm[i] = -nm[i] * rstd[i]; s[i] = 0.f; sx[i] = 0.f; }      // xhat = y * rstd + nm
+    const uint4* yv = reinterpret_cast<const uint4*>(y);
+    const uint4* rv = reinterpret_cast<const uint4*>(res);
+    const uint4* dv = reinterpret_cast<const uint4*>(dout);
+    const float thr = relu ? 0.f : -INFINITY;
+    constexpr int U = RES ? 2 : BN_UNROLL;
+    for (; v + (U - 1) * T < V; v += U * T) {
+        uint4 a[U], d[U], r[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) { a[u] = yv[v + u * T]; d[u] = dv[v + u * T]; if (RES) r[u] = rv[v + u * T]; }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            float f[8], g[8], e[8];
+            unpack8(a[u], f); unpack8(d[u], e);
+            if (RES) unpack8(r[u], g);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const float z = pre_act(f[i], sc[i], sh[i], RES ? g[i] : 0.f);
+                const float dz = z > thr ? e[i] : 0.f;
+                s[i] += dz;
+                sx[i] = fmaf(dz, fmaf(f[i], rstd[i], nm[i]), sx[i]);
+            }
+        }
+    }
+    for (; v < V; v += T) {
+        float f[8], g[8], e[8];
+        unpack8(yv[v], f); unpack8(dv[v], e);
+        if (RES) unpack8(rv[v], g);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const float z = pre_act(f[i], sc[i], sh[i], RES ? g[i] : 0.f);
+            const float dz = z > thr ? e[i] : 0.f;
+            s[i] += dz;
+            sx[i] = fmaf(dz, fmaf(f[i], rstd[i], nm[i]), sx[i]);
+        }
+    }
+    fold16_to_global(s, sx, red, c8n, C, sums);
+}
+
+// dy = sc * (dz - m1 - xhat * m2) = sc*dz + B*y + Cc ; dres = dz
+template <bool RES, bool DRES>
+__global__ void __launch_bounds__(256) k_bn_bwd_apply_stream(const __nv_bfloat16* __restrict__ y, const __nv_bfloat16* __restrict__ res,
+                                                             const __nv_bfloat16* __restrict__ dout, const float* __restrict__ stats,
+                                                             const float* __restrict__ sums, __nv_bfloat16* __restrict__ dy,
+                                                             __nv_bfloat16* __restrict__ dres, float* __restrict__ dgamma, float* __restrict__ dbeta,
+                                                             int64_t V, int c8n, int C, int relu, int has_affine, float inv_m) {
+    if (blockIdx.x == 0 && dgamma && dbeta && has_affine)              // parameter gradients into the flat fp32 buffer
+        for (int c = threadIdx.x; c < C; c += 256) { dbeta[c] += sums[c]; dgamma[c] += sums[C + c]; }
+    const int64_t T = (int64_t)gridDim.x * 256;
+    int64_t v = (int64_t)blockIdx.x * 256 + threadIdx.x;
+    const int c8 = (int)(v & (c8n - 1));
+    float sc[8], sh[8], B[8], Cc[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) { sc[i] = 1.f; sh[i] = 0.f; B[i] = 0.f; Cc[i] = 0.f; }
+    if (has_affine) {
+        float mean[8], rstd[8], m1[8], m2[8];
+        load_ch8(stats, c8, mean); load_ch8(stats + C, c8, rstd); load_ch8(stats + 2 * C, c8, sc); load_ch8(stats + 3 * C, c8, sh);
+        load_ch8(sums, c8, m1); load_ch8(sums + C, c8, m2);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const float k2 = sc[i] * m2[i] * inv_m;                   // sc * mean(dz * xhat)
+            B[i] = -k2 * rstd[i];
+            Cc[i] = -sc[i] * m1[i] * inv_m + k2 * mean[i] * rstd[i];
+        }
+    }
+    const uint4* yv = reinterpret_cast<const uint4*>(y);
+    const uint4* rv = reinterpret_cast<const uint4*>(res);
+    const uint4* dv = reinterpret_cast<const uint4*>(dout);
+    uint4* dyv = reinterpret_cast<uint4*>(dy);
+    uint4* drv = reinterpret_cast<uint4*>(dres);
+    const float thr = relu ? 0.f : -INFINITY;
+    constexpr int U = RES ? 2 : BN_UNROLL;
+    for (; v + (U - 1) * T < V; v += U * T) {
+        uint4 a[U], d[U], r[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) { a[u] = yv[v + u * T]; d[u] = dv[v + u * T]; if (RES) r[u] = rv[v + u * T]; }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            float f[8], g[8], e[8], o[8];
+            unpack8(a[u], f); unpack8(d[u], e);
+            if (RES) unpack8(r[u], g);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const float z = pre_act(f[i], sc[i], sh[i], RES ? g[i] : 0.f);
+                e[i] = z > thr ? e[i] : 0.f;
+                o[i] = fmaf(sc[i], e[i], fmaf(B[i], f[i], Cc[i]));
+            }
+            dyv[v + u * T] = pack8(o);
+            if (DRES) drv[v + u * T] = pack8(e);
+        }
+    }
+    for (; v < V; v += T) {
+        float f[8], g[8], e[8], o[8];
+        unpack8(yv[v], f); unpack8(dv[v], e);
+        if (RES) unpack8(rv[v], g);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const float z = pre_act(f[i], sc[i], sh[i], RES ? g[i] : 0.f);
+            e[i] = z > thr ? e[i] : 0.f;
+            o[i] = fmaf(sc[i], e[i], fmaf(B[i], f[i], Cc[i]));
+        }
+        dyv[v] = pack8(o);
+        if (DRES) drv[v] = pack8(e);
+    }
+}
+
+// launch geometry of the streaming kernels: whole CTAs of 256 threads, >= `min_per_thread` vectors per thread when the
+// tensor is big enough, at most `cap_per_sm` CTAs per SM.  c8n <= 256 and a power of two, so grid * 256 % c8n == 0.
+bool stream_ok(int C) {
+    const int c8n = C >> 3;
+    return C % 8 == 0 && c8n >= 1 && c8n <= 256 && (c8n & (c8n - 1)) == 0;
+}
+int stream_grid(int64_t V, int min_per_thread, int cap_per_sm);
+
 int grid_for(int64_t work_items, int per_cta = 256) {
     int64_t g = (work_items + per_cta - 1) / per_cta;
     const int64_t cap = 148 * 16;
+    return (int)(g < 1 ? 1 : (g > cap ? cap : g));
+}
+
+int stream_grid(int64_t V, int min_per_thread, int cap_per_sm) {
+    int dev = 0, sms = 0;
+    static int cached_sms = 0;
+    if (!cached_sms) {
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        cached_sms = sms > 0 ? sms : 148;
+    }
+    int64_t g = (V + (int64_t)256 * min_per_thread - 1) / ((int64_t)256 * min_per_thread);
+    const int64_t cap = (int64_t)cached_sms * cap_per_sm;
     return (int)(g < 1 ? 1 : (g > cap ? cap : g));
 }
 
@@ -829,6 +1100,16 @@ extern "C" int ewdml_col2im(const void* dcol, void* dx, int N, int H, int W, int
 // sums: fp32 [2*C], must be zero on entry.  want_sq: also accumulate sum of squares in sums[C..2C).
 extern "C" int ewdml_colstats(const void* y, float* sums, int64_t M, int C, int want_sq, void* stream) {
     EWDML_CHECK_ARG(y && sums && M > 0 && C > 0 && C % 2 == 0);
+    if (stream_ok(C)) {
+        // want_sq == 2: sums relative to the per-channel shift K = y[0][:] (finalize with ewdml_bn_finalize3(..., shift_row = y))
+        const int c8n = C / 8;
+        const int64_t V = M * c8n;
+        k_colstats_stream<<<stream_grid(V, 8 * (c8n > 32 ? c8n / 32 : 1), 4), 256, 0, (cudaStream_t)stream>>>(
+            (const __nv_bfloat16*)y, sums, V, c8n, C, want_sq == 2 ? (const __nv_bfloat16*)y : nullptr);
+        NN_LAUNCH_CHECK();
+        return 0;
+    }
+    if (want_sq == 2) { ewdml_set_error("ewdml_colstats: shifted sums need C/8 to be a power of two <= 256 (C = %d)", C); return EWDML_ERR_ARG; }
     if (C % 8 == 0) {
         const int c8n = C / 8, lanes = c8n < 256 ? c8n : 256, rows_par = 256 / lanes;
         const int gx = (c8n + lanes - 1) / lanes;
@@ -858,6 +1139,18 @@ extern "C" int ewdml_bn_finalize(const float* sums, const float* gamma, const fl
                                  float* stats, int C, int64_t M, float momentum, float eps, void* stream) {
     return ewdml_bn_finalize2(sums, gamma, beta, running_mean, running_var, stats, C, M, momentum, eps, nullptr, stream);
 }
+// as ewdml_bn_finalize2 for sums gathered with ewdml_colstats(..., want_sq = 2): shift_row = the tensor whose row 0 was the shift
+extern "C" int ewdml_bn_finalize3(const float* sums, const void* shift_row, const float* gamma, const float* beta, float* running_mean,
+                                  float* running_var, float* stats, int C, int64_t M, float momentum, float eps, int64_t* num_batches,
+                                  void* stream) {
+    EWDML_CHECK_ARG(sums && gamma && beta && stats && C > 0 && M > 0);
+    const float unbias = M > 1 ? (float)((double)M / (double)(M - 1)) : 1.f;
+    k_bn_finalize_shifted<<<(C + 127) / 128, 128, 0, (cudaStream_t)stream>>>(sums, (const __nv_bfloat16*)shift_row, gamma, beta, running_mean,
+                                                                             running_var, stats, C, (float)(1.0 / (double)M), unbias, momentum,
+                                                                             eps, (long long*)num_batches);
+    NN_LAUNCH_CHECK();
+    return 0;
+}
 // as above, and increments *num_batches (nn.BatchNorm2d.num_batches_tracked) in the same launch
 extern "C" int ewdml_bn_finalize2(const float* sums, const float* gamma, const float* beta, float* running_mean, float* running_var,
                                   float* stats, int C, int64_t M, float momentum, float eps, int64_t* num_batches, void* stream) {
@@ -883,6 +1176,19 @@ extern "C" int ewdml_bn_act_fwd(const void* y, const float* stats, const void* r
     ActGeom g = make_act(M, C, pool, N, H, W, relu, stats != nullptr);
     const int64_t rows_out = pool ? M / 4 : M;
     cudaStream_t st = (cudaStream_t)stream;
+    if (!pool && stream_ok(C)) {
+        const int c8n = C / 8;
+        const int64_t V = M * c8n;
+        const int grid = stream_grid(V, 4, 8);
+        if (res)
+            k_bn_act_fwd_stream<true><<<grid, 256, 0, st>>>((const __nv_bfloat16*)y, stats, (const __nv_bfloat16*)res, (__nv_bfloat16*)out, V, c8n, C,
+                                                            relu, stats != nullptr);
+        else
+            k_bn_act_fwd_stream<false><<<grid, 256, 0, st>>>((const __nv_bfloat16*)y, stats, nullptr, (__nv_bfloat16*)out, V, c8n, C, relu,
+                                                             stats != nullptr);
+        NN_LAUNCH_CHECK();
+        return 0;
+    }
     if (C % 8 == 0) {
         const int64_t total = rows_out * (C / 8);
         k_bn_act_fwd<<<grid_for(total), 256, 0, st>>>((const __nv_bfloat16*)y, stats, (const __nv_bfloat16*)res, (__nv_bfloat16*)out, g, total);
@@ -902,6 +1208,30 @@ extern "C" int ewdml_bn_act_bwd(const void* y, const float* stats, const void* r
     const int64_t M = (int64_t)N * H * W;
     ActGeom g = make_act(M, C, pool, N, H, W, relu, stats != nullptr);
     cudaStream_t st = (cudaStream_t)stream;
+    if (!pool && stream_ok(C)) {
+        const int c8n = C / 8;
+        const int64_t V = M * c8n;
+        const __nv_bfloat16 *yb = (const __nv_bfloat16*)y, *rb = (const __nv_bfloat16*)res, *db = (const __nv_bfloat16*)dout;
+        if (stats) {
+            const int grid = stream_grid(V, 8 * (c8n > 32 ? c8n / 32 : 1), 4);
+            if (res) k_bn_bwd_reduce_stream<true><<<grid, 256, 0, st>>>(yb, rb, db, stats, sums, V, c8n, C, relu);
+            else k_bn_bwd_reduce_stream<false><<<grid, 256, 0, st>>>(yb, nullptr, db, stats, sums, V, c8n, C, relu);
+            NN_LAUNCH_CHECK();
+        }
+        const int grid = stream_grid(V, 4, 8);
+        const float inv_m = (float)(1.0 / (double)M);
+        const int aff = stats != nullptr;
+#define BN_APPLY(RES_, DRES_)                                                                                                        \
+        k_bn_bwd_apply_stream<RES_, DRES_><<<grid, 256, 0, st>>>(yb, rb, db, stats, sums, (__nv_bfloat16*)dy, (__nv_bfloat16*)dres, dgamma, \
+                                                                 dbeta, V, c8n, C, relu, aff, inv_m)
+        if (res && dres) BN_APPLY(true, true);
+        else if (res) BN_APPLY(true, false);
+        else if (dres) BN_APPLY(false, true);
+        else BN_APPLY(false, false);
+#undef BN_APPLY
+        NN_LAUNCH_CHECK();
+        return 0;
+    }
     if (C % 8 == 0) {
         const int64_t units = pool ? M / 4 : M;
         if (stats) {

@@ -193,7 +193,9 @@ class Registry:
 
 registry = Registry()
 registry.register("spin_limit", 1 << 26, "device-side flag poll cap before the error word is set: 4096 back-to-back polls, then ~1 us per poll (2^26 = about a minute)")
-registry.register("allreduce_algo", "auto", "fused dense allreduce (K4): auto | oneshot | twoshot")
+registry.register("allreduce_algo", "auto", "fused dense allreduce (K4): auto | oneshot | twoshot | nvls (auto = nvls when the buffer has a multicast mapping)")
+registry.register("heap", "auto", "symmetric heap transport: auto (VMM + NVLS multicast when every rank supports it) | vmm | ipc (cudaMalloc + CUDA IPC)")
+registry.register("multicast", True, "use NVLS multicast stores / in-switch reduction when the heap provides multicast mappings")
 registry.register("coll_allreduce_algo", "auto", "collective engine allreduce: auto | oneshot | twoshot (read by the library)")
 registry.register("coll_oneshot_max_bytes", 1 << 18, "collective engine: one-shot allreduce at or below this size (read by the library)")
 registry.register("gemm_bn", 0, "experimental GEMM tile width: 256 = 128x256 tiles where N % 256 == 0 (read by the library)")

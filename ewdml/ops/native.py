@@ -34,6 +34,7 @@ def _l():
             "ewdml_colstats": [vp, vp, i64, i32, i32, vp],
             "ewdml_bn_finalize": [vp, vp, vp, vp, vp, vp, i32, i64, f32, f32, vp],
             "ewdml_bn_finalize2": [vp, vp, vp, vp, vp, vp, i32, i64, f32, f32, vp, vp],
+            "ewdml_bn_finalize3": [vp, vp, vp, vp, vp, vp, vp, i32, i64, f32, f32, vp, vp],
             "ewdml_f32_to_bf16_stats": [vp, vp, vp, vp, i64, i32, vp],
             "ewdml_bn_act_fwd": [vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, vp],
             "ewdml_bn_act_bwd": [vp, vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, vp],
@@ -276,17 +277,21 @@ class _ConvBlockFn(torch.autograd.Function):
             gemm(col, wb, out=acc, out_mode=OUT_ACCUM)
         else:
             gemm(col, wb, out=y, bias=bias)
+        shifted = False
         if split:
             L.check(lib.ewdml_f32_to_bf16_stats(_p(acc), _p(bias), _p(y), _p(sums), M, Cout, st), "f32_to_bf16_stats")
         elif train_bn and not small:
-            L.check(lib.ewdml_colstats(_p(y), _p(sums), M, Cout, 1, st), "colstats")
+            # shifted sums (relative to row 0 of y): the variance does not cancel when |mean| >> std
+            c8n = Cout // 8
+            shifted = Cout % 8 == 0 and c8n <= 256 and (c8n & (c8n - 1)) == 0
+            L.check(lib.ewdml_colstats(_p(y), _p(sums), M, Cout, 2 if shifted else 1, st), "colstats")
         stats = None
         if bn is not None:
             stats = torch.empty(4 * Cout, dtype=torch.float32, device=dev)
             if bn.training:
                 mom = bn.momentum if bn.momentum is not None else 0.1
                 track = bn.track_running_stats
-                L.check(lib.ewdml_bn_finalize2(_p(sums), _p(bn.weight.detach()), _p(bn.bias.detach()),
+                L.check(lib.ewdml_bn_finalize3(_p(sums), _p(y) if shifted else None, _p(bn.weight.detach()), _p(bn.bias.detach()),
                                                _p(bn.running_mean) if track else None, _p(bn.running_var) if track else None,
                                                _p(stats), Cout, M, float(mom), float(bn.eps),
                                                _p(bn.num_batches_tracked) if track and bn.num_batches_tracked is not None else None, st),

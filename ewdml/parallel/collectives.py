@@ -68,6 +68,7 @@ class CollectiveEngine:
         L.check(self.lib.ewdml_engine_create(C.byref(self._h), rank, world, wins, fl, slot_payload), "engine_create")
         self.slot_payload = int(self.lib.ewdml_engine_slot_payload(self._h))
         self._side: Optional[torch.cuda.Stream] = None
+        self._last_async: Optional[torch.cuda.Event] = None     # last non-blocking op still possibly in flight
 
     # ---- construction ------------------------------------------------------------------------------
     @staticmethod
@@ -123,9 +124,16 @@ class CollectiveEngine:
         return int(self.lib.ewdml_engine_calls(self._h, OPS[op]))
 
     # ---- plumbing -----------------------------------------------------------------------------------
-    @staticmethod
-    def _stream() -> C.c_void_p:
-        return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    def _stream(self) -> C.c_void_p:
+        """Stream handle for the next engine kernel.  The engine has ONE window, one set of DATA/ACK flags and one pair of
+        CTA-election counters, so only one of its kernels may run at a time: a call issued on the current stream first
+        waits for the last non-blocking operation (which runs on the side stream), and the side stream in turn waits for
+        the current stream before every ``i*`` call -- engine work is therefore totally ordered whatever mix of blocking
+        and non-blocking calls the user makes (``r = iall_reduce(a); all_reduce(b); r.wait()`` is safe)."""
+        cur = torch.cuda.current_stream()
+        if self._last_async is not None and (self._side is None or cur != self._side):
+            cur.wait_event(self._last_async)
+        return C.c_void_p(cur.cuda_stream)
 
     def _check(self, t: Optional[torch.Tensor], what: str) -> None:
         if t is None:
@@ -251,6 +259,7 @@ class CollectiveEngine:
             res = fn(*args, **kw)
             ev = torch.cuda.Event()
             ev.record(self._side)
+        self._last_async = ev
         return Request(ev, keep=(args, res))
 
     def iall_reduce(self, t, out=None, scale: float = 1.0) -> Request:

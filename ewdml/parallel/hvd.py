@@ -89,14 +89,58 @@ def _adasum_pair(a: torch.Tensor, b: torch.Tensor) -> torch.Tensor:
     return ca * a + cb * b
 
 
+def _adasum_tree_device(gathered: torch.Tensor, seg_off: torch.Tensor, seg_n: torch.Tensor, max_n: int) -> torch.Tensor:
+    """Binary Adasum tree over ``gathered[W, n]`` with the device kernels (``ewdml_adasum_pair``): every rank holds all W
+    vectors after the allgather, runs the same tree and therefore ends with bit-identical results."""
+    import ctypes as C
+    from ..runtime import lib as L
+    lib = L.load()
+    nseg = int(seg_off.numel())
+    acc = torch.zeros(3 * nseg, dtype=torch.float64, device=gathered.device)
+    st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    parts = [gathered[r] for r in range(gathered.shape[0])]
+    while len(parts) > 1:
+        nxt = []
+        for i in range(0, len(parts), 2):
+            if i + 1 >= len(parts):
+                nxt.append(parts[i])
+                continue
+            out = torch.empty_like(parts[i])
+            L.check(lib.ewdml_adasum_pair(C.c_void_p(parts[i].data_ptr()), C.c_void_p(parts[i + 1].data_ptr()),
+                                          C.c_void_p(out.data_ptr()), nseg, C.c_void_p(seg_off.data_ptr()),
+                                          C.c_void_p(seg_n.data_ptr()), int(max_n), C.c_void_p(acc.data_ptr()), st), "adasum_pair")
+            nxt.append(out)
+        parts = nxt
+    return parts[0]
+
+
+def _native_allreduce(eng, t: torch.Tensor, op: str, postscale: float) -> torch.Tensor:
+    """fp32 allreduce of one tensor on the collective engine; CPU tensors are staged through the device (there is no
+    torch.distributed group under ``init("native")``), Adasum = engine allgather + the device tree."""
+    dev = eng.device
+    t32 = t.to(device=dev, dtype=torch.float32).contiguous().reshape(-1)
+    W = eng.world
+    if op == Adasum:
+        n = t32.numel()
+        pad = (n + 31) // 32 * 32
+        mine = torch.zeros(pad, dtype=torch.float32, device=dev)
+        mine[:n] = t32
+        gathered = torch.empty(W * pad, dtype=torch.float32, device=dev)
+        eng.all_gather(mine, gathered)
+        seg_off = torch.zeros(1, dtype=torch.int64, device=dev)
+        seg_n = torch.full((1,), n, dtype=torch.int64, device=dev)
+        out = _adasum_tree_device(gathered.view(W, pad), seg_off, seg_n, n)[:n] * postscale
+    else:
+        out = eng.all_reduce(t32.clone(), scale=(1.0 / W if op == Average else 1.0) * postscale)
+    return out.view(t.shape).to(device=t.device, dtype=t.dtype)
+
+
 def allreduce(tensor: torch.Tensor, name: Optional[str] = None, op: str = Average,
               prescale_factor: float = 1.0, postscale_factor: float = 1.0) -> torch.Tensor:
     t = tensor.detach().clone() * prescale_factor
     eng = _state.get("engine")
-    if eng is not None and t.is_cuda and op != Adasum:
-        t32 = t.float().contiguous()
-        eng.all_reduce(t32, scale=(1.0 / size() if op == Average else 1.0) * postscale_factor)
-        return t32.to(tensor.dtype)
+    if eng is not None:
+        return _native_allreduce(eng, t, op, postscale_factor) if size() > 1 else t * postscale_factor
     if size() > 1:
         if op == Adasum:
             parts = [torch.empty_like(t) for _ in range(size())]
@@ -149,6 +193,114 @@ def broadcast_optimizer_state(optimizer: torch.optim.Optimizer, root_rank: int =
         optimizer.load_state_dict(obj[0])
 
 
+def _codec_of(comp):
+    """(codec name, QSGD levels, top-k ratio) of a compressor object for the native exchange kernels."""
+    from ..compress import FP16Compressor, HorovodQSGDCompressor, QSGDCompressor, TopKCompressor, TopKQSGDCompressor
+    if isinstance(comp, TopKQSGDCompressor):
+        return "topk-qsgd", comp.quantum_num, comp.compress_ratio
+    if isinstance(comp, TopKCompressor):
+        return "topk", 128, comp.compress_ratio
+    if isinstance(comp, (QSGDCompressor, HorovodQSGDCompressor)):
+        return "qsgd", comp.quantum_num, 1.0
+    if isinstance(comp, FP16Compressor):
+        return "fp16", 128, 1.0
+    if isinstance(comp, NoneCompressor):
+        return "none", 128, 1.0
+    raise TypeError(f"hvd.init('native'): no device codec for compressor {type(comp).__name__}")
+
+
+class _NativeBucket:
+    """All gradients of one optimizer as ONE flat fp32 bucket on the native exchange kernels (``hvd.init("native")``).
+
+    What ``hvd.DistributedOptimizer(compression=QSGDCompressor)`` does per parameter with compress -> allreduce ->
+    decompress (``horvod_pytorch.py:194-201``, ``horovod_compression.py:16-43``) is here two launches for the whole model:
+    K1 (per-tensor norm, QSGD levels, bit-pack, stores into every peer's mailbox -- multicast when the heap has an NVLS
+    mapping) and K2 (wait, unpack, dequantise EACH sender with ITS OWN norm, average).  Uncompressed / fp16 buckets go
+    through the engine's fused-scale allreduce; ``op=Adasum`` gathers the per-rank (decoded) gradients and runs the device
+    Adasum tree.  Segments start on 32-element boundaries, as in :class:`ewdml.parallel.flat.FlatModel`."""
+
+    def __init__(self, params, comp, pg, eng, seed: int = 0):
+        from ..runtime import lib as L
+        from .native_exchange import ExchangePlan, Mailbox, make_codec
+        self.L, self.pg, self.eng = L, pg, eng
+        self.rank, self.world = pg.rank, pg.world
+        self.params = params
+        dev = pg.device
+        self.offs, off = [], 0
+        for p in params:
+            self.offs.append(off)
+            off = (off + p.numel() + 31) // 32 * 32
+        self.total = max(off, 32)
+        self.numels = [p.numel() for p in params]
+        self.flat = torch.zeros(self.total, dtype=torch.float32, device=dev)
+        self.out = torch.zeros(self.total, dtype=torch.float32, device=dev)
+        self.views = [self.flat[o:o + n].view(p.shape) for o, n, p in zip(self.offs, self.numels, params)]
+        self.out_views = [self.out[o:o + n].view(p.shape) for o, n, p in zip(self.offs, self.numels, params)]
+        self.kind, levels, ratio = _codec_of(comp)
+        self.seed, self.q, self.exchanges = seed, 0, 0
+        self.plan = self.mb = None
+        if self.kind in ("qsgd", "topk", "topk-qsgd"):
+            self.plan = ExchangePlan(self.offs, self.numels, make_codec(self.kind, levels, ratio))
+            _state["bucket_n"] = _state.get("bucket_n", 0) + 1
+            self.mb = Mailbox(pg.alloc(f"hvd_bucket{_state['bucket_n']}", Mailbox.nbytes(self.world, self.plan.slot_bytes)),
+                              self.world, self.plan.slot_bytes)
+        self.seg_off = torch.tensor(self.offs, dtype=torch.int64, device=dev)
+        self.seg_n = torch.tensor(self.numels, dtype=torch.int64, device=dev)
+        self._gathered = None
+
+    @property
+    def bytes_sent(self) -> int:
+        if self.plan is None:
+            return int(self.exchanges * 2 * (self.world - 1) / self.world * 4 * sum(self.numels))
+        return self.exchanges * (self.world - 1) * int(self.plan.stats()["payload_bytes"])
+
+    def _decode_each(self, par: int) -> torch.Tensor:
+        """[W, total]: every sender's payload decoded on its own (needed by Adasum, which is not a plain average)."""
+        W, me, mb, L = self.world, self.rank, self.mb, self.L
+        if self._gathered is None:
+            self._gathered = torch.zeros(W, self.total, dtype=torch.float32, device=self.flat.device)
+        for r in range(W):
+            self.plan.recv_apply([(mb.slot(me, par, r), mb.flag(me, par, r))], self.q, 1.0, L.OUT_GRAD, out=self._gathered[r])
+        return self._gathered
+
+    def average(self, op: str, predivide: float) -> None:
+        """p.grad <- reduction over ranks of p.grad (in place), for every parameter of the bucket."""
+        W, me, L = self.world, self.rank, self.L
+        grads = []
+        for p, v in zip(self.params, self.views):
+            if p.grad is None:                       # unused parameter on this rank: it still takes part, with zeros
+                p.grad = torch.zeros_like(p)
+            grads.append(p.grad)
+        torch._foreach_copy_(self.views, grads)
+        if predivide != 1.0:
+            self.flat.div_(predivide)
+        self.exchanges += 1
+        max_n = max(self.numels)
+        if self.plan is None:
+            if self.kind == "fp16":
+                self.flat.copy_(self.flat.half().float())
+            if op == Adasum:
+                g = torch.empty(W * self.total, dtype=torch.float32, device=self.flat.device)
+                self.eng.all_gather(self.flat, g)
+                res = _adasum_tree_device(g.view(W, self.total), self.seg_off, self.seg_n, max_n) * predivide
+            else:
+                res = self.eng.all_reduce(self.flat, scale=(1.0 / W if op == Average else 1.0) * predivide)
+        else:
+            self.q += 1
+            par = self.q & 1
+            mb = self.mb
+            self.plan.send(self.flat, [(mb.slot(r, par, me), mb.flag(r, par, me)) for r in range(W)], self.q, self.seed,
+                           self.q, me, mc_slot=mb.mc_slot(par, me))
+            if op == Adasum:
+                res = _adasum_tree_device(self._decode_each(par), self.seg_off, self.seg_n, max_n) * predivide
+            else:
+                self.plan.recv_apply([(mb.slot(me, par, r), mb.flag(me, par, r)) for r in range(W)], self.q,
+                                     float(W) if op == Average else 1.0, L.OUT_GRAD, out=self.out)
+                res = self.out if predivide == 1.0 else self.out.mul_(predivide)
+        res_views = [res[o:o + n].view(p.shape) for o, n, p in zip(self.offs, self.numels, self.params)]
+        torch._foreach_copy_(grads, res_views)
+
+
 class _DistributedOptimizer:
     def __init__(self, optimizer, named_parameters=None, compression=Compression.none, op: str = Average,
                  gradient_predivide_factor: float = 1.0):
@@ -158,7 +310,16 @@ class _DistributedOptimizer:
         self._predivide = gradient_predivide_factor
         self._params = [p for g in optimizer.param_groups for p in g["params"]]
         self._synchronized = False
-        self.bytes_sent = 0
+        self._bytes_sent = 0
+        self._bucket = None
+        if _state.get("engine") is not None and size() > 1 and any(p.is_cuda for p in self._params):
+            # native runtime: one flat bucket on the exchange kernels (every rank constructs it at the same point)
+            self._bucket = _NativeBucket([p for p in self._params if p.requires_grad], self._compression, _state["pg"],
+                                         _state["engine"])
+
+    @property
+    def bytes_sent(self) -> int:
+        return self._bucket.bytes_sent if self._bucket is not None else self._bytes_sent
 
     def __getattr__(self, item):
         return getattr(self._opt, item)
@@ -168,6 +329,12 @@ class _DistributedOptimizer:
 
     def synchronize(self) -> None:
         W = size()
+        if self._bucket is not None:
+            self._bucket.average(self._op, self._predivide)
+            self._synchronized = True
+            return
+        if _state.get("engine") is not None and W > 1:
+            raise RuntimeError("hvd.init('native') needs CUDA parameters for DistributedOptimizer")
         for p in self._params:
             if p.grad is None:
                 continue
@@ -176,12 +343,12 @@ class _DistributedOptimizer:
                 p.grad.copy_(allreduce(g, op=self._op, postscale_factor=self._predivide))
                 continue
             payload, ctx = self._compression.compress(g)
-            ctx_t = ctx if torch.is_tensor(ctx) else torch.zeros(1)
+            ctx_t = ctx if torch.is_tensor(ctx) else torch.zeros(1, device=payload.device)
             pl = [torch.empty_like(payload) for _ in range(W)]
             cl = [torch.empty_like(ctx_t) for _ in range(W)]
             dist.all_gather(pl, payload.contiguous())
             dist.all_gather(cl, ctx_t.contiguous())
-            self.bytes_sent += (W - 1) * (payload.numel() * payload.element_size() + 4)
+            self._bytes_sent += (W - 1) * (payload.numel() * payload.element_size() + 4)
             dec = [self._compression.decompress(q, c if torch.is_tensor(ctx) else ctx).view_as(p.grad) for q, c in zip(pl, cl)]
             if self._op == Adasum:
                 while len(dec) > 1:

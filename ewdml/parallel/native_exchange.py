@@ -82,11 +82,8 @@ class ExchangePlan:
         return C.c_void_p(torch.cuda.current_stream().cuda_stream)
 
     def send(self, grad: torch.Tensor, dests: Sequence[Tuple[int, int]], seq: int, seed: int, step: int,
-             rng_stream: int) -> None:
-        d = L.Dests()
-        d.n = len(dests)
-        for i, (slot, flag) in enumerate(dests):
-            d.slot[i], d.flag[i] = slot, flag
+             rng_stream: int, mc_slot: int = 0) -> None:
+        d = self._dests(dests, mc_slot)
         L.check(self.lib.ewdml_send(self._h, C.c_void_p(grad.data_ptr()), C.byref(d), seq & 0xFFFFFFFF,
                                     seed & 0xFFFFFFFFFFFFFFFF, step & 0xFFFFFFFF, rng_stream, self._stream()),
                 "ewdml_send")
@@ -105,11 +102,12 @@ class ExchangePlan:
                                           ptr(param_bf16), ptr(out), self._stream()), "ewdml_recv_apply")
 
     @staticmethod
-    def _dests(pairs) -> L.Dests:
+    def _dests(pairs, mc_slot: int = 0) -> L.Dests:
         d = L.Dests()
         d.n = len(pairs)
         for i, (slot, flag) in enumerate(pairs):
             d.slot[i], d.flag[i] = slot, flag
+        d.mc_slot = mc_slot or None       # NVLS: one multicast store per vector instead of one store per destination
         return d
 
     @staticmethod
@@ -120,10 +118,12 @@ class ExchangePlan:
             s.slot[i], s.flag[i] = slot, flag
         return s
 
-    def send_state(self, grad: torch.Tensor, dests_even, dests_odd, state: torch.Tensor, seed: int, rng_stream: int) -> None:
-        """Graph-replayable send: sequence number / RNG step / parity come from the device ``state``."""
-        L.check(self.lib.ewdml_send_state(self._h, C.c_void_p(grad.data_ptr()), C.byref(self._dests(dests_even)),
-                                          C.byref(self._dests(dests_odd)), C.c_void_p(state.data_ptr()),
+    def send_state(self, grad: torch.Tensor, dests_even, dests_odd, state: torch.Tensor, seed: int, rng_stream: int,
+                   mc_even: int = 0, mc_odd: int = 0) -> None:
+        """Graph-replayable send: sequence number / RNG step / parity come from the device ``state``.  ``mc_even`` /
+        ``mc_odd``: multicast addresses of the slot (NVLS), valid only when the destinations are ALL ranks' copies."""
+        L.check(self.lib.ewdml_send_state(self._h, C.c_void_p(grad.data_ptr()), C.byref(self._dests(dests_even, mc_even)),
+                                          C.byref(self._dests(dests_odd, mc_odd)), C.c_void_p(state.data_ptr()),
                                           seed & 0xFFFFFFFFFFFFFFFF, rng_stream, self._stream()), "ewdml_send_state")
 
     def recv_apply_state(self, srcs_even, srcs_odd, state: torch.Tensor, divisor: float, out_mode: int,
@@ -178,6 +178,11 @@ class Mailbox:
     def flag(self, owner: int, parity: int, src: int) -> int:
         return self.sym.ptrs[owner] + (parity * self.nsrc + src) * FLAG_STRIDE
 
+    def mc_slot(self, parity: int, src: int) -> int:
+        """Multicast address of slot (parity, src) in every rank's mailbox, or 0 (no NVLS mapping / switched off)."""
+        mc = getattr(self.sym, "mc_ptr", 0)
+        return mc + FLAG_REGION + (parity * self.nsrc + src) * self.slot_bytes if mc else 0
+
     def local_slot_bytes(self, parity: int, src: int) -> torch.Tensor:
         off = FLAG_REGION + (parity * self.nsrc + src) * self.slot_bytes
         return self.sym.local[off:off + self.slot_bytes]
@@ -223,7 +228,7 @@ class _NativeBase(Exchange):
         mb = Mailbox(self.pg.alloc("init_weights", Mailbox.nbytes(1, plan.slot_bytes)), 1, plan.slot_bytes)
         if self.rank == src:
             plan.send(self.flat.param, [(mb.slot(r, 1, 0), mb.flag(r, 1, 0)) for r in range(self.world) if r != src],
-                      1, 0, 0, 0)
+                      1, 0, 0, 0, mc_slot=mb.mc_slot(1, 0))
         else:
             plan.recv_apply([(mb.slot(self.rank, 1, 0), mb.flag(self.rank, 1, 0))], 1, 1.0, L.OUT_ASSIGN,
                             param=self.flat.param, param_bf16=self.flat.param_bf16)
@@ -321,7 +326,8 @@ class NativeAllgather(_NativeBase):
         me, W, mb = self.rank, self.world, self.mbs[b]
         src = self.flat.grad if self.residual is None else self.residual
         self.plans[b].send_state(src, [(mb.slot(r, 0, me), mb.flag(r, 0, me)) for r in range(W)],
-                                 [(mb.slot(r, 1, me), mb.flag(r, 1, me)) for r in range(W)], self.state, self.cfg.seed, me)
+                                 [(mb.slot(r, 1, me), mb.flag(r, 1, me)) for r in range(W)], self.state, self.cfg.seed, me,
+                                 mb.mc_slot(0, me), mb.mc_slot(1, me))     # all W ranks receive: one multicast store each
 
     def _recv(self, b: int) -> None:
         me, W, mb = self.rank, self.world, self.mbs[b]
@@ -449,11 +455,14 @@ class NativePSWorker(_NativeBase):
                 self.push.recv_apply_state(srcs[0], srcs[1], self.state, float(self.num_workers), L.OUT_SGD, sgd,
                                            self.flat.param, self.flat.momentum, self.flat.param_bf16)
             self._rec(1, cur)
-            self.pull.send_state(self.flat.param, dests[0], dests[1], self.state, self.cfg.seed, 0)
+            # weight pull = ONE multicast store per vector (the server's own unused pull slot receives a copy too)
+            self.pull.send_state(self.flat.param, dests[0], dests[1], self.state, self.cfg.seed, 0,
+                                 pull.mc_slot(0, 0), pull.mc_slot(1, 0))
         else:
             self.push.recv_apply_state(srcs[0], srcs[1], self.state, float(self.num_workers), L.OUT_GRAD, out=self.avg)
             self._rec(1, cur)
-            self.pull.send_state(self.avg, dests[0], dests[1], self.state, self.cfg.seed, 0)
+            self.pull.send_state(self.avg, dests[0], dests[1], self.state, self.cfg.seed, 0,
+                                 pull.mc_slot(0, 0), pull.mc_slot(1, 0))
         self._rec(2, cur)
         return self._finish_stats(st, self.pull, self.num_workers, self.num_workers, want_stats)
 
@@ -476,9 +485,11 @@ class NativeAllreduce(_NativeBase):
             self.comm.bufs[r] = grad_sym.ptrs[r]
             self.comm.peer_flags[r] = self.flags.ptrs[r]
         self.comm.flags = self.flags.ptrs[self.rank]
+        self.comm.mc_buf = getattr(grad_sym, "mc_ptr", 0) or None      # NVLS: in-switch reduction + multicast store
         self.work_counter = self.flags.ptrs[self.rank] + 2048
         from ..config import registry
-        self.algo = {"auto": L.AR_AUTO, "oneshot": L.AR_ONESHOT, "twoshot": L.AR_TWOSHOT}[registry.get("allreduce_algo")]
+        self.algo = {"auto": L.AR_AUTO, "oneshot": L.AR_ONESHOT, "twoshot": L.AR_TWOSHOT,
+                     "nvls": L.AR_NVLS}[registry.get("allreduce_algo")]
 
     def allreduce_(self, n: int, scale: float) -> None:
         L.check(self.lib.ewdml_allreduce_state(C.byref(self.comm), n, scale, self.algo, 0, C.c_void_p(self.state.data_ptr()),

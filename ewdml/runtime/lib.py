@@ -16,7 +16,7 @@ MODE_DENSE, MODE_IDX16, MODE_BITMAP = 0, 1, 2
 SEL_ALL, SEL_TOPK = 0, 1
 VAL_QSGD, VAL_RAW32 = 0, 1
 OUT_SGD, OUT_GRAD, OUT_ASSIGN = 0, 1, 2
-AR_AUTO, AR_ONESHOT, AR_TWOSHOT = 0, 1, 2
+AR_AUTO, AR_ONESHOT, AR_TWOSHOT, AR_NVLS = 0, 1, 2, 3
 (COLL_BCAST, COLL_GATHER, COLL_SCATTER, COLL_ALLGATHER, COLL_ALLTOALL, COLL_REDUCE, COLL_REDUCE_SCATTER,
  COLL_ALLREDUCE, COLL_SEND, COLL_RECV, COLL_BARRIER) = range(11)
 ALGO_AUTO, ALGO_ONESHOT, ALGO_TWOSHOT = 0, 1, 2
@@ -34,7 +34,8 @@ class Codec(C.Structure):
 
 
 class Dests(C.Structure):
-    _fields_ = [("n", C.c_int), ("slot", C.c_void_p * MAX_PEERS), ("flag", C.c_void_p * MAX_PEERS)]
+    _fields_ = [("n", C.c_int), ("slot", C.c_void_p * MAX_PEERS), ("flag", C.c_void_p * MAX_PEERS),
+                ("mc_slot", C.c_void_p)]
 
 
 class Sources(C.Structure):
@@ -48,7 +49,7 @@ class Sgd(C.Structure):
 
 class Comm(C.Structure):
     _fields_ = [("rank", C.c_int), ("world", C.c_int), ("bufs", C.c_void_p * MAX_PEERS),
-                ("peer_flags", C.c_void_p * MAX_PEERS), ("flags", C.c_void_p)]
+                ("peer_flags", C.c_void_p * MAX_PEERS), ("flags", C.c_void_p), ("mc_buf", C.c_void_p)]
 
 
 class NativeError(RuntimeError):
@@ -94,6 +95,7 @@ def load() -> C.CDLL:
         "ewdml_plan_read_seginfo": (i32, [vp, P(u32), vp]),
         "ewdml_allreduce": (i32, [P(Comm), i64, f32, i32, u32, vp, vp]),
         "ewdml_barrier": (i32, [P(Comm), u32, vp]),
+        "ewdml_adasum_pair": (i32, [vp, vp, vp, i32, vp, vp, i64, vp, vp]),
         "ewdml_get_device_error": (i32, [P(u32), vp]),
         "ewdml_set_spin_limit": (i32, [u64]),
         "ewdml_heap_alloc": (i32, [P(vp), C.c_size_t]),
@@ -102,6 +104,20 @@ def load() -> C.CDLL:
         "ewdml_heap_import": (i32, [C.c_char_p, P(vp)]),
         "ewdml_heap_unmap": (i32, [vp]),
         "ewdml_can_access_peer": (i32, [i32, i32, P(i32)]),
+        "ewdml_vmm_query": (i32, [P(i32)]),
+        "ewdml_vmm_granularity": (i32, [i32, P(C.c_size_t)]),
+        "ewdml_vmm_alloc": (i32, [P(vp), C.c_size_t, P(vp), P(i32)]),
+        "ewdml_vmm_import": (i32, [P(vp), i32, C.c_size_t, P(vp)]),
+        "ewdml_vmm_close_fd": (i32, [i32]),
+        "ewdml_vmm_free": (i32, [vp]),
+        "ewdml_mc_create": (i32, [P(vp), i32, C.c_size_t, P(i32)]),
+        "ewdml_mc_import": (i32, [P(vp), i32, C.c_size_t]),
+        "ewdml_mc_add_device": (i32, [vp]),
+        "ewdml_mc_bind_map": (i32, [vp, vp, P(vp)]),
+        "ewdml_fdx_open": (i32, [P(vp), C.c_char_p, i32, i32]),
+        "ewdml_fdx_send": (i32, [vp, i32, i32, u64, C.c_double]),
+        "ewdml_fdx_recv": (i32, [vp, u64, i32, P(i32), P(i32), C.c_double]),
+        "ewdml_fdx_close": (i32, [vp]),
         "ewdml_store_create": (i32, [P(vp), C.c_char_p, i32, i32, i32, C.c_double]),
         "ewdml_store_set": (i32, [vp, C.c_char_p, C.c_char_p, C.c_size_t]),
         "ewdml_store_get": (i32, [vp, C.c_char_p, C.c_char_p, C.c_size_t, P(C.c_size_t)]),

@@ -71,6 +71,10 @@ typedef struct {
     int n;                                   /* number of destination slots                       */
     void* slot[EWDML_MAX_PEERS];             /* peer-mapped (or local) slot base addresses        */
     uint32_t* flag[EWDML_MAX_PEERS];         /* peer-mapped flag words, set to `seq` when done    */
+    void* mc_slot;                           /* NVLS: multicast address of the same slot in EVERY rank's mailbox (or NULL).
+                                              * When set, the payload is written once through it (multimem.st, replicated
+                                              * by the NVSwitch) instead of once per slot[]; the flags are still published
+                                              * per destination through flag[].  Zero-initialise the struct.          */
 } ewdml_dests;
 
 typedef struct {
@@ -135,9 +139,13 @@ typedef struct {
     float* bufs[EWDML_MAX_PEERS];
     uint32_t* peer_flags[EWDML_MAX_PEERS];
     uint32_t* flags;
+    float* mc_buf;     /* NVLS: multicast address of the buffer (all ranks' copies), or NULL.  Zero-initialise the struct. */
 } ewdml_comm;
 
-enum { EWDML_AR_AUTO = 0, EWDML_AR_ONESHOT = 1, EWDML_AR_TWOSHOT = 2 };
+/* NVLS = in-switch reduction: rank r reads its shard with multimem.ld_reduce.add.f32 (the NVSwitch sums the W copies)
+ * and writes the scaled result to every rank with one multimem.st; needs comm->mc_buf.  AUTO picks it when available
+ * and the message is above the one-shot size.                                                                        */
+enum { EWDML_AR_AUTO = 0, EWDML_AR_ONESHOT = 1, EWDML_AR_TWOSHOT = 2, EWDML_AR_NVLS = 3 };
 /* in-place: every rank ends with scale * sum_r bufs[r][0..n) in its own buffer                  */
 int ewdml_allreduce(const ewdml_comm* comm, int64_t n, float scale, int algo, uint32_t seq,
                     uint32_t* work_counter, void* stream);
@@ -145,6 +153,11 @@ int ewdml_allreduce(const ewdml_comm* comm, int64_t n, float scale, int algo, ui
 int ewdml_allreduce_state(const ewdml_comm* comm, int64_t n, float scale, int algo, uint32_t seq,
                           const uint32_t* state, uint32_t* work_counter, void* stream);
 int ewdml_barrier(const ewdml_comm* comm, uint32_t seq, void* stream);
+/* Adasum tree node on the device (horvod_pytorch.py:35,200 op=hvd.Adasum): for every segment (tensor) of two flat fp32
+ * buffers, out = (1 - <a,b>/(2|a|^2)) a + (1 - <a,b>/(2|b|^2)) b.  seg_off / seg_n / acc are device arrays (acc: 3*nseg
+ * doubles of scratch); a and b may be peer-mapped; out may alias either.                                            */
+int ewdml_adasum_pair(const float* a, const float* b, float* out, int nseg, const int64_t* seg_off,
+                      const int64_t* seg_n, int64_t max_seg_numel, double* acc, void* stream);
 /* device error word (0 = ok) set by kernels whose flag spin exceeded the limit                  */
 int ewdml_get_device_error(uint32_t* out, void* stream);
 /* poll cap of every flag wait: 4096 back-to-back polls, then ~1 us per poll; 0 = default 2^26 (about a minute) */
@@ -283,6 +296,12 @@ int ewdml_colstats(const void* y, float* sums, int64_t M, int C, int want_sq, vo
 int ewdml_bn_finalize(const float* sums, const float* gamma, const float* beta, float* running_mean,
                       float* running_var, float* stats, int C, int64_t M, float momentum, float eps, void* stream);
 int ewdml_bn_finalize2(const float* sums, const float* gamma, const float* beta, float* running_mean,
+                       float* running_var, float* stats, int C, int64_t M, float momentum, float eps,
+                       int64_t* num_batches_tracked, void* stream);
+/* want_sq = 2 in ewdml_colstats gathers the sums relative to a per-channel shift K = y[0][:] (sum(y-K), sum((y-K)^2):
+ * no cancellation in the variance when |mean| >> std; needs C/8 a power of two <= 256); finalize those with
+ * ewdml_bn_finalize3(sums, shift_row = y, ...).  shift_row == NULL makes finalize3 identical to finalize2.            */
+int ewdml_bn_finalize3(const float* sums, const void* shift_row, const float* gamma, const float* beta, float* running_mean,
                        float* running_var, float* stats, int C, int64_t M, float momentum, float eps,
                        int64_t* num_batches_tracked, void* stream);
 /* split-K epilogue: bf16 dst = fp32 src + bias, optionally accumulating BatchNorm column statistics in the same pass */

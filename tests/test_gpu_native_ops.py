@@ -189,3 +189,81 @@ def test_whole_model_native_matches_torch(name, shape):
     mean_nat, mean_amp = sum(cos_nat) / len(cos_nat), sum(cos_amp) / len(cos_amp)
     assert mean_nat >= mean_amp - 0.03, (mean_nat, mean_amp)
     assert min(cos_nat) >= min(cos_amp) - 0.15, (min(cos_nat), min(cos_amp))
+
+
+@pytest.mark.parametrize("C,M,mean,std", [(64, 4096, 0.0, 1.0), (256, 1000, 1000.0, 2.0), (2048, 520, -300.0, 0.5), (8, 77, 5.0, 1.0)])
+def test_batchnorm_statistics_shifted(C, M, mean, std):
+    """ewdml_colstats(want_sq=2) + ewdml_bn_finalize3: sums are taken relative to row 0, so mean/var stay accurate when
+    |mean| >> std (E[x^2] - mean^2 in fp32 loses the variance there).  Reference: float64 statistics of the same bf16 data."""
+    import ctypes as Ct
+    from ewdml.ops import native
+    lib = native._l()
+    torch.manual_seed(1)
+    y = (torch.randn(M, C, device=DEV) * std + mean).to(torch.bfloat16).contiguous()
+    gamma = torch.rand(C, device=DEV) + 0.5
+    beta = torch.randn(C, device=DEV)
+    sums = torch.zeros(2 * C, device=DEV)
+    stats = torch.empty(4 * C, device=DEV)
+    st = native._stream()
+    p = native._p
+    native.L.check(lib.ewdml_colstats(p(y), p(sums), M, C, 2, st), "colstats")
+    native.L.check(lib.ewdml_bn_finalize3(p(sums), p(y), p(gamma), p(beta), None, None, p(stats), C, M, 0.1, 1e-5, None, st), "finalize3")
+    torch.cuda.synchronize()
+    yd = y.double()
+    ref_mean, ref_var = yd.mean(0), yd.var(0, unbiased=False)
+    got_mean, got_rstd = stats[:C].double(), stats[C:2 * C].double()
+    assert torch.allclose(got_mean, ref_mean, rtol=1e-5, atol=1e-4 * std)
+    assert torch.allclose(got_rstd, 1.0 / torch.sqrt(ref_var + 1e-5), rtol=2e-3)
+
+
+@pytest.mark.parametrize("C,hw,res,relu", [(64, 32, False, True), (256, 16, True, True), (2048, 4, True, False), (512, 8, False, True),
+                                            (24, 8, False, True)])
+def test_bn_act_forward_backward_streaming(C, hw, res, relu):
+    """Un-pooled BatchNorm + residual + ReLU forward/backward (the streaming kernels for C/8 a power of two, the generic ones
+    otherwise) against fp32 torch autograd on the same bf16 inputs."""
+    from ewdml.ops import native
+    lib = native._l()
+    p, st = native._p, native._stream()
+    torch.manual_seed(2)
+    N = 8
+    M = N * hw * hw
+    y = _round(torch.randn(M, C, device=DEV) * 1.5 + 0.3)
+    r = _round(torch.randn(M, C, device=DEV)) if res else None
+    dout = _round(torch.randn(M, C, device=DEV))
+    gamma = _round(torch.rand(C, device=DEV) + 0.5)
+    beta = _round(torch.randn(C, device=DEV) * 0.2)
+    # reference
+    yr = y.clone().requires_grad_(True)
+    rr = r.clone().requires_grad_(True) if res else None
+    g_, b_ = gamma.clone().requires_grad_(True), beta.clone().requires_grad_(True)
+    z = F.batch_norm(yr, None, None, g_, b_, True, 0.1, 1e-5)
+    if res:
+        z = z + rr
+    o_ref = F.relu(z) if relu else z
+    o_ref.backward(dout)
+    # native
+    yb = y.to(torch.bfloat16).contiguous()
+    rb = r.to(torch.bfloat16).contiguous() if res else None
+    db = dout.to(torch.bfloat16).contiguous()
+    sums = torch.zeros(2 * C, device=DEV)
+    stats = torch.empty(4 * C, device=DEV)
+    c8n = C // 8
+    shifted = C % 8 == 0 and c8n <= 256 and (c8n & (c8n - 1)) == 0
+    native.L.check(lib.ewdml_colstats(p(yb), p(sums), M, C, 2 if shifted else 1, st), "colstats")
+    native.L.check(lib.ewdml_bn_finalize3(p(sums), p(yb) if shifted else None, p(gamma), p(beta), None, None, p(stats), C, M, 0.1, 1e-5,
+                                          None, st), "finalize3")
+    out = torch.empty(M, C, dtype=torch.bfloat16, device=DEV)
+    native.L.check(lib.ewdml_bn_act_fwd(p(yb), p(stats), p(rb), p(out), N, hw, hw, C, int(relu), 0, st), "fwd")
+    _close(out, o_ref, 2e-2, "out")
+    bsums = torch.zeros(2 * C, device=DEV)
+    dy = torch.empty(M, C, dtype=torch.bfloat16, device=DEV)
+    dres = torch.empty(M, C, dtype=torch.bfloat16, device=DEV) if res else None
+    dg, dbt = torch.zeros(C, device=DEV), torch.zeros(C, device=DEV)
+    native.L.check(lib.ewdml_bn_act_bwd(p(yb), p(stats), p(rb), p(db), p(bsums), p(dy), p(dres), p(dg), p(dbt), N, hw, hw, C, int(relu), 0, st),
+                   "bwd")
+    torch.cuda.synchronize()
+    _close(dy, yr.grad, 3e-2, "dy")
+    _close(dg, g_.grad, 2e-2, "dgamma")
+    _close(dbt, b_.grad, 2e-2, "dbeta")
+    if res:
+        _close(dres, rr.grad, 2e-2, "dres")

@@ -24,10 +24,10 @@ def _free_port():
     return ports
 
 
-def _worker(rank, world, port, out_dir):
+def _worker(rank, world, port, out_dir, heap="auto"):
     import ctypes as C
     os.environ.update(RANK=str(rank), WORLD_SIZE=str(world), MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port[0]),
-                      EWDML_STORE_PORT=str(port[1]))
+                      EWDML_STORE_PORT=str(port[1]), EWDML_HEAP=heap)
     from ewdml.parallel.flat import Segment
     from ewdml.parallel.host_codec import HostCodec
     from ewdml.parallel.native_exchange import ExchangePlan, Mailbox, make_codec
@@ -38,6 +38,7 @@ def _worker(rank, world, port, out_dir):
     pg = PeerGroup.from_env(dev)
     lib = L.load()
     res = {}
+    info = {"heap": pg.mode, "multicast": bool(pg.multicast)}
     # ---- sparse allgather vs oracle ---------------------------------------------------------
     sizes = [1000, 70001, 600000]
     segs, off = [], 0
@@ -60,7 +61,9 @@ def _worker(rank, world, port, out_dir):
         ok = True
         for q in (1, 2, 3):
             par = q & 1
-            plan.send(mine, [(mb.slot(r, par, rank), mb.flag(r, par, rank)) for r in range(world)], q, 7, q, rank)
+            # with an NVLS mapping the payload leaves as multicast stores (one per vector), flags stay per destination
+            plan.send(mine, [(mb.slot(r, par, rank), mb.flag(r, par, rank)) for r in range(world)], q, 7, q, rank,
+                      mc_slot=mb.mc_slot(par, rank))
             out = torch.zeros(total, device=dev)
             plan.recv_apply([(mb.slot(rank, par, r), mb.flag(rank, par, r)) for r in range(world)], q, float(world),
                             L.OUT_GRAD, out=out)
@@ -86,9 +89,14 @@ def _worker(rank, world, port, out_dir):
         comm.bufs[r] = buf.ptrs[r]
         comm.peer_flags[r] = flags.ptrs[r]
     comm.flags = flags.ptrs[rank]
+    comm.mc_buf = buf.mc_ptr or None
+    info["allreduce_nvls"] = bool(buf.mc_ptr)
     st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
     expect = sum(torch.arange(n, dtype=torch.float32) * (r + 1) for r in range(world)) / world
-    for q, algo in ((1, L.AR_TWOSHOT), (2, L.AR_ONESHOT), (3, L.AR_TWOSHOT)):
+    algos = [(1, L.AR_TWOSHOT), (2, L.AR_ONESHOT), (3, L.AR_TWOSHOT)]
+    if buf.mc_ptr:          # in-switch reduction (multimem.ld_reduce) + multicast store
+        algos += [(4, L.AR_NVLS), (5, L.AR_NVLS), (6, L.AR_AUTO)]
+    for q, algo in algos:
         x.copy_(torch.arange(n, dtype=torch.float32) * (rank + 1))
         torch.cuda.synchronize()
         pg.host_barrier(f"ar_in_{q}")
@@ -147,19 +155,26 @@ def _worker(rank, world, port, out_dir):
     L.check(lib.ewdml_get_device_error(C.byref(err), st))
     res["device_error"] = err.value
     with open(os.path.join(out_dir, f"r{rank}.json"), "w") as f:
-        json.dump(res, f)
+        json.dump({"res": res, "info": info}, f)
     pg.close()
 
 
+@pytest.mark.parametrize("heap", ["ipc", "auto"])
 @pytest.mark.parametrize("world", [2, 8])
-def test_two_gpu_exchange_and_allreduce(tmp_path, world):
+def test_two_gpu_exchange_and_allreduce(tmp_path, world, heap):
+    """heap=ipc: cudaMalloc + CUDA IPC, unicast pushes.  heap=auto: VMM allocations + NVLS multicast objects when the box
+    offers them (multimem.st pushes, multimem.ld_reduce allreduce), else the same as ipc."""
     if torch.cuda.device_count() < world:
         pytest.skip(f"needs {world} GPUs")
-    mp.spawn(_worker, args=(world, _free_port(), str(tmp_path)), nprocs=world, join=True)
+    mp.spawn(_worker, args=(world, _free_port(), str(tmp_path), heap), nprocs=world, join=True)
     for r in range(world):
-        res = json.load(open(os.path.join(str(tmp_path), f"r{r}.json")))
+        doc = json.load(open(os.path.join(str(tmp_path), f"r{r}.json")))
+        res = doc["res"]
         assert res.pop("device_error") == 0
-        assert all(res.values()), res
+        assert all(res.values()), (res, doc["info"])
+        if heap == "ipc":
+            assert doc["info"]["heap"] == "ipc" and not doc["info"]["multicast"]
+    print("transport:", doc["info"])
 
 
 def _trainer(rank, world, port, out_dir, exchange, method):
@@ -214,4 +229,59 @@ def test_two_gpu_training_replicas_stay_identical(tmp_path, exchange, method):
     if len(workers) > 1:
         assert workers[0]["checksum"] == pytest.approx(workers[1]["checksum"], rel=1e-9)
     if exchange == "ps" and method == 1:      # weights pull: workers hold exactly the server's weights
+        assert workers[0]["checksum"] == pytest.approx(res[0]["checksum"], rel=1e-9)
+
+
+def _ps_resnet(rank, world, port, out_dir, method, network):
+    os.environ.update(RANK=str(rank), WORLD_SIZE=str(world), MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port[0]),
+                      EWDML_STORE_PORT=str(port[1]))
+    from ewdml.config import TrainConfig
+    from ewdml.parallel.peer import PeerGroup
+    from ewdml.train.gpu import GpuTrainer
+    dev = torch.device("cuda", rank)
+    torch.cuda.set_device(dev)
+    pg = PeerGroup.from_env(dev)
+    cfg = TrainConfig(network=network, dataset="Cifar10", batch_size=16, lr=0.01, momentum=0.9, method=method, exchange="ps",
+                      topk_ratio=0.01, dtype="bf16", compute="native", enable_gpu=True).validate()
+    role = "server" if rank == 0 else "worker"
+    tr = GpuTrainer(cfg, dev, pg, role=role)
+    g = torch.Generator().manual_seed(5 + rank)
+    x = torch.randn(16, 3, 32, 32, generator=g).to(dev).contiguous(memory_format=torch.channels_last)
+    y = torch.randint(0, 10, (16,), generator=g).to(dev)
+    pg.host_barrier("built")
+    losses = []
+    eager, graphed = 2, 3
+    if role == "server":
+        for _ in range(eager + 3 + graphed):          # the workers' capture() performs 3 real warm-up exchanges
+            tr.server_step()
+    else:
+        for _ in range(eager):
+            losses.append(float(tr.step(x, y)[0]))
+        tr.capture(x, y)
+        for _ in range(graphed):
+            losses.append(float(tr.step(x, y)[0]))
+    torch.cuda.synchronize()
+    res = {"role": role, "checksum": float(tr.flat.param.double().sum()), "losses": losses, "err": tr.check_device_error(),
+           "heap": pg.mode, "multicast": bool(pg.multicast)}
+    with open(os.path.join(out_dir, f"r{rank}.json"), "w") as f:
+        json.dump(res, f)
+    pg.host_barrier("end")
+    pg.close()
+
+
+@pytest.mark.parametrize("method", [1, 3, 5])
+def test_parameter_server_resnet_all_gpus(tmp_path, method):
+    """BASELINE config 4 in small: ResNet-18 on every visible GPU (8 on the target box), rank 0 = server, native kernels,
+    eager steps then the CUDA-graph replay -- the configuration whose flag waits timed out in round 1."""
+    world = torch.cuda.device_count()
+    if world < 2:
+        pytest.skip("needs 2 GPUs")
+    mp.spawn(_ps_resnet, args=(world, _free_port(), str(tmp_path), method, "ResNet18"), nprocs=world, join=True)
+    res = [json.load(open(os.path.join(str(tmp_path), f"r{r}.json"))) for r in range(world)]
+    assert all(r["err"] == 0 for r in res), res
+    workers = [r for r in res if r["role"] == "worker"]
+    assert all(l == l for w in workers for l in w["losses"])
+    for w in workers[1:]:
+        assert w["checksum"] == pytest.approx(workers[0]["checksum"], rel=1e-9)
+    if method == 1:
         assert workers[0]["checksum"] == pytest.approx(res[0]["checksum"], rel=1e-9)
