@@ -235,4 +235,11 @@ def main(a, ClockSampler, metric_name):
                                   "ms_per_step": wall_e / a.steps, "last_loss": last_loss},
                           "clocks": clocks, "bytes_sent_per_step": sent, "gpu_launches": 0}), flush=True)
     if world > 1:
-        dist.barrier(); dist.destroy_process_group()
+        # tearing the process group down while a CUDA graph that captured NCCL kernels is alive hangs in destroy_process_group
+        # (seen at 2 GPUs): drop the graph first, and leave without the collective teardown once every rank has printed
+        import sys
+        sys.stdout.flush()
+        dist.barrier()
+        graph = None
+        torch.cuda.synchronize()
+        os._exit(0)

@@ -34,10 +34,26 @@ def main():
     pg = PeerGroup.from_env(dev)
     peaks = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "MEASURED_PEAKS.json")
     hbm = json.load(open(peaks))["hbm_gbs"] if os.path.exists(peaks) else HBM_GBS
-    sizes_mb = [1, 16, 256] if a.quick else [1, 4, 16, 64, 256, 1024]
+    sizes_mb = [1, 16, 256] if a.quick else [1, 16, 64, 256, 1024]
     combos = [("topk-qsgd", 0.01, 128)] if a.quick else \
         [("topk-qsgd", r, 128) for r in (0.001, 0.01, 0.1)] + [("topk-qsgd", 0.01, s) for s in (4, 16, 256)] + \
         [("topk", 0.01, 128), ("qsgd", 1.0, 128), ("none", 1.0, 128)]
+
+    def timeit2(send, recv):
+        """median (K1 ms, K2 ms, total ms), each the max over ranks: K1 = select + encode + push, K2 = wait + decode + average."""
+        rows = []
+        for i in range(3 + a.iters):
+            torch.cuda.synchronize()
+            if world > 1:
+                dist.barrier()
+            e = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
+            e[0].record(); send(); e[1].record(); recv(); e[2].record(); torch.cuda.synchronize()
+            t = torch.tensor([e[0].elapsed_time(e[1]), e[1].elapsed_time(e[2]), e[0].elapsed_time(e[2])], device=dev)
+            if world > 1:
+                dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            if i >= 3:
+                rows.append(t.tolist())
+        return [statistics.median(r[j] for r in rows) for j in range(3)]
 
     def timeit(fn):
         ts = []
@@ -71,16 +87,20 @@ def main():
             lib = L.load()
             import ctypes as C
 
-            def ours():
+            def k1():
                 L.check(lib.ewdml_state_advance(C.c_void_p(state.data_ptr()), 1, ExchangePlan._stream()))
                 plan.send_state(g, [(mb_.slot(r, 0, rank), mb_.flag(r, 0, rank)) for r in range(world)],
-                                [(mb_.slot(r, 1, rank), mb_.flag(r, 1, rank)) for r in range(world)], state, 1, rank)
+                                [(mb_.slot(r, 1, rank), mb_.flag(r, 1, rank)) for r in range(world)], state, 1, rank,
+                                mb_.mc_slot(0, rank), mb_.mc_slot(1, rank))
+
+            def k2():
                 plan.recv_apply_state([(mb_.slot(rank, 0, r), mb_.flag(rank, 0, r)) for r in range(world)],
                                       [(mb_.slot(rank, 1, r), mb_.flag(rank, 1, r)) for r in range(world)], state,
                                       float(world), L.OUT_GRAD, out=out)
-            t_ours = timeit(ours)
+            t_k1, t_k2, t_ours = timeit2(k1, k2)
             st = plan.stats()
             payload = st["payload_bytes"]
+            multicast = bool(mb_.mc_slot(0, rank))
             # library path
             k = max(1, int(n * ratio))
             if comp in ("topk-qsgd", "topk"):
@@ -104,9 +124,19 @@ def main():
                         dist.all_reduce(out[:n])
                     out[:n].div_(world)
             t_lib = timeit(lib_path) if mb <= 256 or comp == "none" else None
-            t_roof = max(2 * n * 4 / (hbm * 1e9), (world - 1) * payload / (NVLINK_GBS * 1e9)) * 1e3
+            # each kernel chain against ITS OWN bytes: K1 reads the gradient twice (band pass + encode pass; once for the dense and
+            # QSGD-only codecs) and puts the payload on the wire once per peer (once in total with NVLS multicast); K2 reads the
+            # W payloads and writes the dense average
+            reads = 1 if comp in ("none", "qsgd") else 2
+            wire = payload if multicast else (world - 1) * payload
+            roof_k1 = max(reads * n * 4 / (hbm * 1e9), wire / (NVLINK_GBS * 1e9)) * 1e3
+            roof_k2 = (world * payload + n * 4) / (hbm * 1e9) * 1e3
+            t_roof = roof_k1 + roof_k2
             if rank == 0:
                 print(json.dumps({"gradient_mb": mb, "world": world, "compressor": comp, "ratio": ratio, "levels": s,
+                                  "multicast": multicast, "k1_ms": round(t_k1, 4), "k2_ms": round(t_k2, 4),
+                                  "k1_roofline_ms": round(roof_k1, 4), "k2_roofline_ms": round(roof_k2, 4),
+                                  "k1_fraction": round(roof_k1 / t_k1, 3), "k2_fraction": round(roof_k2 / t_k2, 3),
                                   "ms": round(t_ours, 4), "library_ms": None if t_lib is None else round(t_lib, 4),
                                   "speedup_vs_library": None if t_lib is None else round(t_lib / t_ours, 2),
                                   "payload_bytes": int(payload), "nvlink_bytes_per_rank": int((world - 1) * payload),
@@ -115,8 +145,10 @@ def main():
             plan.close()
             del mb_
     if world > 1:
-        dist.barrier(); dist.destroy_process_group()
+        dist.barrier()
     pg.close()
+    if world > 1:
+        dist.destroy_process_group()
 
 
 if __name__ == "__main__":

@@ -204,9 +204,20 @@ __device__ uint32_t radix_round(const uint32_t* keys, const float* raw, uint32_t
                                 uint32_t* s_digit) {
     for (int b = threadIdx.x; b < EWDML_HIST_BINS; b += blockDim.x) h[b] = 0;
     __syncthreads();
-    for (uint32_t i = threadIdx.x; i < n; i += blockDim.x) {
-        uint32_t key = RAW ? KEY(raw[i]) : keys[i];
-        if (prefix_shift >= 32 || (key >> prefix_shift) == prefix) atomicAdd(&h[(key >> shift) & digit_mask], 1u);
+    // Warp-aggregated histogram: the candidates of a band share their leading bits, so in the first round nearly every
+    // lane of a warp hits the SAME bin -- 32 serialised shared-memory atomics per warp and ~200 us for a 2.4 M-element
+    // tensor in round 1.  Lanes with equal digits elect one leader that adds their count once.  (Uniform trip count so
+    // the full-warp match is legal.)
+    const int lane = threadIdx.x & 31;
+    for (uint32_t base = 0; base < n; base += blockDim.x) {
+        const uint32_t i = base + threadIdx.x;
+        uint32_t d = 0xFFFFFFFFu;
+        if (i < n) {
+            const uint32_t key = RAW ? KEY(raw[i]) : keys[i];
+            if (prefix_shift >= 32 || (key >> prefix_shift) == prefix) d = (key >> shift) & digit_mask;
+        }
+        const uint32_t peers = __match_any_sync(0xffffffffu, d);
+        if (d != 0xFFFFFFFFu && lane == __ffs(peers) - 1) atomicAdd(&h[d], (uint32_t)__popc(peers));
     }
     __syncthreads();
     // 1024 threads x 2 bins, suffix sums via a forward scan

@@ -1019,6 +1019,292 @@ __global__ void __launch_bounds__(256) k_bn_bwd_apply_stream(const __nv_bfloat16
     }
 }
 
+// ---------------------------------------------------------------------------------------------
+// Fused BatchNorm passes: statistics + normalise in ONE cooperative kernel, backward reduce + apply in ONE.
+//
+// A training-mode BatchNorm needs the per-channel sums of the whole tensor before it can touch a single element, which
+// is why round 1 had separate kernels (colstats -> finalize -> act; reduce -> apply).  With every CTA co-resident
+// (cooperative launch, grid = SMs x occupancy) the dependency becomes a grid-wide barrier inside one kernel: phase 1
+// streams the tensor from HBM and reduces, the barrier publishes the sums, phase 2 streams the same tensor again -- now
+// largely out of the 126 MB L2 -- and writes the result.  Per layer that removes two launches forward and one backward
+// (ResNet-50: 159 launches per step) and up to a third of the HBM traffic; the tiny finalize kernel disappears into
+// phase 2 (every thread derives scale/shift for its own 8 channels, CTA 0 stores the saved statistics and updates the
+// running ones).  The kernels keep the fixed-channel-group-per-thread structure of the streaming kernels above.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t ld_acquire_gpu_u32(const uint32_t* p) {
+    uint32_t v;
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+// All CTAs of the (cooperatively launched) grid arrive; `bar` is a zero-initialised word used once per launch.
+__device__ __forceinline__ void grid_barrier_once(uint32_t* bar) {
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence();
+        atomicAdd(bar, 1u);
+        while (ld_acquire_gpu_u32(bar) < gridDim.x) __nanosleep(20);
+    }
+    __syncthreads();
+}
+__device__ __forceinline__ void ldcg_ch8(const float* p, int c8, float (&o)[8]) {      // L2 loads: written by other CTAs in phase 1
+    const float4 a = __ldcg(reinterpret_cast<const float4*>(p) + c8 * 2), b = __ldcg(reinterpret_cast<const float4*>(p) + c8 * 2 + 1);
+    o[0] = a.x; o[1] = a.y; o[2] = a.z; o[3] = a.w; o[4] = b.x; o[5] = b.y; o[6] = b.z; o[7] = b.w;
+}
+
+struct BnFwdArgs {
+    const __nv_bfloat16* y; const __nv_bfloat16* res; __nv_bfloat16* out;
+    float* sums;            // [2C] zero on entry (have_sums = 0) or finished un-shifted sums (have_sums = 1)
+    uint32_t* bar;          // zero on entry
+    const float* gamma; const float* beta;
+    float* running_mean; float* running_var; long long* num_batches;
+    float* stats;           // out: [mean | rstd | scale | shift]
+    int64_t V; int c8n, C, relu, have_sums;
+    float inv_m, unbias, momentum, eps;
+};
+
+#define BN_U1 8      // vectors in flight per thread, one input stream
+
+template <bool RES>
+__global__ void __launch_bounds__(256) k_bn_fwd_coop(const BnFwdArgs a) {
+    __shared__ float red[256 * 16];
+    const int64_t T = (int64_t)gridDim.x * 256;
+    const int64_t g0 = (int64_t)blockIdx.x * 256 + threadIdx.x;
+    const int c8 = (int)(g0 & (a.c8n - 1));
+    const uint4* yv = reinterpret_cast<const uint4*>(a.y);
+    float K[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) K[i] = 0.f;
+    if (!a.have_sums) {
+        // ---- phase 1: sums of (y - K), (y - K)^2 with K = row 0 ---------------------------------------
+        for (int i = threadIdx.x; i < a.c8n * 16; i += 256) red[i] = 0.f;
+        __syncthreads();
+        unpack8(yv[c8], K);
+        float s[8], q[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) { s[i] = 0.f; q[i] = 0.f; }
+        int64_t v = g0;
+        for (; v + (BN_U1 - 1) * T < a.V; v += BN_U1 * T) {
+            uint4 x[BN_U1];
+#pragma unroll
+            for (int u = 0; u < BN_U1; ++u) x[u] = yv[v + u * T];
+#pragma unroll
+            for (int u = 0; u < BN_U1; ++u) {
+                float f[8];
+                unpack8(x[u], f);
+#pragma unroll
+                for (int i = 0; i < 8; ++i) { const float d = f[i] - K[i]; s[i] += d; q[i] = fmaf(d, d, q[i]); }
+            }
+        }
+        for (; v < a.V; v += T) {
+            float f[8];
+            unpack8(yv[v], f);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) { const float d = f[i] - K[i]; s[i] += d; q[i] = fmaf(d, d, q[i]); }
+        }
+        fold16_to_global(s, q, red, a.c8n, a.C, a.sums);
+        grid_barrier_once(a.bar);
+    }
+    // ---- phase 2: scale / shift for this thread's channels, then normalise ------------------------------
+    float sc[8], sh[8];
+    {
+        float s1[8], s2[8], ga[8], be[8];
+        ldcg_ch8(a.sums, c8, s1); ldcg_ch8(a.sums + a.C, c8, s2);
+        load_ch8(a.gamma, c8, ga); load_ch8(a.beta, c8, be);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const float m1 = s1[i] * a.inv_m;
+            const float mean = K[i] + m1;
+            float var = fmaf(-m1, m1, s2[i] * a.inv_m);
+            var = var > 0.f ? var : 0.f;
+            sc[i] = ga[i] * rsqrtf(var + a.eps);
+            sh[i] = fmaf(-mean, sc[i], be[i]);
+        }
+    }
+    if (blockIdx.x == 0) {          // saved statistics for the backward pass + running statistics (nn.BatchNorm2d semantics)
+        if (threadIdx.x == 0 && a.num_batches) *a.num_batches += 1;
+        for (int c = threadIdx.x; c < a.C; c += 256) {
+            const float Kc = a.have_sums ? 0.f : __bfloat162float(a.y[c]);
+            const float m1 = __ldcg(a.sums + c) * a.inv_m;
+            const float mean = Kc + m1;
+            float var = fmaf(-m1, m1, __ldcg(a.sums + a.C + c) * a.inv_m);
+            var = var > 0.f ? var : 0.f;
+            const float rstd = rsqrtf(var + a.eps);
+            const float s = a.gamma[c] * rstd;
+            a.stats[c] = mean; a.stats[a.C + c] = rstd; a.stats[2 * a.C + c] = s; a.stats[3 * a.C + c] = fmaf(-mean, s, a.beta[c]);
+            if (a.running_mean) {
+                a.running_mean[c] = fmaf(a.momentum, mean - a.running_mean[c], a.running_mean[c]);
+                a.running_var[c] = fmaf(a.momentum, var * a.unbias - a.running_var[c], a.running_var[c]);
+            }
+        }
+    }
+    const uint4* rv = reinterpret_cast<const uint4*>(a.res);
+    uint4* ov = reinterpret_cast<uint4*>(a.out);
+    const float lo = a.relu ? 0.f : -INFINITY;
+    constexpr int U = RES ? 4 : BN_U1;
+    int64_t v = g0;
+    for (; v + (U - 1) * T < a.V; v += U * T) {
+        uint4 x[U], r[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) { x[u] = yv[v + u * T]; if (RES) r[u] = rv[v + u * T]; }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            float f[8], g[8], o[8];
+            unpack8(x[u], f);
+            if (RES) unpack8(r[u], g);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) o[i] = fmaxf(pre_act(f[i], sc[i], sh[i], RES ? g[i] : 0.f), lo);
+            ov[v + u * T] = pack8(o);
+        }
+    }
+    for (; v < a.V; v += T) {
+        float f[8], g[8], o[8];
+        unpack8(yv[v], f);
+        if (RES) unpack8(rv[v], g);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) o[i] = fmaxf(pre_act(f[i], sc[i], sh[i], RES ? g[i] : 0.f), lo);
+        ov[v] = pack8(o);
+    }
+}
+
+struct BnBwdArgs {
+    const __nv_bfloat16* y; const __nv_bfloat16* res; const __nv_bfloat16* dout;
+    const float* stats;
+    float* sums;            // [2C] zero on entry
+    uint32_t* bar;          // zero on entry
+    __nv_bfloat16* dy; __nv_bfloat16* dres;
+    float* dgamma; float* dbeta;
+    int64_t V; int c8n, C, relu;
+    float inv_m;
+};
+
+template <bool RES, bool DRES>
+__global__ void __launch_bounds__(256) k_bn_bwd_coop(const BnBwdArgs a) {
+    __shared__ float red[256 * 16];
+    const int64_t T = (int64_t)gridDim.x * 256;
+    const int64_t g0 = (int64_t)blockIdx.x * 256 + threadIdx.x;
+    const int c8 = (int)(g0 & (a.c8n - 1));
+    const uint4* yv = reinterpret_cast<const uint4*>(a.y);
+    const uint4* rv = reinterpret_cast<const uint4*>(a.res);
+    const uint4* dv = reinterpret_cast<const uint4*>(a.dout);
+    const float thr = a.relu ? 0.f : -INFINITY;
+    float rstd[8], nm[8], sc[8], sh[8];
+    load_ch8(a.stats, c8, nm); load_ch8(a.stats + a.C, c8, rstd); load_ch8(a.stats + 2 * a.C, c8, sc); load_ch8(a.stats + 3 * a.C, c8, sh);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) nm[i] = -nm[i] * rstd[i];               // xhat = y * rstd + nm
+    constexpr int U = RES ? 2 : 4;
+    // ---- phase 1: sum(dz), sum(dz * xhat) ---------------------------------------------------------------
+    for (int i = threadIdx.x; i < a.c8n * 16; i += 256) red[i] = 0.f;
+    __syncthreads();
+    {
+        float s[8], sx[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) { s[i] = 0.f; sx[i] = 0.f; }
+        int64_t v = g0;
+        for (; v + (U - 1) * T < a.V; v += U * T) {
+            uint4 x[U], d[U], r[U];
+#pragma unroll
+            for (int u = 0; u < U; ++u) { x[u] = yv[v + u * T]; d[u] = dv[v + u * T]; if (RES) r[u] = rv[v + u * T]; }
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                float f[8], g[8], e[8];
+                unpack8(x[u], f); unpack8(d[u], e);
+                if (RES) unpack8(r[u], g);
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    const float z = pre_act(f[i], sc[i], sh[i], RES ? g[i] : 0.f);
+                    const float dz = z > thr ? e[i] : 0.f;
+                    s[i] += dz;
+                    sx[i] = fmaf(dz, fmaf(f[i], rstd[i], nm[i]), sx[i]);
+                }
+            }
+        }
+        for (; v < a.V; v += T) {
+            float f[8], g[8], e[8];
+            unpack8(yv[v], f); unpack8(dv[v], e);
+            if (RES) unpack8(rv[v], g);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const float z = pre_act(f[i], sc[i], sh[i], RES ? g[i] : 0.f);
+                const float dz = z > thr ? e[i] : 0.f;
+                s[i] += dz;
+                sx[i] = fmaf(dz, fmaf(f[i], rstd[i], nm[i]), sx[i]);
+            }
+        }
+        fold16_to_global(s, sx, red, a.c8n, a.C, a.sums);
+    }
+    grid_barrier_once(a.bar);
+    // ---- phase 2: dy = sc*dz + B*y + Cc --------------------------------------------------------------------
+    if (blockIdx.x == 0 && a.dgamma && a.dbeta)
+        for (int c = threadIdx.x; c < a.C; c += 256) { a.dbeta[c] += __ldcg(a.sums + c); a.dgamma[c] += __ldcg(a.sums + a.C + c); }
+    float B[8], Cc[8];
+    {
+        float m1[8], m2[8];
+        ldcg_ch8(a.sums, c8, m1); ldcg_ch8(a.sums + a.C, c8, m2);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const float k2 = sc[i] * m2[i] * a.inv_m;
+            B[i] = -k2 * rstd[i];
+            Cc[i] = -sc[i] * m1[i] * a.inv_m - k2 * nm[i];              // nm = -mean * rstd
+        }
+    }
+    uint4* dyv = reinterpret_cast<uint4*>(a.dy);
+    uint4* drv = reinterpret_cast<uint4*>(a.dres);
+    int64_t v = g0;
+    for (; v + (U - 1) * T < a.V; v += U * T) {
+        uint4 x[U], d[U], r[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) { x[u] = yv[v + u * T]; d[u] = dv[v + u * T]; if (RES) r[u] = rv[v + u * T]; }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            float f[8], g[8], e[8], o[8];
+            unpack8(x[u], f); unpack8(d[u], e);
+            if (RES) unpack8(r[u], g);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const float z = pre_act(f[i], sc[i], sh[i], RES ? g[i] : 0.f);
+                e[i] = z > thr ? e[i] : 0.f;
+                o[i] = fmaf(sc[i], e[i], fmaf(B[i], f[i], Cc[i]));
+            }
+            dyv[v + u * T] = pack8(o);
+            if (DRES) drv[v + u * T] = pack8(e);
+        }
+    }
+    for (; v < a.V; v += T) {
+        float f[8], g[8], e[8], o[8];
+        unpack8(yv[v], f); unpack8(dv[v], e);
+        if (RES) unpack8(rv[v], g);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const float z = pre_act(f[i], sc[i], sh[i], RES ? g[i] : 0.f);
+            e[i] = z > thr ? e[i] : 0.f;
+            o[i] = fmaf(sc[i], e[i], fmaf(B[i], f[i], Cc[i]));
+        }
+        dyv[v] = pack8(o);
+        if (DRES) drv[v] = pack8(e);
+    }
+}
+
+int sm_count_cached() {
+    static int sms = 0;
+    if (!sms) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        if (sms <= 0) sms = 148;
+    }
+    return sms;
+}
+
+// grid of a cooperative streaming kernel: every CTA resident at once (SMs x occupancy), fewer when the tensor is small
+template <typename K>
+int coop_grid(K kernel, int64_t V, int per_thread) {
+    int occ = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, 256, 0) != cudaSuccess || occ < 1) { cudaGetLastError(); occ = 1; }
+    const int64_t cap = (int64_t)sm_count_cached() * occ;
+    int64_t g = (V + (int64_t)256 * per_thread - 1) / ((int64_t)256 * per_thread);
+    return (int)(g < 1 ? 1 : (g > cap ? cap : g));
+}
+
 // launch geometry of the streaming kernels: whole CTAs of 256 threads, >= `min_per_thread` vectors per thread when the
 // tensor is big enough, at most `cap_per_sm` CTAs per SM.  c8n <= 256 and a power of two, so grid * 256 % c8n == 0.
 bool stream_ok(int C) {
@@ -1197,6 +1483,69 @@ extern "C" int ewdml_bn_act_fwd(const void* y, const float* stats, const void* r
         k_bn_act_fwd_scalar<<<grid_for(total), 256, 0, st>>>((const __nv_bfloat16*)y, stats, (const __nv_bfloat16*)res, (__nv_bfloat16*)out, g, total);
     }
     NN_LAUNCH_CHECK();
+    return 0;
+}
+
+// Training-mode BatchNorm forward in one cooperative launch (statistics -> barrier -> normalise [+res] [+ReLU]); un-pooled
+// tensors with C/8 a power of two <= 256.  sums: fp32 [2*C + 32]: 2*C zeroed accumulators + one zeroed barrier word at
+// sums[2*C] (have_sums = 1: sums[0..2C) already hold finished UN-shifted sums, e.g. from ewdml_f32_to_bf16_stats; no
+// statistics phase, no barrier).  Writes stats = [mean | rstd | scale | shift] and updates the running statistics.
+// Returns EWDML_ERR_STATE (nothing launched) when the shape is not covered: call colstats + finalize + bn_act_fwd instead.
+extern "C" int ewdml_bn_fwd_fused(const void* y, float* sums, int have_sums, const float* gamma, const float* beta, float* running_mean,
+                                  float* running_var, int64_t* num_batches, float* stats, const void* res, void* out, int N, int H,
+                                  int W, int C, int relu, float momentum, float eps, void* stream) {
+    EWDML_CHECK_ARG(y && sums && gamma && beta && stats && out && N > 0 && C > 0);
+    if (!stream_ok(C)) return EWDML_ERR_STATE;
+    const int64_t M = (int64_t)N * H * W;
+    BnFwdArgs a;
+    a.y = (const __nv_bfloat16*)y; a.res = (const __nv_bfloat16*)res; a.out = (__nv_bfloat16*)out;
+    a.sums = sums; a.bar = reinterpret_cast<uint32_t*>(sums + 2 * C); a.gamma = gamma; a.beta = beta;
+    a.running_mean = running_mean; a.running_var = running_var; a.num_batches = (long long*)num_batches; a.stats = stats;
+    a.c8n = C / 8; a.V = M * a.c8n; a.C = C; a.relu = relu; a.have_sums = have_sums;
+    a.inv_m = (float)(1.0 / (double)M); a.unbias = M > 1 ? (float)((double)M / (double)(M - 1)) : 1.f;
+    a.momentum = momentum; a.eps = eps;
+    void* args[] = {&a};
+    cudaStream_t st = (cudaStream_t)stream;
+    cudaError_t e;
+    if (res) {
+        const int grid = coop_grid(k_bn_fwd_coop<true>, a.V, 4);
+        e = have_sums ? (k_bn_fwd_coop<true><<<grid, 256, 0, st>>>(a), cudaGetLastError())
+                      : cudaLaunchCooperativeKernel((void*)k_bn_fwd_coop<true>, dim3(grid), dim3(256), args, 0, st);
+    } else {
+        const int grid = coop_grid(k_bn_fwd_coop<false>, a.V, 8);
+        e = have_sums ? (k_bn_fwd_coop<false><<<grid, 256, 0, st>>>(a), cudaGetLastError())
+                      : cudaLaunchCooperativeKernel((void*)k_bn_fwd_coop<false>, dim3(grid), dim3(256), args, 0, st);
+    }
+    if (e != cudaSuccess) { ewdml_set_error("ewdml_bn_fwd_fused: launch failed: %s", cudaGetErrorString(e)); return (int)e; }
+    ewdml_counter_add(EWDML_CTR_COMPUTE_LAUNCHES, 1);
+    return 0;
+}
+
+// Backward of a BatchNorm block in one cooperative launch (reduce -> barrier -> apply).  Same contract as ewdml_bn_act_bwd
+// except that sums holds 2*C + 32 floats (all zero on entry; sums[2*C] is the barrier word) and stats must be given.
+// Returns EWDML_ERR_STATE (nothing launched) for shapes it does not cover (pooled blocks, C/8 not a power of two <= 256).
+extern "C" int ewdml_bn_bwd_fused(const void* y, const float* stats, const void* res, const void* dout, float* sums, void* dy, void* dres,
+                                  float* dgamma, float* dbeta, int N, int H, int W, int C, int relu, void* stream) {
+    EWDML_CHECK_ARG(y && dout && sums && dy && stats);
+    if (!stream_ok(C)) return EWDML_ERR_STATE;
+    const int64_t M = (int64_t)N * H * W;
+    BnBwdArgs a;
+    a.y = (const __nv_bfloat16*)y; a.res = (const __nv_bfloat16*)res; a.dout = (const __nv_bfloat16*)dout; a.stats = stats;
+    a.sums = sums; a.bar = reinterpret_cast<uint32_t*>(sums + 2 * C); a.dy = (__nv_bfloat16*)dy; a.dres = (__nv_bfloat16*)dres;
+    a.dgamma = dgamma; a.dbeta = dbeta; a.c8n = C / 8; a.V = M * a.c8n; a.C = C; a.relu = relu; a.inv_m = (float)(1.0 / (double)M);
+    void* args[] = {&a};
+    cudaStream_t st = (cudaStream_t)stream;
+    cudaError_t e;
+#define BWD_COOP(RES_, DRES_, PT_)                                                                                        \
+    e = cudaLaunchCooperativeKernel((void*)k_bn_bwd_coop<RES_, DRES_>, dim3(coop_grid(k_bn_bwd_coop<RES_, DRES_>, a.V, PT_)), \
+                                    dim3(256), args, 0, st)
+    if (res && dres) BWD_COOP(true, true, 2);
+    else if (res) BWD_COOP(true, false, 2);
+    else if (dres) BWD_COOP(false, true, 4);
+    else BWD_COOP(false, false, 4);
+#undef BWD_COOP
+    if (e != cudaSuccess) { ewdml_set_error("ewdml_bn_bwd_fused: launch failed: %s", cudaGetErrorString(e)); return (int)e; }
+    ewdml_counter_add(EWDML_CTR_COMPUTE_LAUNCHES, 1);
     return 0;
 }
 

@@ -9,9 +9,11 @@
 #include <netinet/tcp.h>
 #include <poll.h>
 #include <sys/socket.h>
+#include <sys/time.h>
 #include <unistd.h>
 
 #include <atomic>
+#include <cerrno>
 #include <chrono>
 #include <condition_variable>
 #include <cstring>
@@ -26,6 +28,9 @@
 void ewdml_set_error(const char* fmt, ...);
 
 namespace {
+
+// Largest value the store carries (optimizer state of a VGG-size model under Adam is ~80 MB; the length prefix is 32 bits).
+constexpr uint32_t kMaxBlob = 1u << 30;
 
 bool send_all(int fd, const void* buf, size_t n) {
     const char* p = (const char*)buf;
@@ -52,7 +57,7 @@ bool send_blob(int fd, const std::string& s) {
 bool recv_blob(int fd, std::string* s) {
     uint32_t n = 0;
     if (!recv_all(fd, &n, 4)) return false;
-    if (n > (64u << 20)) return false;
+    if (n > kMaxBlob) return false;
     s->resize(n);
     return n == 0 || recv_all(fd, &(*s)[0], n);
 }
@@ -136,8 +141,19 @@ extern "C" int ewdml_store_create(ewdml_store** out, const char* addr, int port,
         int one = 1;
         setsockopt(sv->listen_fd, SOL_SOCKET, SO_REUSEADDR, &one, sizeof(one));
         sockaddr_in sa{};
-        sa.sin_family = AF_INET; sa.sin_port = htons((uint16_t)port); sa.sin_addr.s_addr = htonl(INADDR_ANY);
-        if (::bind(sv->listen_fd, (sockaddr*)&sa, sizeof(sa)) != 0 || ::listen(sv->listen_fd, 128) != 0) {
+        sa.sin_family = AF_INET; sa.sin_port = htons((uint16_t)port);
+        // Listen only where the job says the master lives (MASTER_ADDR; loopback for single-node jobs) instead of on every
+        // interface: the store is unauthenticated, so it should not be reachable from networks the job does not use.
+        // EWDML_STORE_BIND_ANY=1 restores the wildcard (multi-homed masters whose MASTER_ADDR is not a local address).
+        const char* any = getenv("EWDML_STORE_BIND_ANY");
+        bool bound = false;
+        if (!(any && atoi(any)) && inet_pton(AF_INET, addr, &sa.sin_addr) == 1)
+            bound = ::bind(sv->listen_fd, (sockaddr*)&sa, sizeof(sa)) == 0;
+        if (!bound) {
+            sa.sin_addr.s_addr = htonl(INADDR_ANY);
+            bound = ::bind(sv->listen_fd, (sockaddr*)&sa, sizeof(sa)) == 0;
+        }
+        if (!bound || ::listen(sv->listen_fd, 128) != 0) {
             ewdml_set_error("store: cannot listen on port %d: %s", port, strerror(errno));
             ::close(sv->listen_fd); delete sv; delete s;
             return EWDML_ERR_IO;
@@ -150,7 +166,7 @@ extern "C" int ewdml_store_create(ewdml_store** out, const char* addr, int port,
         s->fd = ::socket(AF_INET, SOCK_STREAM, 0);
         sockaddr_in sa{};
         sa.sin_family = AF_INET; sa.sin_port = htons((uint16_t)port);
-        if (inet_pton(AF_INET, rank == 0 ? "127.0.0.1" : addr, &sa.sin_addr) != 1) {
+        if (inet_pton(AF_INET, addr, &sa.sin_addr) != 1) {
             ewdml_set_error("store: address must be an IPv4 literal, got %s", addr);
             ::close(s->fd); ewdml_store_destroy(s);
             return EWDML_ERR_ARG;
@@ -166,16 +182,41 @@ extern "C" int ewdml_store_create(ewdml_store** out, const char* addr, int port,
     }
     int one = 1;
     setsockopt(s->fd, IPPROTO_TCP, TCP_NODELAY, &one, sizeof(one));
+    // A blocking get / barrier waits for a peer.  A peer that died never arrives, so the wait has a deadline: after
+    // EWDML_STORE_TIMEOUT_S (default 1800 s: longer than any legitimate skew between ranks, e.g. a server waiting for its
+    // workers' last step) the call fails with EWDML_ERR_TIMEOUT instead of hanging the job.
+    const char* te = getenv("EWDML_STORE_TIMEOUT_S");
+    double wait_s = te ? atof(te) : 1800.0;
+    if (wait_s > 0) {
+        timeval tv;
+        tv.tv_sec = (time_t)wait_s;
+        tv.tv_usec = (suseconds_t)((wait_s - (double)tv.tv_sec) * 1e6);
+        setsockopt(s->fd, SOL_SOCKET, SO_RCVTIMEO, &tv, sizeof(tv));
+    }
     *out = s;
     return 0;
 }
 
+static int io_error(const char* what, const char* key) {
+    if (errno == EAGAIN || errno == EWOULDBLOCK) {
+        ewdml_set_error("%s(%s): timed out waiting for a peer (EWDML_STORE_TIMEOUT_S); the store connection is now unusable", what, key);
+        return EWDML_ERR_TIMEOUT;
+    }
+    ewdml_set_error("%s(%s): connection lost", what, key);
+    return EWDML_ERR_IO;
+}
+
 extern "C" int ewdml_store_set(ewdml_store* s, const char* key, const void* val, size_t len) {
     if (!s || !key) return EWDML_ERR_ARG;
+    if (len > kMaxBlob) {
+        ewdml_set_error("store_set(%s): value of %zu bytes exceeds the store limit of %u bytes", key, len, kMaxBlob);
+        return EWDML_ERR_OVERFLOW;
+    }
     std::lock_guard<std::mutex> lk(s->mu);
     uint8_t op = OP_SET, ok = 0;
+    errno = 0;
     if (!send_all(s->fd, &op, 1) || !send_blob(s->fd, key) || !send_blob(s->fd, std::string((const char*)val, len)) ||
-        !recv_all(s->fd, &ok, 1)) { ewdml_set_error("store_set(%s): connection lost", key); return EWDML_ERR_IO; }
+        !recv_all(s->fd, &ok, 1)) return io_error("store_set", key);
     return 0;
 }
 
@@ -184,10 +225,8 @@ extern "C" int ewdml_store_get(ewdml_store* s, const char* key, void* val, size_
     std::lock_guard<std::mutex> lk(s->mu);
     uint8_t op = OP_GET;
     std::string v;
-    if (!send_all(s->fd, &op, 1) || !send_blob(s->fd, key) || !recv_blob(s->fd, &v)) {
-        ewdml_set_error("store_get(%s): connection lost", key);
-        return EWDML_ERR_IO;
-    }
+    errno = 0;
+    if (!send_all(s->fd, &op, 1) || !send_blob(s->fd, key) || !recv_blob(s->fd, &v)) return io_error("store_get", key);
     if (len) *len = v.size();
     if (v.size() > cap) { ewdml_set_error("store_get(%s): value of %zu bytes exceeds buffer %zu", key, v.size(), cap); return EWDML_ERR_OVERFLOW; }
     if (val && !v.empty()) memcpy(val, v.data(), v.size());
@@ -203,10 +242,9 @@ extern "C" int ewdml_store_barrier(ewdml_store* s, const char* name) {
         std::lock_guard<std::mutex> lk(s->mu);
         uint8_t op = OP_ADD;
         int64_t one = 1, now = 0;
-        if (!send_all(s->fd, &op, 1) || !send_blob(s->fd, key) || !send_all(s->fd, &one, 8) || !recv_all(s->fd, &now, 8)) {
-            ewdml_set_error("store_barrier(%s): connection lost", name);
-            return EWDML_ERR_IO;
-        }
+        errno = 0;
+        if (!send_all(s->fd, &op, 1) || !send_blob(s->fd, key) || !send_all(s->fd, &one, 8) || !recv_all(s->fd, &now, 8))
+            return io_error("store_barrier", name);
     }
     std::string wait_key = "__ctr__" + key + "#" + std::to_string((int64_t)epoch * s->world);
     return ewdml_store_get(s, wait_key.c_str(), nullptr, 16, nullptr);

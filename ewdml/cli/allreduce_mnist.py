@@ -41,10 +41,17 @@ def main(argv=None):
     p.add_argument("--checkpoint-format", default="", help="rank-0 checkpoint per epoch, e.g. ./checkpoint-{epoch}.pt")
     p.add_argument("--max-steps", type=int, default=0)
     p.add_argument("--synthetic-size", type=int, default=2048)
+    p.add_argument("--backend", default="auto", choices=["auto", "native", "nccl", "gloo"],
+                   help="native = this framework's NVLink kernels (K1/K2 for compressed gradients, the collective engine for the rest); "
+                        "auto = native on CUDA when libewdml.so is built, else nccl / gloo")
     a = p.parse_args(argv)
 
     cuda = not a.no_cuda and torch.cuda.is_available()
-    hvd.init("nccl" if cuda else "gloo")
+    backend = a.backend
+    if backend == "auto":
+        from ..runtime import lib as _L
+        backend = ("native" if _L.available() else "nccl") if cuda else "gloo"
+    hvd.init(backend)
     torch.manual_seed(a.seed)
     device = torch.device("cuda", hvd.local_rank() % torch.cuda.device_count()) if cuda else torch.device("cpu")
     if cuda:

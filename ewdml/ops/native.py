@@ -7,6 +7,7 @@ gradients are accumulated by the kernels straight into the flat fp32 gradient bu
 from __future__ import annotations
 
 import ctypes as C
+import os
 from typing import Optional
 
 import torch
@@ -35,6 +36,8 @@ def _l():
             "ewdml_bn_finalize": [vp, vp, vp, vp, vp, vp, i32, i64, f32, f32, vp],
             "ewdml_bn_finalize2": [vp, vp, vp, vp, vp, vp, i32, i64, f32, f32, vp, vp],
             "ewdml_bn_finalize3": [vp, vp, vp, vp, vp, vp, vp, i32, i64, f32, f32, vp, vp],
+            "ewdml_bn_fwd_fused": [vp, vp, i32, vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, f32, f32, vp],
+            "ewdml_bn_bwd_fused": [vp, vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, vp],
             "ewdml_f32_to_bf16_stats": [vp, vp, vp, vp, i64, i32, vp],
             "ewdml_bn_act_fwd": [vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, vp],
             "ewdml_bn_act_bwd": [vp, vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, vp],
@@ -66,6 +69,16 @@ def _p(t: Optional[torch.Tensor]):
 OUT_BF16, OUT_F32, OUT_ACCUM = 0, 1, 2
 USE_SMALL_CONV = False   # direct first-layer kernels (kept for reference; im2col + tcgen05 GEMM measured faster on B200)
 USE_IGEMM = True      # implicit-GEMM path for 3x3 / stride 1 / pad 1 convolutions with C_in, C_out % 64 == 0
+# cooperative one-launch BatchNorm forward / backward (un-pooled blocks).  Correct and tested, but NOT faster on B200: the grid
+# barrier + cooperative launch cost what the two saved launches cost (ResNet-50 7.77 ms fused vs 7.60 ms with the separate
+# streaming kernels, VGG-11 1.157 vs 1.141 ms; profiles/README.md), so it stays opt-in (EWDML_FUSED_BN=1).
+USE_FUSED_BN = os.environ.get("EWDML_FUSED_BN", "0") == "1"
+
+
+def _stream_ok(c: int) -> bool:
+    """Shapes the streaming / fused BatchNorm kernels cover: C/8 a power of two <= 256 (csrc/ops/nn.cu stream_ok)."""
+    c8n = c // 8
+    return c % 8 == 0 and 1 <= c8n <= 256 and (c8n & (c8n - 1)) == 0
 
 # device step state of the active trainer (uint32[4] tensor) -- lets dropout masks change on graph replays
 STEP_STATE = {"tensor": None}
@@ -238,7 +251,9 @@ class _ConvBlockFn(torch.autograd.Function):
         wb = _weight_bf16(conv.weight, Cout, K, pad=not small)
         bias = conv.bias.detach() if conv.bias is not None else None
         train_bn = bn is not None and bn.training
-        sums = ARENA.zeros(2 * Cout, dev) if train_bn else None
+        sums = ARENA.zeros(2 * Cout + 32, dev) if train_bn else None       # + one barrier word for the fused (cooperative) BN kernel
+        # un-pooled training BatchNorm with C/8 a power of two: statistics, finalize and normalise run as ONE cooperative kernel
+        fuse_bn = USE_FUSED_BN and train_bn and not pool and _stream_ok(Cout)
         if small:
             igemm = direct = False
             col = xn
@@ -278,15 +293,31 @@ class _ConvBlockFn(torch.autograd.Function):
         else:
             gemm(col, wb, out=y, bias=bias)
         shifted = False
+        have_sums = small or split
         if split:
             L.check(lib.ewdml_f32_to_bf16_stats(_p(acc), _p(bias), _p(y), _p(sums), M, Cout, st), "f32_to_bf16_stats")
+        elif fuse_bn:
+            pass                                                       # the fused kernel gathers the statistics itself
         elif train_bn and not small:
             # shifted sums (relative to row 0 of y): the variance does not cancel when |mean| >> std
             c8n = Cout // 8
             shifted = Cout % 8 == 0 and c8n <= 256 and (c8n & (c8n - 1)) == 0
             L.check(lib.ewdml_colstats(_p(y), _p(sums), M, Cout, 2 if shifted else 1, st), "colstats")
         stats = None
-        if bn is not None:
+        resn = to_nhwc_bf16(residual) if residual is not None else None
+        fused_done = False
+        if fuse_bn:
+            stats = torch.empty(4 * Cout, dtype=torch.float32, device=dev)
+            out = torch.empty(N, HO, WO, Cout, dtype=BF16, device=dev)
+            mom = bn.momentum if bn.momentum is not None else 0.1
+            track = bn.track_running_stats
+            L.check(lib.ewdml_bn_fwd_fused(_p(y), _p(sums), int(have_sums), _p(bn.weight.detach()), _p(bn.bias.detach()),
+                                           _p(bn.running_mean) if track else None, _p(bn.running_var) if track else None,
+                                           _p(bn.num_batches_tracked) if track and bn.num_batches_tracked is not None else None,
+                                           _p(stats), _p(resn), _p(out), N, HO, WO, Cout, int(relu), float(mom), float(bn.eps), st),
+                    "bn_fwd_fused")
+            fused_done = True
+        elif bn is not None:
             stats = torch.empty(4 * Cout, dtype=torch.float32, device=dev)
             if bn.training:
                 mom = bn.momentum if bn.momentum is not None else 0.1
@@ -300,10 +331,10 @@ class _ConvBlockFn(torch.autograd.Function):
                 rstd = torch.rsqrt(bn.running_var + bn.eps)
                 sc = bn.weight.detach() * rstd
                 stats.copy_(torch.cat([bn.running_mean, rstd, sc, bn.bias.detach() - bn.running_mean * sc]))
-        resn = to_nhwc_bf16(residual) if residual is not None else None
-        HP, WP = (HO // 2, WO // 2) if pool else (HO, WO)
-        out = torch.empty(N, HP, WP, Cout, dtype=BF16, device=dev)
-        L.check(lib.ewdml_bn_act_fwd(_p(y), _p(stats), _p(resn), _p(out), N, HO, WO, Cout, int(relu), int(pool), st), "bn_act_fwd")
+        if not fused_done:
+            HP, WP = (HO // 2, WO // 2) if pool else (HO, WO)
+            out = torch.empty(N, HP, WP, Cout, dtype=BF16, device=dev)
+            L.check(lib.ewdml_bn_act_fwd(_p(y), _p(stats), _p(resn), _p(out), N, HO, WO, Cout, int(relu), int(pool), st), "bn_act_fwd")
         ctx.save_for_backward(col, y, stats if stats is not None else torch.empty(0, device=dev),
                               resn if resn is not None else torch.empty(0, device=dev))
         ctx.meta = (conv, bn, relu, pool, N, H, W, Cin, HO, WO, Cout, kh, stride, pad, M, K, Kp, direct, igemm, small)
@@ -325,7 +356,7 @@ class _ConvBlockFn(torch.autograd.Function):
         if need_dz:
             dy = torch.empty(M, Cout, dtype=BF16, device=dev)
             dres = torch.empty(M, Cout, dtype=BF16, device=dev) if ctx.has_res else None
-            sums = ARENA.zeros(2 * Cout, dev)
+            sums = ARENA.zeros(2 * Cout + 32, dev)
             dg = db = None
             if bn is not None:
                 if bn.weight.grad is None:
@@ -333,8 +364,12 @@ class _ConvBlockFn(torch.autograd.Function):
                 if bn.bias.grad is None:
                     bn.bias.grad = torch.zeros_like(bn.bias)
                 dg, db = bn.weight.grad, bn.bias.grad
-            L.check(lib.ewdml_bn_act_bwd(_p(y), _p(stats), _p(resn), _p(dn), _p(sums), _p(dy), _p(dres), _p(dg), _p(db),
-                                         N, HO, WO, Cout, int(relu), int(pool), st), "bn_act_bwd")
+            if USE_FUSED_BN and stats is not None and not pool and _stream_ok(Cout):
+                L.check(lib.ewdml_bn_bwd_fused(_p(y), _p(stats), _p(resn), _p(dn), _p(sums), _p(dy), _p(dres), _p(dg), _p(db),
+                                               N, HO, WO, Cout, int(relu), st), "bn_bwd_fused")
+            else:
+                L.check(lib.ewdml_bn_act_bwd(_p(y), _p(stats), _p(resn), _p(dn), _p(sums), _p(dy), _p(dres), _p(dg), _p(db),
+                                             N, HO, WO, Cout, int(relu), int(pool), st), "bn_act_bwd")
         else:
             dy = dn.view(M, Cout)
             dres = dy if ctx.has_res else None

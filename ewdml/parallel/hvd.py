@@ -182,9 +182,10 @@ def broadcast_optimizer_state(optimizer: torch.optim.Optimizer, root_rank: int =
             buf = io.BytesIO()
             torch.save(optimizer.state_dict(), buf)
             pg.store.set(key, buf.getvalue())
-        blob = pg.store.get(key, cap=1 << 28)
+        blob = pg.store.get(key)
         if rank() != root_rank:
-            optimizer.load_state_dict(torch.load(io.BytesIO(blob), map_location="cpu", weights_only=False))
+            # tensors + plain containers only: the store is an unauthenticated TCP service, never unpickle arbitrary objects from it
+            optimizer.load_state_dict(torch.load(io.BytesIO(blob), map_location="cpu", weights_only=True))
         pg.host_barrier(key + "/done")
         return
     obj = [optimizer.state_dict() if rank() == root_rank else None]

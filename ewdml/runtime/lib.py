@@ -185,9 +185,15 @@ class Store:
         check(self._lib.ewdml_store_set(self._h, key.encode(), val, len(val)), "store_set")
 
     def get(self, key: str, cap: int = 1 << 16) -> bytes:
+        """Blocking get.  ``cap`` is only the first guess: a larger value is fetched again into a buffer of its real size."""
         buf = C.create_string_buffer(cap)
         n = C.c_size_t()
-        check(self._lib.ewdml_store_get(self._h, key.encode(), buf, cap, C.byref(n)), "store_get")
+        rc = self._lib.ewdml_store_get(self._h, key.encode(), buf, cap, C.byref(n))
+        if rc == -4 and n.value > cap:                 # EWDML_ERR_OVERFLOW: the length is known now
+            cap = n.value
+            buf = C.create_string_buffer(cap)
+            rc = self._lib.ewdml_store_get(self._h, key.encode(), buf, cap, C.byref(n))
+        check(rc, "store_get")
         return buf.raw[:n.value]
 
     def barrier(self, name: str = "default") -> None:

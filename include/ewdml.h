@@ -304,6 +304,15 @@ int ewdml_bn_finalize2(const float* sums, const float* gamma, const float* beta,
 int ewdml_bn_finalize3(const float* sums, const void* shift_row, const float* gamma, const float* beta, float* running_mean,
                        float* running_var, float* stats, int C, int64_t M, float momentum, float eps,
                        int64_t* num_batches_tracked, void* stream);
+/* One-launch (cooperative, grid barrier inside) training BatchNorm for un-pooled blocks with C/8 a power of two <= 256:
+ * forward = statistics + finalize + normalise [+res] [+ReLU]; backward = reduce + apply (+ dgamma/dbeta).  `sums` holds
+ * 2*C + 32 zeroed floats (sums[2*C] is the barrier word); have_sums = 1 means sums[0..2C) are finished un-shifted sums
+ * (split-K epilogue) and no statistics phase runs.  EWDML_ERR_STATE = shape not covered, nothing launched.            */
+int ewdml_bn_fwd_fused(const void* y, float* sums, int have_sums, const float* gamma, const float* beta, float* running_mean,
+                       float* running_var, int64_t* num_batches_tracked, float* stats, const void* res, void* out, int N,
+                       int H, int W, int C, int relu, float momentum, float eps, void* stream);
+int ewdml_bn_bwd_fused(const void* y, const float* stats, const void* res, const void* dout, float* sums, void* dy, void* dres,
+                       float* dgamma, float* dbeta, int N, int H, int W, int C, int relu, void* stream);
 /* split-K epilogue: bf16 dst = fp32 src + bias, optionally accumulating BatchNorm column statistics in the same pass */
 int ewdml_f32_to_bf16_stats(const float* src, const float* bias, void* dst, float* sums, int64_t M, int C, void* stream);
 int ewdml_bn_act_fwd(const void* y, const float* stats, const void* res, void* out, int N, int H, int W, int C,

@@ -267,3 +267,57 @@ def test_bn_act_forward_backward_streaming(C, hw, res, relu):
     _close(dbt, b_.grad, 2e-2, "dbeta")
     if res:
         _close(dres, rr.grad, 2e-2, "dres")
+
+
+@pytest.mark.parametrize("C,hw,res,relu,mean", [(64, 32, False, True, 0.3), (256, 16, True, True, 0.3), (2048, 4, True, False, 0.0),
+                                                 (512, 8, False, True, 40.0), (8, 6, False, True, 0.0)])
+def test_bn_fused_cooperative_forward_backward(C, hw, res, relu, mean):
+    """ewdml_bn_fwd_fused / ewdml_bn_bwd_fused (statistics + normalise, reduce + apply, each ONE cooperative launch with a
+    grid barrier) against fp32 torch autograd on the same bf16 inputs, including a tensor whose mean dwarfs its spread."""
+    from ewdml.ops import native
+    lib = native._l()
+    p, st = native._p, native._stream()
+    torch.manual_seed(3)
+    N = 8
+    M = N * hw * hw
+    y = _round(torch.randn(M, C, device=DEV) * 1.5 + mean)
+    r = _round(torch.randn(M, C, device=DEV)) if res else None
+    dout = _round(torch.randn(M, C, device=DEV))
+    gamma = _round(torch.rand(C, device=DEV) + 0.5)
+    beta = _round(torch.randn(C, device=DEV) * 0.2)
+    yr = y.clone().requires_grad_(True)
+    rr = r.clone().requires_grad_(True) if res else None
+    g_, b_ = gamma.clone().requires_grad_(True), beta.clone().requires_grad_(True)
+    rm_ref, rv_ref = torch.zeros(C, device=DEV), torch.ones(C, device=DEV)
+    z = F.batch_norm(yr, rm_ref, rv_ref, g_, b_, True, 0.1, 1e-5)
+    if res:
+        z = z + rr
+    o_ref = F.relu(z) if relu else z
+    o_ref.backward(dout)
+    yb = y.to(torch.bfloat16).contiguous()
+    rb = r.to(torch.bfloat16).contiguous() if res else None
+    db = dout.to(torch.bfloat16).contiguous()
+    for rep in range(2):                               # twice: the barrier word and the sums must come back clean from the caller
+        sums = torch.zeros(2 * C + 32, device=DEV)
+        stats = torch.empty(4 * C, device=DEV)
+        rm, rv = torch.zeros(C, device=DEV), torch.ones(C, device=DEV)
+        nbt = torch.zeros((), dtype=torch.int64, device=DEV)
+        out = torch.empty(M, C, dtype=torch.bfloat16, device=DEV)
+        native.L.check(lib.ewdml_bn_fwd_fused(p(yb), p(sums), 0, p(gamma), p(beta), p(rm), p(rv), p(nbt), p(stats), p(rb), p(out),
+                                              N, hw, hw, C, int(relu), 0.1, 1e-5, st), "bn_fwd_fused")
+        _close(out, o_ref, 2e-2, "out")
+        assert int(nbt) == 1
+        assert torch.allclose(rm, rm_ref, rtol=1e-3, atol=1e-3 * max(1.0, abs(mean)))
+        assert torch.allclose(rv, rv_ref, rtol=5e-3, atol=1e-3)
+        bsums = torch.zeros(2 * C + 32, device=DEV)
+        dy = torch.empty(M, C, dtype=torch.bfloat16, device=DEV)
+        dres = torch.empty(M, C, dtype=torch.bfloat16, device=DEV) if res else None
+        dg, dbt = torch.zeros(C, device=DEV), torch.zeros(C, device=DEV)
+        native.L.check(lib.ewdml_bn_bwd_fused(p(yb), p(stats), p(rb), p(db), p(bsums), p(dy), p(dres), p(dg), p(dbt), N, hw, hw, C,
+                                              int(relu), st), "bn_bwd_fused")
+        torch.cuda.synchronize()
+        _close(dy, yr.grad, 3e-2, "dy")
+        _close(dg, g_.grad, 2e-2, "dgamma")
+        _close(dbt, b_.grad, 2e-2, "dbeta")
+        if res:
+            _close(dres, rr.grad, 2e-2, "dres")
