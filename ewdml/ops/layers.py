@@ -48,11 +48,21 @@ class BatchNorm2d(nn.BatchNorm2d):
 
 
 class ReLU(nn.ReLU):
-    pass
+    def forward(self, x):
+        if _native(x) and not self.inplace:
+            from . import native
+            return native.relu(x)
+        return super().forward(x)
 
 
 class MaxPool2d(nn.MaxPool2d):
-    pass
+    def forward(self, x):
+        k = self.kernel_size if isinstance(self.kernel_size, int) else self.kernel_size[0]
+        st = self.stride if isinstance(self.stride, int) else self.stride[0]
+        if _native(x) and x.dim() == 4 and k == 2 and st == 2 and not self.padding and not self.ceil_mode:
+            from . import native
+            return native.max_pool2x2(x)
+        return super().forward(x)
 
 
 class AvgPool2d(nn.AvgPool2d):

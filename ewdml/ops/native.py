@@ -32,6 +32,9 @@ def _l():
             "ewdml_conv_small_fwd": [vp, i32, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, i32, vp],
             "ewdml_conv_small_wgrad": [vp, i32, vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, i32, vp],
             "ewdml_col2im": [vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, vp],
+            "ewdml_conv_direct_fwd": [vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, i32, vp],
+            "ewdml_conv_direct_dgrad": [vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, i32, vp],
+            "ewdml_conv_direct_wgrad": [vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, i32, vp],
             "ewdml_colstats": [vp, vp, i64, i32, i32, vp],
             "ewdml_bn_finalize": [vp, vp, vp, vp, vp, vp, i32, i64, f32, f32, vp],
             "ewdml_bn_finalize2": [vp, vp, vp, vp, vp, vp, i32, i64, f32, f32, vp, vp],
@@ -221,7 +224,9 @@ def _colsum_into(dy2d: torch.Tensor, target: torch.Tensor) -> None:
 
 
 def _conv_supported(conv, x) -> bool:
-    return (conv.out_channels % 8 == 0 and conv.groups == 1 and conv.dilation == (1, 1)
+    """Square kernel / stride / padding, no groups, no dilation.  C_out % 8 == 0 goes to the tcgen05 GEMM paths, anything
+    else (LeNet's 20 / 50 channels) to the direct small-channel kernels (csrc/ops/conv_direct.cu)."""
+    return (conv.groups == 1 and conv.dilation == (1, 1)
             and conv.kernel_size[0] == conv.kernel_size[1] and conv.stride[0] == conv.stride[1]
             and conv.padding[0] == conv.padding[1] and isinstance(conv.padding, tuple))
 
@@ -240,21 +245,32 @@ class _ConvBlockFn(torch.autograd.Function):
         HO, WO = (H + 2 * pad - kh) // stride + 1, (W + 2 * pad - kh) // stride + 1
         M, K = N * HO * WO, kh * kh * Cin
         Kp = _r8(K)
+        generic = Cout % 8 != 0                       # direct CUDA-core kernels: channel counts the GEMM tiles do not take
         small = (USE_SMALL_CONV and Cin <= 4 and kh * kh * Cin <= 36 and Cout in (64, 128) and not ctx.needs_input_grad[0]
                  and x.dtype in (torch.float32, BF16))
         if small:
             xn = x.permute(0, 2, 3, 1).contiguous()          # NHWC view of a channels-last tensor: no copy, no cast
         else:
             xn = to_nhwc_bf16(x)
-        direct = kh == 1 and stride == 1 and pad == 0 and Cin % 8 == 0
+        direct = kh == 1 and stride == 1 and pad == 0 and Cin % 8 == 0 and not generic
         igemm = USE_IGEMM and kh == 3 and stride == 1 and pad == 1 and Cin % 64 == 0 and Cout % 64 == 0
-        wb = _weight_bf16(conv.weight, Cout, K, pad=not small)
+        wb = _weight_bf16(conv.weight, Cout, K, pad=not (small or generic))
         bias = conv.bias.detach() if conv.bias is not None else None
         train_bn = bn is not None and bn.training
         sums = ARENA.zeros(2 * Cout + 32, dev) if train_bn else None       # + one barrier word for the fused (cooperative) BN kernel
         # un-pooled training BatchNorm with C/8 a power of two: statistics, finalize and normalise run as ONE cooperative kernel
         fuse_bn = USE_FUSED_BN and train_bn and not pool and _stream_ok(Cout)
-        if small:
+        if generic:
+            if train_bn and Cout % 2:
+                raise RuntimeError("native BatchNorm needs an even channel count")
+            igemm = direct = small = False
+            col = xn
+            y = torch.empty(M, Cout, dtype=BF16, device=dev)
+            L.check(lib.ewdml_conv_direct_fwd(_p(xn), _p(wb), _p(bias), _p(y), N, H, W, Cin, Cout, kh, kh, stride, pad, st),
+                    "conv_direct_fwd")
+            if train_bn:
+                L.check(lib.ewdml_colstats(_p(y), _p(sums), M, Cout, 1, st), "colstats")
+        elif small:
             igemm = direct = False
             col = xn
             y = torch.empty(M, Cout, dtype=BF16, device=dev)
@@ -274,8 +290,9 @@ class _ConvBlockFn(torch.autograd.Function):
                 col = torch.empty(M, Kp, dtype=BF16, device=dev)
                 L.check(lib.ewdml_im2col(_p(xn), _p(col), N, H, W, Cin, kh, kh, stride, pad, st), "im2col")
             m_rows, kb = M, (Kp + 63) // 64
-        if small:
+        if small or generic:
             m_rows, kb = M, 1
+        small = small or generic                   # from here on: "the output y and its statistics already exist"
         tiles = ((m_rows + 127) // 128) * ((Cout + 127) // 128)
         split = (not small) and tiles <= 96 and kb >= 16
         # few output tiles + long reduction: split-K into an fp32 accumulator, then one pass that adds the bias, rounds
@@ -337,7 +354,7 @@ class _ConvBlockFn(torch.autograd.Function):
             L.check(lib.ewdml_bn_act_fwd(_p(y), _p(stats), _p(resn), _p(out), N, HO, WO, Cout, int(relu), int(pool), st), "bn_act_fwd")
         ctx.save_for_backward(col, y, stats if stats is not None else torch.empty(0, device=dev),
                               resn if resn is not None else torch.empty(0, device=dev))
-        ctx.meta = (conv, bn, relu, pool, N, H, W, Cin, HO, WO, Cout, kh, stride, pad, M, K, Kp, direct, igemm, small)
+        ctx.meta = (conv, bn, relu, pool, N, H, W, Cin, HO, WO, Cout, kh, stride, pad, M, K, Kp, direct, igemm, small, generic)
         ctx.has_res = residual is not None
         return out.permute(0, 3, 1, 2)
 
@@ -346,7 +363,7 @@ class _ConvBlockFn(torch.autograd.Function):
         lib = _l()
         st = _stream()
         col, y, stats, resn = ctx.saved_tensors
-        conv, bn, relu, pool, N, H, W, Cin, HO, WO, Cout, kh, stride, pad, M, K, Kp, direct, igemm, small = ctx.meta
+        conv, bn, relu, pool, N, H, W, Cin, HO, WO, Cout, kh, stride, pad, M, K, Kp, direct, igemm, small, generic = ctx.meta
         dev = dout.device
         stats = stats if stats.numel() else None
         resn = resn if resn.numel() else None
@@ -379,7 +396,14 @@ class _ConvBlockFn(torch.autograd.Function):
                 conv.bias.grad = torch.zeros_like(conv.bias)
             _colsum_into(dy, conv.bias.grad)
         dx = None
-        if small:
+        if generic:
+            L.check(lib.ewdml_conv_direct_wgrad(_p(col), _p(dy), _p(gw), N, H, W, Cin, Cout, kh, kh, stride, pad, st), "conv_direct_wgrad")
+            if ctx.needs_input_grad[0]:
+                wb = _weight_bf16(conv.weight, Cout, K, pad=False)
+                dxn = torch.empty(N, H, W, Cin, dtype=BF16, device=dev)
+                L.check(lib.ewdml_conv_direct_dgrad(_p(dy), _p(wb), _p(dxn), N, H, W, Cin, Cout, kh, kh, stride, pad, st), "conv_direct_dgrad")
+                dx = dxn.permute(0, 3, 1, 2)
+        elif small:
             L.check(lib.ewdml_conv_small_wgrad(_p(col), int(col.dtype == torch.float32), _p(dy), _p(gw), N, H, W, Cin, Cout, kh, kh,
                                                stride, pad, st), "conv_small_wgrad")
         elif igemm:
@@ -450,7 +474,7 @@ class _LinearFn(torch.autograd.Function):
             xb = _empty2d(B, x.shape[1], x.device)
             xb.copy_(x)
             x = xb
-        wb = _weight_bf16(lin.weight, lin.out_features, lin.in_features)
+        wb = _weight_bf16(lin.weight, lin.out_features, lin.in_features)[:, :lin.in_features]   # in_features % 8 != 0: padded pitch, logical K
         y = _empty2d(B, lin.out_features, x.device, zero=True)
         gemm(x, wb, out=y, bias=lin.bias.detach() if lin.bias is not None else None)
         if relu:
@@ -594,13 +618,61 @@ def linear(x, weight, bias):
     raise RuntimeError("native linear is reached through linear_block(); see ewdml.ops.layers.Linear.forward")
 
 
+class _ReluFn(torch.autograd.Function):
+    """Stand-alone ReLU on the native elementwise kernels (nn.ReLU sites outside a fused conv / linear block)."""
+
+    @staticmethod
+    def forward(ctx, x):
+        xc = x.contiguous() if x.dtype == BF16 else x.to(BF16).contiguous()
+        y = torch.empty_like(xc)
+        L.check(_l().ewdml_relu_fwd(_p(xc), _p(y), xc.numel(), _stream()), "relu_fwd")
+        ctx.save_for_backward(y)
+        ctx.in_dtype = x.dtype
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        (y,) = ctx.saved_tensors
+        d = dy.to(BF16).contiguous()
+        dx = torch.empty_like(d)
+        L.check(_l().ewdml_relu_bwd(_p(d), _p(y), _p(dx), d.numel(), _stream()), "relu_bwd")
+        return dx.to(ctx.in_dtype)
+
+
+class _Pool2x2Fn(torch.autograd.Function):
+    """Stand-alone 2x2 / stride-2 max-pool (optionally followed by ReLU): the pooling half of the fused BatchNorm/activation
+    kernels with an identity affine (``stats = NULL``), forward and backward."""
+
+    @staticmethod
+    def forward(ctx, x, relu):
+        N, Cn, H, W = x.shape
+        xn = to_nhwc_bf16(x)
+        out = torch.empty(N, H // 2, W // 2, Cn, dtype=BF16, device=x.device)
+        L.check(_l().ewdml_bn_act_fwd(_p(xn), None, None, _p(out), N, H, W, Cn, int(relu), 1, _stream()), "pool_fwd")
+        ctx.save_for_backward(xn)
+        ctx.meta = (N, Cn, H, W, relu, x.dtype)
+        return out.permute(0, 3, 1, 2)
+
+    @staticmethod
+    def backward(ctx, dout):
+        (xn,) = ctx.saved_tensors
+        N, Cn, H, W, relu, in_dtype = ctx.meta
+        dn = to_nhwc_bf16(dout)
+        dx = torch.empty(N, H, W, Cn, dtype=BF16, device=dout.device)
+        sums = ARENA.zeros(2 * Cn + 32, dout.device)
+        L.check(_l().ewdml_bn_act_bwd(_p(xn), None, None, _p(dn), _p(sums), _p(dx), None, None, None, N, H, W, Cn, int(relu), 1, _stream()),
+                "pool_bwd")
+        return dx.permute(0, 3, 1, 2).to(in_dtype), None
+
+
 def relu(x):
-    xc = x if x.is_contiguous() else x.contiguous()
-    if xc.dtype != BF16:
-        return torch.relu(x)
-    return torch.relu(xc)      # stand-alone ReLU is rare on the native path (fused elsewhere)
+    """nn.ReLU as a stand-alone native op (bf16 out)."""
+    return _ReluFn.apply(x)
 
 
 def max_pool2x2(x, relu=False):
-    y = torch.nn.functional.max_pool2d(x, 2, 2)
-    return torch.relu(y) if relu else y
+    """nn.MaxPool2d(2, 2) [+ ReLU] as a stand-alone native op; odd spatial sizes fall back to torch (floor semantics)."""
+    if x.shape[2] % 2 or x.shape[3] % 2 or x.shape[1] % 2:
+        y = torch.nn.functional.max_pool2d(x, 2, 2)
+        return torch.relu(y) if relu else y
+    return _Pool2x2Fn.apply(x, relu)

@@ -40,6 +40,9 @@ def _round(t):
     (64, 64, 3, 1, 1, 4, True, True, True, False),         # implicit GEMM, BN=64 tiles, tiny spatial size
     (256, 512, 3, 1, 1, 2, True, True, True, False),       # implicit GEMM + split-K (few tiles, K = 2304)
     (512, 512, 3, 1, 1, 4, True, True, False, True),       # implicit GEMM + split-K + residual
+    (1, 20, 5, 1, 0, 28, False, True, True, False),        # LeNet conv1: direct small-channel kernels (C_out % 8 != 0)
+    (20, 50, 5, 1, 0, 12, False, True, True, False),       # LeNet conv2: direct kernels incl. dgrad
+    (6, 10, 3, 2, 1, 9, False, False, False, False),       # direct kernels, strided + padded, odd spatial size
 ])
 def test_conv_block_forward_backward(cin, cout, k, stride, pad, hw, bn, relu, pool, res):
     from ewdml.ops import native
@@ -83,8 +86,9 @@ def test_conv_block_forward_backward(cin, cout, k, stride, pad, hw, bn, relu, po
     out.backward(go.to(torch.bfloat16))
     torch.cuda.synchronize()
     _close(out, y, name="out")
-    _close(xn.grad, xr.grad, name="dx")
-    _close(conv.weight.grad, conv_r.weight.grad, name="dW")
+    # direct small-channel kernels behind relu + pool on a 4x4 / 8x8 map: a handful of near-tie mask flips weigh more
+    _close(xn.grad, xr.grad, tol=8e-2 if cout % 8 else 6e-2, name="dx")
+    _close(conv.weight.grad, conv_r.weight.grad, tol=8e-2 if cout % 8 else 6e-2, name="dW")
     if bn:
         _close(bnm.weight.grad, bn_r.weight.grad, name="dgamma")
         _close(bnm.bias.grad, bn_r.bias.grad, name="dbeta")
@@ -96,7 +100,8 @@ def test_conv_block_forward_backward(cin, cout, k, stride, pad, hw, bn, relu, po
         _close(rn.grad, rr.grad, name="dres")
 
 
-@pytest.mark.parametrize("B,fin,fout,relu", [(128, 512, 512, True), (128, 512, 10, False), (64, 800, 500, False), (37, 2048, 10, False)])
+@pytest.mark.parametrize("B,fin,fout,relu", [(128, 512, 512, True), (128, 512, 10, False), (64, 800, 500, False), (37, 2048, 10, False),
+                                             (64, 500, 10, False)])      # LeNet fc2: in_features not a multiple of 8
 def test_linear_block(B, fin, fout, relu):
     from ewdml.ops import native
     torch.manual_seed(1)
@@ -140,7 +145,8 @@ def test_cross_entropy_and_avgpool_and_dropout():
     assert torch.equal(d.grad != 0, y != 0)
 
 
-@pytest.mark.parametrize("name,shape", [("VGG11", (16, 3, 32, 32)), ("ResNet18", (8, 3, 32, 32)), ("ResNet50", (8, 3, 32, 32))])
+@pytest.mark.parametrize("name,shape", [("VGG11", (16, 3, 32, 32)), ("ResNet18", (8, 3, 32, 32)), ("ResNet50", (8, 3, 32, 32)),
+                                        ("LeNet", (16, 1, 28, 28))])
 def test_whole_model_native_matches_torch(name, shape):
     """Same weights, same batch: native loss close to fp32 torch, per-tensor gradient cosine > 0.98."""
     from ewdml.models import build_model
@@ -179,16 +185,23 @@ def test_whole_model_native_matches_torch(name, shape):
     finally:
         L.set_compute("torch")
     assert abs(loss.item() - loss_ref.item()) < 0.05 * max(1.0, abs(loss_ref.item()))
-    cos_nat, cos_amp = [], []
+    cos_nat, cos_amp, names = [], [], []
     for (n, p), pr, pa in zip(m_nat.named_parameters(), m_ref.parameters(), m_amp.parameters()):
         g, gr, ga = p.grad.float().flatten(), pr.grad.float().flatten(), pa.grad.float().flatten()
         if gr.norm() < 1e-5 or (n.endswith("bias") and p.dim() == 1 and "bn" not in n and "features" in n):
             continue                      # conv bias in front of BatchNorm: true gradient is 0
         cos_nat.append(F.cosine_similarity(g, gr, dim=0).item())
         cos_amp.append(F.cosine_similarity(ga, gr, dim=0).item())
+        names.append(n)
     mean_nat, mean_amp = sum(cos_nat) / len(cos_nat), sum(cos_amp) / len(cos_amp)
     assert mean_nat >= mean_amp - 0.03, (mean_nat, mean_amp)
     assert min(cos_nat) >= min(cos_amp) - 0.15, (min(cos_nat), min(cos_amp))
+    # per tensor (round 1 only bounded the worst tensor, loosely): wherever the library's own bf16 gradient is faithful to the
+    # fp32 one (cosine >= 0.9), the native gradient of the SAME tensor must be as faithful, give or take 0.05.  Tensors whose
+    # bf16 gradient is itself noise-dominated (50-layer net, batch 8: cosines of 0.1-0.4 for both arms) carry no signal to
+    # compare against and stay under the mean / min criteria above.
+    bad = [(n, round(cn, 4), round(ca, 4)) for n, cn, ca in zip(names, cos_nat, cos_amp) if ca >= 0.9 and cn < ca - 0.05]
+    assert not bad, bad
 
 
 @pytest.mark.parametrize("C,M,mean,std", [(64, 4096, 0.0, 1.0), (256, 1000, 1000.0, 2.0), (2048, 520, -300.0, 0.5), (8, 77, 5.0, 1.0)])
@@ -321,3 +334,24 @@ def test_bn_fused_cooperative_forward_backward(C, hw, res, relu, mean):
         _close(dbt, b_.grad, 2e-2, "dbeta")
         if res:
             _close(dres, rr.grad, 2e-2, "dres")
+
+
+def test_standalone_relu_and_maxpool_native():
+    """nn.ReLU / nn.MaxPool2d(2, 2) outside a fused block run the native elementwise / pooling kernels, forward and backward."""
+    from ewdml.ops import layers as Lyr
+    torch.manual_seed(4)
+    x = _round(torch.randn(4, 16, 8, 8, device=DEV)).contiguous(memory_format=torch.channels_last)
+    g = _round(torch.randn(4, 16, 4, 4, device=DEV))
+    Lyr.set_compute("native")
+    try:
+        xa = x.clone().requires_grad_(True)
+        ya = Lyr.MaxPool2d(2, 2)(Lyr.ReLU()(xa))
+        ya.backward(g)
+    finally:
+        Lyr.set_compute("torch")
+    xb = x.clone().requires_grad_(True)
+    yb = F.max_pool2d(F.relu(xb), 2, 2)
+    yb.backward(g)
+    assert ya.dtype == torch.bfloat16
+    _close(ya, yb, 1e-2, "pool(relu(x))")
+    _close(xa.grad, xb.grad, 2e-2, "dx")

@@ -359,3 +359,37 @@ def test_hvd_api_on_native_kernels(tmp_path):
         assert r["qsgd"]["bytes_sent"] > 0 and r["qsgd"]["bytes_sent"] < r["none"]["bytes_sent"]
     for name in ("none", "fp16", "qsgd", "topkqsgd", "qsgd_adasum"):   # replicas stay bit-identical under every compressor / op
         assert all(r[name]["weights"] == res[0][name]["weights"] for r in res), name
+
+
+def test_static_scratch_entry_on_two_devices():
+    """``ewdml_bn_stats_static`` keeps its scratch in a device array inside the library; that array exists once PER GPU and its
+    address has to be looked up with that GPU current.  One process, two devices, a second stream on the second device:
+    each result must match the caller-supplied-scratch path on its own device (a shared or stale address would not)."""
+    import ctypes as C
+    from ewdml.runtime import lib as L
+    lib = L.load()
+    vp, i32, i64, f32 = C.c_void_p, C.c_int, C.c_int64, C.c_float
+    lib.ewdml_bn_stats_static.restype = i32
+    lib.ewdml_bn_stats_static.argtypes = [vp, vp, vp, vp, vp, vp, i32, i64, f32, f32, vp]
+    lib.ewdml_colstats.restype = i32
+    lib.ewdml_colstats.argtypes = [vp, vp, i64, i32, i32, vp]
+    lib.ewdml_bn_finalize.restype = i32
+    lib.ewdml_bn_finalize.argtypes = [vp, vp, vp, vp, vp, vp, i32, i64, f32, f32, vp]
+    p = lambda t: C.c_void_p(t.data_ptr())
+    for rep in range(2):                                         # second round: both devices' arrays hold stale sums
+        for d in (0, 1):
+            dev = torch.device("cuda", d)
+            with torch.cuda.device(dev):
+                stream = torch.cuda.Stream(device=dev) if d == 1 else torch.cuda.current_stream(dev)
+                with torch.cuda.stream(stream):
+                    g = torch.Generator().manual_seed(50 + 2 * rep + d)
+                    M, Cn = 4000 + 100 * d, 128 * (d + 1)
+                    y = (torch.randn(M, Cn, generator=g) + d).to(dev).to(torch.bfloat16)
+                    gamma, beta = (torch.rand(Cn, generator=g) + 0.5).to(dev), torch.randn(Cn, generator=g).to(dev)
+                    st = C.c_void_p(stream.cuda_stream)
+                    sums, sa, sb = torch.zeros(2 * Cn, device=dev), torch.empty(4 * Cn, device=dev), torch.empty(4 * Cn, device=dev)
+                    L.check(lib.ewdml_colstats(p(y), p(sums), M, Cn, 1, st))
+                    L.check(lib.ewdml_bn_finalize(p(sums), p(gamma), p(beta), None, None, p(sa), Cn, M, 0.1, 1e-5, st))
+                    L.check(lib.ewdml_bn_stats_static(p(y), p(gamma), p(beta), None, None, p(sb), Cn, M, 0.1, 1e-5, st))
+                stream.synchronize()
+                assert torch.allclose(sb, sa, rtol=1e-4, atol=1e-5), (rep, d)
