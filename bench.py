@@ -207,12 +207,22 @@ def run_ewdml(a):
                "last_loss": last_loss}
     # exchange statistics (one extra step with stats collection, outside the timed regions)
     st = None
-    if role == "worker":
-        _, st = tr.step(x0, y0, want_stats=True)
-    else:
-        st = tr.server_step(want_stats=True)
+    for _ in range(3):          # three eager steps, the last one is reported: the first eager launch after graph replays pays one-off costs
+        if role == "worker":
+            _, st = tr.step(x0, y0, want_stats=True)
+        else:
+            st = tr.server_step(want_stats=True)
     barrier()
     clocks = sampler.stop() if sampler else None
+    # selection diagnostics of that last exchange: segments whose sampled band missed the k-th magnitude (exact-scan fallback)
+    sel = None
+    try:
+        plans = getattr(tr.exchange, "plans", None) or [getattr(tr.exchange, "push", None)]
+        infos = [i for p in plans if p is not None for i in p.seginfo()]
+        sel = {"segments": len(infos), "fallback_segments": sum(i["fallback"] for i in infos),
+               "tie_segments": sum(1 for i in infos if i["need_eq"]), "max_candidates": max((i["ncand"] for i in infos), default=0)}
+    except Exception:  # noqa: BLE001 -- diagnostics only
+        pass
     err = tr.check_device_error()
     value = a.batch_size * n_workers * a.steps / (ms / 1e3)
     out = {
@@ -231,7 +241,7 @@ def run_ewdml(a):
         "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "device_ms_total": ms, "wall_ms_total": wall_ms,
         "exchange": None if st is None else {"bytes_sent_per_step": st.bytes_sent, "bytes_recv_per_step": st.bytes_recv,
                                              "dense_bytes": tr.flat.dense_nbytes(),
-                                             "ms_send": st.t_send * 1e3, "ms_recv_apply": st.t_recv * 1e3},
+                                             "ms_send": st.t_send * 1e3, "ms_recv_apply": st.t_recv * 1e3, "selection": sel},
         "device_error": err,
     }
     if rank == 0:

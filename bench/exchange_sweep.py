@@ -125,10 +125,11 @@ def main():
                     out[:n].div_(world)
             t_lib = timeit(lib_path) if mb <= 256 or comp == "none" else None
             # each kernel chain against ITS OWN bytes: K1 reads the gradient twice (band pass + encode pass; once for the dense and
-            # QSGD-only codecs) and puts the payload on the wire once per peer (once in total with NVLS multicast); K2 reads the
-            # W payloads and writes the dense average
+            # QSGD-only codecs); on the wire an allgather delivers (W-1) payloads INTO every rank whatever the sender does --
+            # multicast only cuts the sender's egress from (W-1) payloads to one -- so the link bound is the ingress; K2 reads
+            # the W payloads and writes the dense average
             reads = 1 if comp in ("none", "qsgd") else 2
-            wire = payload if multicast else (world - 1) * payload
+            wire = (world - 1) * payload
             roof_k1 = max(reads * n * 4 / (hbm * 1e9), wire / (NVLINK_GBS * 1e9)) * 1e3
             roof_k2 = (world * payload + n * 4) / (hbm * 1e9) * 1e3
             t_roof = roof_k1 + roof_k2
