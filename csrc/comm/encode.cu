@@ -362,7 +362,7 @@ static int send_impl(ewdml_plan* p, const float* grad, const ewdml_dests* dests,
     do {                                                                                                              \
         EWDML_CUDA(cudaFuncSetAttribute(k_encode_push<MODE_, SEL_, VAL_>, cudaFuncAttributeMaxDynamicSharedMemorySize,  \
                                         160 * 1024));                                                                 \
-        k_encode_push<MODE_, SEL_, VAL_><<<p->ntiles < 2 * 148 ? p->ntiles : 2 * 148, 256, smem, st>>>(a);                                            \
+        k_encode_push<MODE_, SEL_, VAL_><<<p->ntiles < 2 * ewdml_sm_count() ? p->ntiles : 2 * ewdml_sm_count(), 256, smem, st>>>(a);                                            \
     } while (0)
     const int sel = p->codec.sel, val = p->codec.val;
     if (p->codec.mode == EWDML_MODE_DENSE) {

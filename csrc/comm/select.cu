@@ -358,7 +358,7 @@ int ewdml_launch_select(ewdml_plan* p, const float* grad, cudaStream_t st) {
         EWDML_LAUNCH_CHECK();
         k_bounds<<<p->nseg, 256, 0, st>>>(p->d_seg, p->d_hist, p->d_seginfo);
         EWDML_LAUNCH_CHECK();
-        k_band<<<p->ntiles < 2 * 148 ? p->ntiles : 2 * 148, 256, 0, st>>>(grad, p->d_tile, p->d_seginfo, p->d_cand, p->d_seg,
+        k_band<<<p->ntiles < 2 * ewdml_sm_count() ? p->ntiles : 2 * ewdml_sm_count(), 256, 0, st>>>(grad, p->d_tile, p->d_seginfo, p->d_cand, p->d_seg,
                                                                       p->d_tile_sumsq, p->ntiles);
         EWDML_LAUNCH_CHECK();
         k_refine<<<p->nseg, 1024, 0, st>>>(grad, p->d_seg, p->d_seginfo, p->d_cand, p->d_tile_sumsq, want_norm,

@@ -16,6 +16,7 @@ void ewdml_set_error(const char* fmt, ...);
 void ewdml_count_launch(int n = 1);
 extern "C" uint32_t* ewdml_device_error_word();      // device pointer, lazily allocated per device
 extern "C" uint64_t ewdml_spin_limit();
+extern "C" int ewdml_sm_count();                     // SMs of the current device (cached per device)
 
 #define EWDML_CUDA(expr)                                                                   \
     do {                                                                                   \

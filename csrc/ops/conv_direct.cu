@@ -110,7 +110,7 @@ DGeom make(int N, int H, int W, int Cin, int Cout, int KH, int KW, int stride, i
 
 int grid_of(int64_t items) {
     int64_t b = (items + 255) / 256;
-    return (int)(b < 1 ? 1 : (b > 148 * 16 ? 148 * 16 : b));
+    return (int)(b < 1 ? 1 : (b > (int64_t)ewdml_sm_count() * 16 ? (int64_t)ewdml_sm_count() * 16 : b));
 }
 
 #define DC_LAUNCH_CHECK()                                                                                                    \

@@ -693,7 +693,7 @@ int gemm_dispatch(const void* A, const void* B, void* C, int M, int N, int K, in
     if (split <= 0) {
         split = 1;
         if (out_mode == 2) {                       // only the accumulate mode may be split
-            int target = 2 * 148;
+            int target = 2 * ewdml_sm_count();
             while (tiles * split * 2 <= target && split * 2 <= g.kb_total / 2) split *= 2;
         }
     }

@@ -1315,7 +1315,7 @@ int stream_grid(int64_t V, int min_per_thread, int cap_per_sm);
 
 int grid_for(int64_t work_items, int per_cta = 256) {
     int64_t g = (work_items + per_cta - 1) / per_cta;
-    const int64_t cap = 148 * 16;
+    const int64_t cap = (int64_t)ewdml_sm_count() * 16;
     return (int)(g < 1 ? 1 : (g > cap ? cap : g));
 }
 
@@ -1399,7 +1399,7 @@ extern "C" int ewdml_colstats(const void* y, float* sums, int64_t M, int C, int 
     if (C % 8 == 0) {
         const int c8n = C / 8, lanes = c8n < 256 ? c8n : 256, rows_par = 256 / lanes;
         const int gx = (c8n + lanes - 1) / lanes;
-        int gy = (int)((4 * 148 + gx - 1) / gx);
+        int gy = (int)((4 * ewdml_sm_count() + gx - 1) / gx);
         int64_t rows_per = (M + gy - 1) / gy;
         if (rows_per < 8 * rows_par) rows_per = 8 * rows_par;
         gy = (int)((M + rows_per - 1) / rows_per);
@@ -1409,7 +1409,7 @@ extern "C" int ewdml_colstats(const void* y, float* sums, int64_t M, int C, int 
     }
     const int cp = C / 2, lanes = cp < 256 ? cp : 256;
     const int gx = (cp + lanes - 1) / lanes;
-    int gy = (int)((2 * 148 + gx - 1) / gx);
+    int gy = (int)((2 * ewdml_sm_count() + gx - 1) / gx);
     int64_t rows_per = (M + gy - 1) / gy;
     const int rows_par = 256 / lanes;
     if (rows_per < 4 * rows_par) rows_per = 4 * rows_par;
@@ -1586,7 +1586,7 @@ extern "C" int ewdml_bn_act_bwd(const void* y, const float* stats, const void* r
         if (stats) {
             const int c8n = C / 8, lanes = c8n < 256 ? c8n : 256, par = 256 / lanes;
             const int gx = (c8n + lanes - 1) / lanes;
-            int gy = (int)((4 * 148 + gx - 1) / gx);
+            int gy = (int)((4 * ewdml_sm_count() + gx - 1) / gx);
             int64_t per = (units + gy - 1) / gy;
             if (per < 4 * par) per = 4 * par;
             gy = (int)((units + per - 1) / per);
@@ -1611,7 +1611,7 @@ extern "C" int ewdml_bn_act_bwd(const void* y, const float* stats, const void* r
     if (stats) {
         const int lanes = C < 256 ? C : 256;
         const int gx = (C + lanes - 1) / lanes;
-        int gy = (int)((2 * 148 + gx - 1) / gx);
+        int gy = (int)((2 * ewdml_sm_count() + gx - 1) / gx);
         int64_t rows_per = (M + gy - 1) / gy;
         const int rows_par = 256 / lanes;
         if (rows_per < 4 * rows_par) rows_per = 4 * rows_par;
@@ -1637,7 +1637,7 @@ extern "C" int ewdml_f32_to_bf16_stats(const float* src, const float* bias, void
     EWDML_CHECK_ARG(src && dst && M > 0 && C > 0 && C % 8 == 0);
     const int c8n = C / 8, lanes = c8n < 256 ? c8n : 256, rows_par = 256 / lanes;
     const int gx = (c8n + lanes - 1) / lanes;
-    int gy = (int)((4 * 148 + gx - 1) / gx);
+    int gy = (int)((4 * ewdml_sm_count() + gx - 1) / gx);
     int64_t rows_per = (M + gy - 1) / gy;
     if (rows_per < 4 * rows_par) rows_per = 4 * rows_par;
     gy = (int)((M + rows_per - 1) / rows_per);
@@ -1668,7 +1668,7 @@ extern "C" int ewdml_conv_small_wgrad(const void* x, int x_is_f32, const void* d
     const int64_t M = (int64_t)N * g.HO * g.WO;
     EWDML_CHECK_ARG((g.K + 256 / Cout - 1) / (256 / Cout) <= 20);
     const int64_t nb = (M + 63) / 64;
-    const int grid = (int)(nb < 2 * 148 ? nb : 2 * 148);
+    const int grid = (int)(nb < 2 * ewdml_sm_count() ? nb : 2 * ewdml_sm_count());
     cudaStream_t st = (cudaStream_t)stream;
     if (x_is_f32) k_conv_small_wgrad<float><<<grid, 256, 0, st>>>((const float*)x, (const __nv_bfloat16*)dy, dw, g, Cout, M);
     else k_conv_small_wgrad<__nv_bfloat16><<<grid, 256, 0, st>>>((const __nv_bfloat16*)x, (const __nv_bfloat16*)dy, dw, g, Cout, M);

@@ -70,6 +70,19 @@ extern "C" int ewdml_set_spin_limit(uint64_t iters) {
     return 0;
 }
 
+// SM count of the current device, queried once per device (launch geometry of every persistent / grid-stride kernel).
+extern "C" int ewdml_sm_count() {
+    static std::atomic<int> cache[64];
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
+    int v = cache[dev].load(std::memory_order_relaxed);
+    if (v <= 0) {
+        if (cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || v <= 0) v = 148;
+        cache[dev].store(v, std::memory_order_relaxed);
+    }
+    return v;
+}
+
 // One error word per device, allocated on first use and never freed (process lifetime).
 static std::mutex g_err_mu;
 static uint32_t* g_err_word[64] = {nullptr};

@@ -6,7 +6,7 @@ system-scope flag traffic -> ST/LD/ATOM *.STRONG.SYS, MEMBAR.*.SYS) and register
 import collections, os, re, subprocess
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 SO = os.path.join(ROOT, "ewdml", "_C", "libewdml.so")
-KEEP = re.compile(r"\b(UTC[A-Z]*MMA\S*|LDTM\S*|STTM\S*|UTMALDG\S*|UTMASTG\S*|UBLKCP\S*|UTCBAR\S*|UTCATOMSWS\S*|SYNCS\.\S+|REDG\.\S+|"
+KEEP = re.compile(r"\b(LDGMC\S*|UTC[A-Z]*MMA\S*|LDTM\S*|STTM\S*|UTMALDG\S*|UTMASTG\S*|UBLKCP\S*|UTCBAR\S*|UTCATOMSWS\S*|SYNCS\.\S+|REDG\.\S+|"
                   r"(?:ST|STG|LD|LDG|ATOMG?|RED)\.\S*STRONG\.SYS\S*|MEMBAR\.\S+|ATOMG\.\S+|ATOMS\.\S+|VOTEU?\.\S+|HMMA\S*|MUFU\.EX2)")
 
 
@@ -31,7 +31,9 @@ def main():
     with open(os.path.join(ROOT, "profiles", "sass_evidence.txt"), "w") as f:
         f.write("# SASS evidence (cuobjdump -sass ewdml/_C/libewdml.so, sm_100a) -- mnemonic counts per kernel; scripts/sass_evidence.py\n\n"
                 "tcgen05.mma -> UTC*MMA, tcgen05.ld -> LDTM, TMA load -> UTMALDG, tcgen05.commit -> UTCBAR, mbarrier -> SYNCS.*,\n"
-                "red.global.add.v4.f32 -> REDG.E.ADD.F32x4, system-scope flag ops -> *.STRONG.SYS / MEMBAR.*.SYS\n\n")
+                "red.global.add.v4.f32 -> REDG.E.ADD.F32x4, system-scope flag ops -> *.STRONG.SYS / MEMBAR.*.SYS,\n"
+                "multimem.ld_reduce (NVLS in-switch reduction) -> LDGMC.E.ADD.F32x4; multimem.st is a plain STG to a multicast address\n"
+                "(the PTX forms are listed in profiles/ptx_multimem.txt)\n\n")
         for name, c in sorted(zip(names, per.values()), key=lambda t: t[0]):
             if c:
                 f.write(f"{name:58s} " + ", ".join(f"{k} x{v}" for k, v in sorted(c.items())) + "\n")

@@ -41,7 +41,9 @@ def test_keras_style_trainer_with_callbacks(tmp_path):
     """tensorflow_mnist.py's capability: Adam + DistributedOptimizer, broadcast / metric-average / LR warm-up callbacks,
     rank-0 checkpoint per epoch."""
     ck = str(tmp_path / "checkpoint-{epoch}.pt")
-    cmd = [sys.executable, "-m", "ewdml.cli.launch", "-np", "2", "--master-port", "29743", "--",
+    import socket
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()     # a port that is free right now
+    cmd = [sys.executable, "-m", "ewdml.cli.launch", "-np", "2", "--master-port", str(port), "--",
            sys.executable, "-m", "ewdml.cli.allreduce_mnist_keras", "--epochs", "2", "--steps-per-epoch", "6", "--no-cuda",
            "--synthetic-size", "256", "--batch-size", "16", "--warmup-epochs", "1", "--checkpoint-format", ck]
     out = subprocess.run(cmd, capture_output=True, text=True, timeout=300, cwd=ROOT)
