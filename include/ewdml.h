@@ -216,6 +216,33 @@ int ewdml_heap_export(void* base, uint8_t handle[64]);           /* cudaIpcMemHa
 int ewdml_heap_import(const uint8_t handle[64], void** mapped);  /* enables peer access lazily  */
 int ewdml_heap_unmap(void* mapped);
 int ewdml_can_access_peer(int dev, int peer, int* out);
+int ewdml_sm_count(void);                                        /* SMs of the current device, cached per device */
+
+/* Second heap transport: CUDA virtual-memory-management allocations + NVLS multicast objects (what replaces the smcuda BTL's
+ * IPC handshake, ompi:opal/mca/btl/smcuda/btl_smcuda.c:1081, and common/cuda's handle get / open,
+ * ompi:opal/mca/common/cuda/common_cuda.c:1006-1152, when stores must be replicated by the NVSwitch).  Driver entry points are
+ * resolved at run time (no libcuda link dependency).  Sequence per symmetric buffer: every rank ewdml_vmm_alloc -> send the fd to
+ * every peer (ewdml_fdx_send) -> ewdml_vmm_import each received fd; rank 0 ewdml_mc_create -> fd to all; the others
+ * ewdml_mc_import; all ewdml_mc_add_device; HOST BARRIER; all ewdml_mc_bind_map.  A store to mc_base + x is replicated into
+ * offset x of every rank's allocation (multimem.st); multimem.ld_reduce from it returns the in-switch sum of all copies.        */
+typedef struct ewdml_vmm_buf ewdml_vmm_buf;
+typedef struct ewdml_fdx ewdml_fdx;
+int ewdml_vmm_query(int out[3]);                                 /* {VMM usable, multicast usable, POSIX-fd handles usable} */
+int ewdml_vmm_granularity(int ndev, size_t* out);                /* allocation size quantum (ndev > 1: also the multicast one) */
+int ewdml_vmm_alloc(ewdml_vmm_buf** out, size_t bytes, void** base, int* fd);      /* zero-filled; bytes % granularity == 0 */
+int ewdml_vmm_import(ewdml_vmm_buf** out, int fd, size_t bytes, void** mapped);    /* a peer's allocation, mapped read/write */
+int ewdml_vmm_close_fd(int fd);
+int ewdml_vmm_free(ewdml_vmm_buf* buf);                          /* unmap + release (own, imported or multicast object)   */
+int ewdml_mc_create(ewdml_vmm_buf** out, int ndev, size_t bytes, int* fd);         /* root only                               */
+int ewdml_mc_import(ewdml_vmm_buf** out, int fd, size_t bytes);
+int ewdml_mc_add_device(ewdml_vmm_buf* mc);                      /* current device; every rank, before any bind            */
+int ewdml_mc_bind_map(ewdml_vmm_buf* mc, ewdml_vmm_buf* mem, void** mc_base);
+/* file-descriptor channel between the ranks of one node (abstract UNIX datagram sockets, SCM_RIGHTS, tagged, with a stash for
+ * messages that arrive early; sends never block without draining the own queue)                                              */
+int ewdml_fdx_open(ewdml_fdx** out, const char* job, int rank, int world);
+int ewdml_fdx_send(ewdml_fdx* x, int dst, int fd, uint64_t tag, double timeout_s);
+int ewdml_fdx_recv(ewdml_fdx* x, uint64_t tag, int src, int* fd, int* src_out, double timeout_s);
+int ewdml_fdx_close(ewdml_fdx* x);
 /* Deterministic offset allocator inside one peer-mapped region (OSHMEM memheap analogue): the same alloc/free sequence
  * gives the same offsets on every rank, so symmetric objects need no rendezvous after the region was exchanged.      */
 typedef struct ewdml_symheap ewdml_symheap;
@@ -285,6 +312,14 @@ int ewdml_conv_small_fwd(const void* x, int x_is_f32, const void* w, const float
                          int Cin, int Cout, int KH, int KW, int stride, int pad, void* stream);
 int ewdml_conv_small_wgrad(const void* x, int x_is_f32, const void* dy, float* dw, int N, int H, int W, int Cin,
                            int Cout, int KH, int KW, int stride, int pad, void* stream);
+/* direct small-channel convolutions (C_out % 8 != 0: LeNet's 1 -> 20 -> 50 channel 5x5 layers, lenet.py:18-19): NHWC bf16
+ * activations, [C_out][KH][KW][C_in] bf16 weights, fp32 accumulation; wgrad ACCUMULATES into the fp32 gradient            */
+int ewdml_conv_direct_fwd(const void* x, const void* w, const float* bias, void* y, int N, int H, int W, int Cin, int Cout,
+                          int KH, int KW, int stride, int pad, void* stream);
+int ewdml_conv_direct_dgrad(const void* dy, const void* w, void* dx, int N, int H, int W, int Cin, int Cout, int KH, int KW,
+                            int stride, int pad, void* stream);
+int ewdml_conv_direct_wgrad(const void* x, const void* dy, float* dw, int N, int H, int W, int Cin, int Cout, int KH, int KW,
+                            int stride, int pad, void* stream);
 int ewdml_pad_nhwc(const void* x, void* out, int N, int H, int W, int C, void* stream);
 int ewdml_col2im(const void* dcol, void* dx, int N, int H, int W, int C, int KH, int KW, int stride, int pad, void* stream);
 
