@@ -73,6 +73,7 @@ struct Server {
     std::map<std::string, std::string> kv;
     std::map<std::string, int64_t> counters;
     std::atomic<bool> stop{false};
+    std::atomic<int> active{0};        // connections being served (the hosting rank's own included)
     std::vector<int> fds;
 
     void serve(int fd) {
@@ -104,6 +105,7 @@ struct Server {
             }
         }
         ::close(fd);
+        active.fetch_sub(1);
     }
 
     void accept_loop() {
@@ -116,6 +118,7 @@ struct Server {
             setsockopt(fd, IPPROTO_TCP, TCP_NODELAY, &one, sizeof(one));
             std::lock_guard<std::mutex> lk(mu);
             fds.push_back(fd);
+            active.fetch_add(1);
             workers.emplace_back([this, fd] { serve(fd); });
         }
     }
@@ -255,6 +258,12 @@ extern "C" int ewdml_store_destroy(ewdml_store* s) {
     if (s->fd >= 0) { ::shutdown(s->fd, SHUT_RDWR); ::close(s->fd); }
     if (s->server) {
         Server* sv = s->server;
+        // The hosting rank usually leaves a final barrier first (its reply travels over loopback) and closes right away.
+        // Stopping the server then would cut the replies still owed to the other ranks ("connection lost" in THEIR barrier,
+        // seen once in a 4-GPU test run), so the server lingers until every client has disconnected -- or 20 s, for clients
+        // that died without closing.
+        for (int waited_ms = 0; sv->active.load() > 0 && waited_ms < 20000; waited_ms += 5)
+            std::this_thread::sleep_for(std::chrono::milliseconds(5));
         sv->stop.store(true);
         sv->cv.notify_all();
         { std::lock_guard<std::mutex> lk(sv->mu); for (int fd : sv->fds) ::shutdown(fd, SHUT_RDWR); }
