@@ -219,7 +219,11 @@ def run_ewdml(a):
     try:
         plans = getattr(tr.exchange, "plans", None) or [getattr(tr.exchange, "push", None)]
         infos = [i for p in plans if p is not None for i in p.seginfo()]
+        fb = torch.tensor([float(sum(p.fallbacks() for p in plans if p is not None))], dtype=torch.float64, device=device)
+        if world > 1:
+            dist.all_reduce(fb)
         sel = {"segments": len(infos), "fallback_segments": sum(i["fallback"] for i in infos),
+               "fallbacks_all_ranks_whole_run": int(fb.item()), "exchanges_whole_run": tr.step_idx,
                "tie_segments": sum(1 for i in infos if i["need_eq"]), "max_candidates": max((i["ncand"] for i in infos), default=0)}
     except Exception:  # noqa: BLE001 -- diagnostics only
         pass

@@ -150,6 +150,16 @@ extern "C" int ewdml_plan_slot_layout(const ewdml_plan* p, int64_t out[4]) {
     return 0;
 }
 
+// Segments whose sampled band missed the k-th magnitude (exact-scan fallback in k_refine) since the plan was created; syncs.
+extern "C" int ewdml_plan_fallbacks(ewdml_plan* p, int64_t* out, void* stream) {
+    EWDML_CHECK_ARG(p && out);
+    uint32_t h = 0;
+    EWDML_CUDA(cudaMemcpyAsync(&h, p->d_stats + 4, sizeof(h), cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+    EWDML_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
+    *out = h;
+    return 0;
+}
+
 extern "C" int ewdml_plan_read_stats(ewdml_plan* p, int64_t out[4], void* stream) {
     EWDML_CHECK_ARG(p && out);
     uint32_t h[8];

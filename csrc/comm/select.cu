@@ -14,6 +14,8 @@
 //
 // Full read #2 is the encode kernel (encode.cu).  Keys are the fp32 bit patterns with the sign
 // cleared, so integer order == magnitude order.
+#include <stdlib.h>
+
 #include "plan.h"
 
 #define KEY(v) (__float_as_uint(v) & 0x7FFFFFFFu)
@@ -52,7 +54,7 @@ __global__ void __launch_bounds__(256) k_sample_hist(const float* __restrict__ g
 }
 
 __global__ void __launch_bounds__(256) k_bounds(const SegDesc* __restrict__ segs, uint32_t* __restrict__ hist,
-                                                SegInfo* __restrict__ info) {
+                                                SegInfo* __restrict__ info, double sigmas) {
     __shared__ uint32_t scan_smem[40];
     __shared__ int s_hi, s_lo;
     const SegDesc sg = segs[blockIdx.x];
@@ -75,7 +77,7 @@ __global__ void __launch_bounds__(256) k_bounds(const SegDesc* __restrict__ segs
         r_lo = r_hi = (long long)sg.k;
     } else {
         double var = rs * (1.0 - frac);
-        double delta = 6.0 * sqrt(var > 1.0 ? var : 1.0) + 2.0;
+        double delta = sigmas * sqrt(var > 1.0 ? var : 1.0) + 2.0;
         r_lo = (long long)floor(rs - delta);
         r_hi = (long long)ceil(rs + delta);
     }
@@ -251,7 +253,8 @@ __device__ void exact_select(const uint32_t* keys, const float* raw, uint32_t n,
 
 __global__ void __launch_bounds__(1024) k_refine(const float* __restrict__ grad, const SegDesc* __restrict__ segs,
                                                  SegInfo* __restrict__ info, const uint32_t* __restrict__ cand,
-                                                 const double* __restrict__ tile_sumsq, int want_norm, float levels) {
+                                                 const double* __restrict__ tile_sumsq, int want_norm, float levels,
+                                                 uint32_t* __restrict__ fallback_total) {
     __shared__ uint32_t h[EWDML_HIST_BINS];
     __shared__ uint32_t scan_smem[40];
     __shared__ double red_smem[32];
@@ -302,6 +305,7 @@ __global__ void __launch_bounds__(1024) k_refine(const float* __restrict__ grad,
         si.need_eq = need_eq;
         si.eq_taken = 0;
         si.fallback = fallback ? 1u : 0u;
+        if (fallback) atomicAdd(fallback_total, 1u);          // running count since plan creation (ewdml_plan_fallbacks)
         float norm = (float)sqrt(sumsq);
         bool ok = want_norm && norm > 0.f && isfinite(norm);
         si.norm = want_norm ? norm : 0.f;
@@ -348,6 +352,21 @@ __global__ void __launch_bounds__(256) k_norm_finish(const SegDesc* __restrict__
     }
 }
 
+// Width of the sampled band in standard deviations of the sampled rank (EWDML_BAND_SIGMA, default 16).  The estimate assumes
+// an independent sample; the strided sample of a weight tensor is not quite one (per-channel scales), so a wider band trades a
+// few more candidates for fewer exact-scan fallbacks, which one CTA pays with three passes over the whole tensor.  Measured on
+// ResNet-50 (1 GPU, 209 exchanges x 161 tensors): 6 sigma = 65 fallbacks and 8.18 ms per step, 12 sigma = 0 and 7.57 ms, 24 sigma = 0
+// and 7.62 ms; with W ranks any rank's fallback delays every rank, which was the multi-GPU gap to the dense path.
+static double band_sigmas() {
+    static double v = 0.0;
+    if (v == 0.0) {
+        const char* e = getenv("EWDML_BAND_SIGMA");
+        v = e ? atof(e) : 16.0;
+        if (!(v >= 1.0 && v <= 1000.0)) v = 16.0;
+    }
+    return v;
+}
+
 // Host: enqueue the selection chain for a plan.
 int ewdml_launch_select(ewdml_plan* p, const float* grad, cudaStream_t st) {
     const ewdml_codec& c = p->codec;
@@ -356,13 +375,13 @@ int ewdml_launch_select(ewdml_plan* p, const float* grad, cudaStream_t st) {
     if (c.sel == EWDML_SEL_TOPK) {
         k_sample_hist<<<p->nsample, 256, 0, st>>>(grad, p->d_seg, p->d_sample, p->d_hist);
         EWDML_LAUNCH_CHECK();
-        k_bounds<<<p->nseg, 256, 0, st>>>(p->d_seg, p->d_hist, p->d_seginfo);
+        k_bounds<<<p->nseg, 256, 0, st>>>(p->d_seg, p->d_hist, p->d_seginfo, band_sigmas());
         EWDML_LAUNCH_CHECK();
         k_band<<<p->ntiles < 2 * ewdml_sm_count() ? p->ntiles : 2 * ewdml_sm_count(), 256, 0, st>>>(grad, p->d_tile, p->d_seginfo, p->d_cand, p->d_seg,
                                                                       p->d_tile_sumsq, p->ntiles);
         EWDML_LAUNCH_CHECK();
         k_refine<<<p->nseg, 1024, 0, st>>>(grad, p->d_seg, p->d_seginfo, p->d_cand, p->d_tile_sumsq, want_norm,
-                                           (float)c.levels);
+                                           (float)c.levels, p->d_stats + 4);
         EWDML_LAUNCH_CHECK();
     } else if (want_norm) {
         k_sumsq<<<p->ntiles, 256, 0, st>>>(grad, p->d_tile, p->d_tile_sumsq);

@@ -139,6 +139,12 @@ class ExchangePlan:
         L.check(self.lib.ewdml_plan_read_stats(self._h, out, self._stream()), "read_stats")
         return {"entries": out[0], "data_bytes": out[1], "payload_bytes": out[2], "error": out[3]}
 
+    def fallbacks(self) -> int:
+        """Segments that took the exact-scan fallback of the top-k selection since this plan was created."""
+        out = C.c_int64(0)
+        L.check(self.lib.ewdml_plan_fallbacks(self._h, C.byref(out), self._stream()), "plan_fallbacks")
+        return int(out.value)
+
     def seginfo(self):
         out = (C.c_uint32 * (4 * self.nseg))()
         L.check(self.lib.ewdml_plan_read_seginfo(self._h, out, self._stream()), "read_seginfo")

@@ -93,6 +93,7 @@ def load() -> C.CDLL:
         "ewdml_allreduce_state": (i32, [P(Comm), i64, f32, i32, u32, vp, vp, vp]),
         "ewdml_plan_read_stats": (i32, [vp, P(i64), vp]),
         "ewdml_plan_read_seginfo": (i32, [vp, P(u32), vp]),
+        "ewdml_plan_fallbacks": (i32, [vp, P(i64), vp]),
         "ewdml_allreduce": (i32, [P(Comm), i64, f32, i32, u32, vp, vp]),
         "ewdml_barrier": (i32, [P(Comm), u32, vp]),
         "ewdml_adasum_pair": (i32, [vp, vp, vp, i32, vp, vp, i64, vp, vp]),

@@ -112,6 +112,8 @@ int ewdml_plan_read_stats(ewdml_plan* plan, int64_t out[4], void* stream);
 /* Debug/test access to the per-segment selection results of the last send:
  * out[4*i+0]=threshold key, +1=ties taken, +2=norm bits, +3=candidate count                     */
 int ewdml_plan_read_seginfo(ewdml_plan* plan, uint32_t* out, void* stream);
+/* running count of segments that needed the exact-scan fallback of the top-k selection (sampled band missed); syncs */
+int ewdml_plan_fallbacks(ewdml_plan* plan, int64_t* out, void* stream);
 
 /* Graph-replayable forms.  `state` is a device array of 4 uint32 {seq, step, first, applies} advanced by
  * ewdml_state_advance (one tiny launch at the start of every optimizer application; bump_seq = 1 for
