@@ -352,7 +352,7 @@ __global__ void __launch_bounds__(256) k_norm_finish(const SegDesc* __restrict__
     }
 }
 
-// Width of the sampled band in standard deviations of the sampled rank (EWDML_BAND_SIGMA, default 16).  The estimate assumes
+// Width of the sampled band in standard deviations of the sampled rank (EWDML_BAND_SIGMA, default 12).  The estimate assumes
 // an independent sample; the strided sample of a weight tensor is not quite one (per-channel scales), so a wider band trades a
 // few more candidates for fewer exact-scan fallbacks, which one CTA pays with three passes over the whole tensor.  Measured on
 // ResNet-50 (1 GPU, 209 exchanges x 161 tensors): 6 sigma = 65 fallbacks and 8.18 ms per step, 12 sigma = 0 and 7.57 ms, 24 sigma = 0
@@ -361,8 +361,8 @@ static double band_sigmas() {
     static double v = 0.0;
     if (v == 0.0) {
         const char* e = getenv("EWDML_BAND_SIGMA");
-        v = e ? atof(e) : 16.0;
-        if (!(v >= 1.0 && v <= 1000.0)) v = 16.0;
+        v = e ? atof(e) : 12.0;
+        if (!(v >= 1.0 && v <= 1000.0)) v = 12.0;
     }
     return v;
 }
