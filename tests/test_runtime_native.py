@@ -98,3 +98,85 @@ def test_collective_engine_environment_override():
     assert run({"EWDML_COLL_ALLREDUCE_ALGO": "twoshot"}) == ["2", "2"]
     assert run({"EWDML_COLL_ONESHOT_MAX_BYTES": "32"}) == ["2", "2"]
     assert run({"EWDML_COLL_ONESHOT_MAX_BYTES": str(1 << 31)}) == ["1", "1"]
+
+
+def _fdx_proc(rank, world, job, out_dir):
+    """Every rank sends a pipe's write end to every other rank, tagged; receives in the OPPOSITE order it was sent in (the
+    stash has to hold the early ones); then writes its rank through every descriptor it received."""
+    import ctypes as C
+    from ewdml.runtime import lib as L
+    lib = L.load()
+    h = C.c_void_p()
+    L.check(lib.ewdml_fdx_open(C.byref(h), job.encode(), rank, world), "fdx_open")
+    time.sleep(0.2 * rank)                                   # staggered start: senders meet receivers that are not bound yet
+    r_end, w_end = os.pipe()
+    for dst in range(world):
+        if dst != rank:
+            for tag in (7, 8):
+                L.check(lib.ewdml_fdx_send(h, dst, w_end, (tag << 8) | 0, 30.0), "fdx_send")
+    got = {}
+    for tag in (8, 7):                                       # opposite order
+        for src in reversed(range(world)):
+            if src != rank:
+                fd, who = C.c_int(-1), C.c_int(-1)
+                L.check(lib.ewdml_fdx_recv(h, (tag << 8) | 0, src, C.byref(fd), C.byref(who), 30.0), "fdx_recv")
+                assert who.value == src and fd.value >= 0
+                got[(tag, src)] = fd.value
+    for (tag, src), fd in got.items():
+        os.write(fd, bytes([rank, tag]))                     # lands in rank `src`'s pipe: the descriptor really is its pipe
+        os.close(fd)
+    os.close(w_end)
+    data = b""
+    while len(data) < 2 * 2 * (world - 1):
+        data += os.read(r_end, 64)
+    pairs = sorted((data[i], data[i + 1]) for i in range(0, len(data), 2))
+    json.dump({"pairs": pairs}, open(os.path.join(out_dir, f"fdx{rank}.json"), "w"))
+    # a receive that nobody answers times out instead of hanging
+    fd = C.c_int(-1)
+    rc = lib.ewdml_fdx_recv(h, 999, -1, C.byref(fd), None, 0.3)
+    assert rc == -3, rc                                      # EWDML_ERR_TIMEOUT
+    lib.ewdml_fdx_close(h)
+
+
+def test_fd_channel_passes_descriptors_between_processes(tmp_path):
+    """csrc/runtime/vmm.cu's descriptor channel (what carries the cuMemCreate / multicast-object handles between the ranks of a
+    node): SCM_RIGHTS over abstract UNIX datagram sockets, tag + source matching, out-of-order receives, time-outs.  No GPU."""
+    import uuid
+    world = 3
+    mp.spawn(_fdx_proc, args=(world, uuid.uuid4().hex[:12], str(tmp_path)), nprocs=world, join=True)
+    for r in range(world):
+        res = json.load(open(tmp_path / f"fdx{r}.json"))
+        others = [o for o in range(world) if o != r]
+        assert res["pairs"] == sorted([o, t] for o in others for t in (7, 8))
+
+
+def _store_edge(rank, world, port, out_dir):
+    os.environ["EWDML_STORE_TIMEOUT_S"] = "1.5"
+    from ewdml.runtime import lib as L
+    st = L.Store("127.0.0.1", port, rank, world, timeout_s=30.0)
+    res = {}
+    if rank == 0:
+        st.set("large", os.urandom(3 << 20))                 # larger than the default first-guess buffer of get()
+    res["large"] = len(st.get("large"))
+    st.barrier("a")
+    if rank == 1:
+        t0 = time.time()
+        try:
+            st.get("never-set")                              # nobody sets it: the deadline turns the wait into an error
+            res["timeout"] = "returned"
+        except L.NativeError as e:
+            res["timeout"] = "timed out" if "timed out" in str(e) else str(e)
+        res["waited"] = time.time() - t0
+    json.dump(res, open(os.path.join(out_dir, f"edge{rank}.json"), "w"))
+    if rank != 1:
+        st.close()
+
+
+def test_store_large_values_and_deadline(tmp_path):
+    """A value beyond get()'s first-guess buffer is fetched again at its real size; a blocking get whose key never appears fails
+    with a time-out after EWDML_STORE_TIMEOUT_S instead of hanging the rank (a dead peer must not hang the job)."""
+    world = 2
+    mp.spawn(_store_edge, args=(world, _free_port(), str(tmp_path)), nprocs=world, join=True)
+    r0, r1 = (json.load(open(tmp_path / f"edge{r}.json")) for r in (0, 1))
+    assert r0["large"] == r1["large"] == 3 << 20
+    assert r1["timeout"] == "timed out" and 1.0 < r1["waited"] < 10.0
