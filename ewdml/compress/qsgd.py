@@ -42,10 +42,19 @@ def qsgd_quantize(t: torch.Tensor, s: int, u: torch.Tensor, norm: Optional[torch
     if norm is None:
         norm = t.norm()
     norm = norm.reshape(()).to(torch.float32)
+    if t.is_cuda:
+        # device tensors: no host branch (float(norm) would synchronise once per tensor) -- a zero / non-finite norm selects
+        # scale 0, every level becomes 0 and the norm that travels is 0, on the tensor's own device
+        ok = torch.isfinite(norm) & (norm > 0)
+        scale = torch.where(ok, float(s) / torch.where(ok, norm, torch.ones_like(norm)), torch.zeros_like(norm))
+        lf = scale * t.abs()
+        prev = lf.floor()
+        level = (prev + (u.to(torch.float32) < (lf - prev)).to(torch.float32)).clamp_(max=float(s))
+        return level * t.sign(), torch.where(ok, norm, torch.zeros_like(norm)).reshape(1)
     if float(norm) == 0.0 or not math.isfinite(float(norm)):
         # zero tensor, or a sum of squares that overflows fp32: nothing is sent and the receiver reconstructs zeros
         # (the reference divides by the norm unguarded, qsgd.py:21; a non-finite norm would decode to NaN)
-        return torch.zeros_like(t), torch.zeros(1, dtype=torch.float32)
+        return torch.zeros_like(t), torch.zeros(1, dtype=torch.float32, device=t.device)
     scale = torch.tensor(float(s), dtype=torch.float32) / norm      # s / norm first, as the reference
     lf = scale * t.abs()
     prev = lf.floor()

@@ -75,8 +75,8 @@ class FlatAdam:
         g = grad if self.weight_decay == 0 else grad.add(self.param, alpha=self.weight_decay)
         self.exp_avg.mul_(b1).add_(g, alpha=1 - b1)
         self.exp_avg_sq.mul_(b2).addcmul_(g, g, value=1 - b2)
-        bc1 = 1.0 - torch.pow(torch.tensor(b1, dtype=torch.float64, device=self.t.device), self.t)
-        bc2 = 1.0 - torch.pow(torch.tensor(b2, dtype=torch.float64, device=self.t.device), self.t)
+        bc1 = 1.0 - torch.pow(float(b1), self.t)          # scalar base ** device exponent: no host -> device copy in the step
+        bc2 = 1.0 - torch.pow(float(b2), self.t)
         step_size = (self.lr * torch.sqrt(bc2) / bc1).to(torch.float32)
         self.param.sub_(self.exp_avg / self.exp_avg_sq.sqrt().add_(self.eps) * step_size)
         if self.param_bf16 is not None:
