@@ -167,13 +167,14 @@ class GpuTrainer:
         flat momentum buffer, device step state (sequence number / RNG position), error-feedback residual."""
         from ..utils import checkpoint as ckpt
         torch.cuda.synchronize(self.device)
-        ckpt.save_model(self.model, path, is_writer)
+        crc = ckpt.save_model(self.model, path, is_writer)
         extra = {"momentum": self.flat.momentum.detach().cpu() if self.flat.momentum is not None else None,
                  "device_state": self.exchange.state.detach().cpu(),
                  "residual": self.exchange.residual.detach().cpu() if getattr(self.exchange, "residual", None) is not None else None,
                  "adam": {k: v.detach().cpu() for k, v in self.exchange.adam.state_dict().items()}
                  if getattr(self.exchange, "adam", None) is not None else None}
-        ckpt.save_sidecar(path, step=self.step_idx, optimizer_state=None, extra=extra, is_writer=is_writer)
+        ckpt.save_sidecar(path, step=self.step_idx, optimizer_state=None, extra=extra, is_writer=is_writer, model_crc=crc,
+                          rng_rank=self.rank)
 
     def load_checkpoint(self, path: str) -> int:
         """Restore weights (+ sidecar when present); returns the step to continue from.  A captured graph stays valid:

@@ -74,17 +74,32 @@ class NNTrainer:
                     self.optimizer.load_state_dict(side["optimizer"])
                 except Exception as e:  # optimizer shape changed: keep weights, restart momentum
                     logger.warning("could not restore optimizer state: %s", e)
+            ex = side.get("extra") or {}
+            if ex.get("momentum") is not None and getattr(self.flat, "momentum", None) is not None:
+                self.flat.momentum.copy_(ex["momentum"])
+            exch = getattr(self, "exchange", None)
+            if ex.get("residual") is not None and getattr(exch, "residual", None) is not None:
+                exch.residual.copy_(ex["residual"])
             if side.get("torch_rng") is not None:
-                torch.set_rng_state(side["torch_rng"])
+                # only the rank that wrote the sidecar continues its own generator; the others re-derive theirs
+                if side.get("rng_rank") in (None, getattr(self, "rank", None)):
+                    torch.set_rng_state(side["torch_rng"])
+                else:
+                    ckpt.reseed_for_rank(self.cfg.seed, getattr(self, "rank", 0), self.cur_step)
         logger.info("resumed from %s at step %d", path, self.cur_step)
 
     def _generate_model_path(self) -> str:
         return ckpt.model_path(self.cfg.train_dir, self.cur_step, self.cfg.legacy_checkpoint_name)
 
     def _save_model(self, file_path: str, is_writer: bool = True):
-        ckpt.save_model(self.network, file_path, is_writer)
-        ckpt.save_sidecar(file_path, step=self.cur_step, optimizer_state=self.optimizer.state_dict(),
-                          is_writer=is_writer)
+        crc = ckpt.save_model(self.network, file_path, is_writer)
+        exch = getattr(self, "exchange", None)
+        mom = getattr(self.flat, "momentum", None)
+        res = getattr(exch, "residual", None)
+        extra = {"momentum": mom.detach().cpu() if mom is not None else None,           # flat-buffer optimizers keep their
+                 "residual": res.detach().cpu() if res is not None else None}          # state outside optimizer.state_dict()
+        ckpt.save_sidecar(file_path, step=self.cur_step, optimizer_state=self.optimizer.state_dict(), extra=extra,
+                          is_writer=is_writer, model_crc=crc, rng_rank=getattr(self, "rank", None))
 
     @torch.no_grad()
     def _evaluate_model(self, test_loader):

@@ -25,14 +25,29 @@ def model_path(train_dir: str, step: Optional[int] = None, legacy_name: bool = T
     return base if (legacy_name or step is None) else base + str(step)
 
 
-def _atomic_save(obj: Any, path: str) -> None:
+def _file_crc(path: str) -> int:
+    import zlib
+    crc = 0
+    with open(path, "rb") as f:
+        while True:
+            chunk = f.read(1 << 20)
+            if not chunk:
+                break
+            crc = zlib.crc32(chunk, crc)
+    return crc & 0xFFFFFFFF
+
+
+def _atomic_save(obj: Any, path: str) -> int:
+    """tmp + rename; returns the CRC-32 of the bytes written."""
     d = os.path.dirname(path)
     if d:
         os.makedirs(d, exist_ok=True)
     tmp = f"{path}.tmp.{os.getpid()}"
     with open(tmp, "wb") as f:
         torch.save(obj, f)
+    crc = _file_crc(tmp)
     os.replace(tmp, path)
+    return crc
 
 
 def cpu_state_dict(model: torch.nn.Module) -> "OrderedDict[str, torch.Tensor]":
@@ -44,17 +59,24 @@ def cpu_state_dict(model: torch.nn.Module) -> "OrderedDict[str, torch.Tensor]":
     return out
 
 
-def save_model(model: torch.nn.Module, path: str, is_writer: bool = True) -> None:
+def save_model(model: torch.nn.Module, path: str, is_writer: bool = True) -> Optional[int]:
+    """Writes the reference-format model file; returns its CRC-32 (pass it to :func:`save_sidecar`)."""
     if is_writer:
-        _atomic_save(cpu_state_dict(model), path)
+        return _atomic_save(cpu_state_dict(model), path)
+    return None
 
 
 def save_sidecar(path: str, *, step: int, optimizer_state: Optional[Dict] = None,
-                 extra: Optional[Dict] = None, is_writer: bool = True) -> None:
+                 extra: Optional[Dict] = None, is_writer: bool = True, model_crc: Optional[int] = None,
+                 rng_rank: Optional[int] = None) -> None:
+    """Model file first, sidecar second.  The two are separate renames, so a crash in between leaves a NEW model beside an
+    OLD sidecar; ``model_crc`` ties the sidecar to the exact model bytes it was written for and :func:`load_sidecar` ignores
+    a sidecar whose model has changed (weights are kept, step / optimizer state restart).  ``rng_rank``: whose generator
+    state ``torch_rng`` is -- other ranks must not adopt it (they would all draw the same dropout / QSGD streams)."""
     if not is_writer:
         return
     blob = {"format": "ewdml-sidecar-1", "step": int(step), "optimizer": optimizer_state,
-            "torch_rng": torch.get_rng_state(), "extra": extra or {}}
+            "torch_rng": torch.get_rng_state(), "rng_rank": rng_rank, "model_crc": model_crc, "extra": extra or {}}
     _atomic_save(blob, path + ".state")
 
 
@@ -69,4 +91,17 @@ def load_sidecar(path: str) -> Optional[Dict]:
     if not os.path.isfile(p):
         return None
     with open(p, "rb") as f:
-        return torch.load(f, map_location="cpu", weights_only=False)
+        side = torch.load(f, map_location="cpu", weights_only=False)
+    crc = side.get("model_crc") if isinstance(side, dict) else None
+    if crc is not None and os.path.isfile(path) and _file_crc(path) != crc:
+        import logging
+        logging.getLogger("ewdml").warning("%s was written for a different version of %s (interrupted checkpoint?): "
+                                           "keeping the weights, ignoring the stale step / optimizer state", p, path)
+        return None
+    return side
+
+
+def reseed_for_rank(seed: int, rank: int, step: int) -> None:
+    """Generator state of a rank that did not write the sidecar: derived from (seed, rank, step) so that ranks keep
+    distinct dropout / quantisation streams after a resume."""
+    torch.manual_seed((int(seed) + 1000 * (int(rank) + 1)) * 1_000_003 + int(step))

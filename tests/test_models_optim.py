@@ -161,3 +161,27 @@ def test_single_process_trainer_and_resume(tmp_path):
     assert torch.equal(mom_saved, mom_now)
     hist = r.train(loader, test, total_steps=6)
     assert [h["step"] for h in hist] == [4, 5]
+
+
+def test_sidecar_is_tied_to_its_model_file(tmp_path):
+    """Model file and sidecar are two renames.  A crash between them leaves a new model beside an old sidecar: the sidecar
+    carries the CRC of the model bytes it belongs to and is ignored (weights kept, step / optimizer restart) when they differ."""
+    import torch
+    from ewdml.models import build_model
+    from ewdml.utils import checkpoint as ckpt
+    m = build_model("LeNet", 10)
+    path = str(tmp_path / "model_step_")
+    crc = ckpt.save_model(m, path)
+    ckpt.save_sidecar(path, step=7, optimizer_state={"x": 1}, extra={"momentum": torch.ones(3)}, model_crc=crc, rng_rank=1)
+    side = ckpt.load_sidecar(path)
+    assert side["step"] == 7 and side["rng_rank"] == 1 and torch.equal(side["extra"]["momentum"], torch.ones(3))
+    with torch.no_grad():
+        m.fc2.bias.add_(1.0)
+    ckpt.save_model(m, path)                         # "crash" before the matching sidecar is written
+    assert ckpt.load_sidecar(path) is None
+    ckpt.load_model(build_model("LeNet", 10), path)  # the weights themselves still load
+    # ranks that did not write the sidecar derive distinct generator states from (seed, rank, step)
+    ckpt.reseed_for_rank(1, 2, 7); a = torch.rand(4)
+    ckpt.reseed_for_rank(1, 3, 7); b = torch.rand(4)
+    ckpt.reseed_for_rank(1, 2, 7); c = torch.rand(4)
+    assert torch.equal(a, c) and not torch.equal(a, b)
