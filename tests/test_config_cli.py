@@ -106,3 +106,38 @@ def test_c_abi_header_is_c99_and_links_from_c(tmp_path):
     assert cc.returncode == 0, cc.stderr
     out = subprocess.run([exe], capture_output=True, text=True, timeout=60)
     assert out.returncode == 0 and "offsets 0 1024 used 71168" in out.stdout and "counter 3" in out.stdout
+
+
+def test_cloud_tool_plan_and_dry_run(tmp_path):
+    """tools/cloud.py (the instance-renting half of the reference's pytorch_ec2.py): self-referential configuration, the
+    run_instances requests for master + workers, dry-run of launch / hosts / terminate, hosts-file format -- all offline."""
+    import importlib.util, json, os, subprocess, sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    tool = os.path.join(root, "tools", "cloud.py")
+    cfgf = tmp_path / "c.json"
+    cfgf.write_text(json.dumps({"name": "t1", "region": "eu-west-1", "image_id": "ami-x", "key_name": "k", "n_workers": 3,
+                                "master_type": "p6-b200.48xlarge", "spot_price": "9.5", "hosts_file": str(tmp_path / "hosts")}))
+    out = subprocess.run([sys.executable, tool, "--config", str(cfgf), "plan"], capture_output=True, text=True, timeout=60)
+    assert out.returncode == 0, out.stderr
+    plan = json.loads(out.stdout)
+    assert plan["config"]["availability_zone"] == "eu-west-1b" and plan["config"]["worker_type"] == "p6-b200.48xlarge"
+    reqs = plan["run_instances"]
+    assert [r["MaxCount"] for r in reqs] == [1, 3]
+    assert reqs[1]["InstanceMarketOptions"]["SpotOptions"]["MaxPrice"] == "9.5"
+    assert {t["Value"] for t in reqs[0]["TagSpecifications"][0]["Tags"]} == {"t1", "master"}
+    dry = subprocess.run([sys.executable, tool, "--config", str(cfgf), "--dry-run", "launch"], capture_output=True, text=True, timeout=60)
+    assert dry.returncode == 0 and dry.stdout.count("ec2.run_instances(") == 2
+    assert subprocess.run([sys.executable, tool, "--config", str(cfgf), "--dry-run", "terminate"], capture_output=True, text=True,
+                          timeout=60).returncode == 0
+    # hosts file in the format tools/cluster.py reads (master first)
+    spec = importlib.util.spec_from_file_location("ewdml_cloud_tool", tool)
+    mod = importlib.util.module_from_spec(spec); spec.loader.exec_module(mod)
+    cfg = mod.load_config(str(cfgf))
+    mod.write_hosts([{"id": "i-1", "role": "master", "private_ip": "10.0.0.1", "public_ip": ""},
+                     {"id": "i-2", "role": "worker", "private_ip": "10.0.0.2", "public_ip": ""}], cfg)
+    spec2 = importlib.util.spec_from_file_location("ewdml_cluster_tool", os.path.join(root, "tools", "cluster.py"))
+    cl = importlib.util.module_from_spec(spec2); spec2.loader.exec_module(cl)
+    assert cl.read_hosts(str(tmp_path / "hosts")) == [("ubuntu@10.0.0.1", 8), ("ubuntu@10.0.0.2", 8)]
+    import pytest
+    with pytest.raises(ValueError):
+        mod.resolve({"a": "%(b)s", "b": "%(a)sx"})
