@@ -19,6 +19,13 @@ def main():
         import torch
         info["torch"] = torch.__version__
         info["cuda_devices"] = torch.cuda.device_count() if torch.cuda.is_available() else 0
+        if lib.available() and torch.cuda.is_available():
+            # what the symmetric heap can use on this device: VMM allocations, POSIX-fd handles, NVLS multicast objects
+            import ctypes as C
+            q = (C.c_int * 3)()
+            lib.load().ewdml_vmm_query(q)
+            info["transport"] = {"vmm": bool(q[0]), "multicast": bool(q[1]), "posix_fd_handles": bool(q[2]),
+                                 "sm_count": int(lib.load().ewdml_sm_count())}
     except Exception:
         pass
     print(json.dumps(info, indent=1, default=str))

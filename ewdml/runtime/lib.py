@@ -105,6 +105,7 @@ def load() -> C.CDLL:
         "ewdml_heap_import": (i32, [C.c_char_p, P(vp)]),
         "ewdml_heap_unmap": (i32, [vp]),
         "ewdml_can_access_peer": (i32, [i32, i32, P(i32)]),
+        "ewdml_sm_count": (i32, []),
         "ewdml_vmm_query": (i32, [P(i32)]),
         "ewdml_vmm_granularity": (i32, [i32, P(C.c_size_t)]),
         "ewdml_vmm_alloc": (i32, [P(vp), C.c_size_t, P(vp), P(i32)]),
