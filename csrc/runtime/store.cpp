@@ -104,7 +104,14 @@ struct Server {
                 break;
             }
         }
-        ::close(fd);
+        // Forget the descriptor before closing it: the number may be handed to an unrelated socket of this process right
+        // away, and destroy() shuts down everything still listed.
+        {
+            std::lock_guard<std::mutex> lk(mu);
+            for (size_t i = 0; i < fds.size(); ++i)
+                if (fds[i] == fd) { fds[i] = fds.back(); fds.pop_back(); break; }
+            ::close(fd);
+        }
         active.fetch_sub(1);
     }
 
@@ -264,9 +271,9 @@ extern "C" int ewdml_store_destroy(ewdml_store* s) {
         // that died without closing.
         for (int waited_ms = 0; sv->active.load() > 0 && waited_ms < 20000; waited_ms += 5)
             std::this_thread::sleep_for(std::chrono::milliseconds(5));
-        sv->stop.store(true);
+        // stop is set under the mutex the waiters check their predicate under, so no waiter can miss the wake-up.
+        { std::lock_guard<std::mutex> lk(sv->mu); sv->stop.store(true); for (int fd : sv->fds) ::shutdown(fd, SHUT_RDWR); }
         sv->cv.notify_all();
-        { std::lock_guard<std::mutex> lk(sv->mu); for (int fd : sv->fds) ::shutdown(fd, SHUT_RDWR); }
         if (sv->accept_thread.joinable()) sv->accept_thread.join();
         for (auto& t : sv->workers) if (t.joinable()) t.join();
         ::close(sv->listen_fd);

@@ -5,6 +5,7 @@ import os
 import socket
 import time
 
+import pytest
 import torch.multiprocessing as mp
 
 
@@ -180,3 +181,29 @@ def test_store_large_values_and_deadline(tmp_path):
     r0, r1 = (json.load(open(tmp_path / f"edge{r}.json")) for r in (0, 1))
     assert r0["large"] == r1["large"] == 3 << 20
     assert r1["timeout"] == "timed out" and 1.0 < r1["waited"] < 10.0
+
+
+@pytest.mark.parametrize("sanitizer", ["thread", "address,undefined"])
+def test_store_under_sanitizers(tmp_path, sanitizer):
+    """The store's server and client code under ThreadSanitizer and Address/UB sanitizer: several ranks as threads, values
+    that cross the buffer-resize path, named barriers, and the host leaving first (tests/native/store_stress.cpp)."""
+    import shutil
+    import subprocess
+    if shutil.which("g++") is None:
+        pytest.skip("no g++")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    exe = str(tmp_path / "store_stress")
+    build = subprocess.run(["g++", "-std=c++17", "-O1", "-g", f"-fsanitize={sanitizer}", "-fno-omit-frame-pointer",
+                            os.path.join(root, "tests", "native", "store_stress.cpp"),
+                            os.path.join(root, "csrc", "runtime", "store.cpp"), "-lpthread", "-o", exe],
+                           capture_output=True, text=True)
+    if build.returncode != 0 and "sanitizer" in build.stderr.lower() and "cannot find" in build.stderr.lower():
+        pytest.skip("sanitizer runtime not installed")
+    assert build.returncode == 0, build.stderr[-2000:]
+    env = dict(os.environ, TSAN_OPTIONS="halt_on_error=1 exitcode=66", ASAN_OPTIONS="detect_leaks=1 exitcode=67",
+               UBSAN_OPTIONS="halt_on_error=1 print_stacktrace=1")
+    env.pop("LD_PRELOAD", None)
+    run = subprocess.run([exe, str(_free_port()), "6", "40"], capture_output=True, text=True, timeout=300, env=env)
+    assert run.returncode == 0, (run.stdout + run.stderr)[-3000:]
+    assert "store_stress ok" in run.stdout
+    assert "Sanitizer" not in run.stderr, run.stderr[-3000:]
