@@ -174,3 +174,19 @@ def test_adam_with_numpy_gradients_agrees_with_the_reference_optimizer(ref, kw):
         assert torch.equal(a.detach(), b.detach())
     if flat is not None:
         assert torch.allclose(flat.param, torch.cat([p.detach().flatten() for p in p_ref]), atol=1e-6, rtol=0)
+
+
+@pytest.mark.parametrize("ctor", ["vgg11", "vgg13", "vgg13_bn", "vgg16", "vgg16_bn", "vgg19", "vgg19_bn"])
+def test_other_vgg_variants_are_checkpoint_compatible_with_the_reference(ref, ctor):
+    import ewdml.models as M
+    torch.manual_seed(0)
+    _load_both_ways(getattr(ref["model_ops.vgg"], ctor)(), getattr(M, ctor)(10), torch.randn(2, 3, 32, 32))
+
+
+@pytest.mark.parametrize("ctor", ["ResNet34", "ResNet101", "ResNet152"])
+def test_deeper_resnets_are_checkpoint_compatible_with_the_reference(ref, ctor):
+    import ewdml.models as M
+    torch.manual_seed(0)
+    mk = getattr(ref["model_ops.resnet"], ctor)
+    theirs = mk(10) if ctor == "ResNet34" else mk()
+    _load_both_ways(theirs, getattr(M, ctor)(10), torch.randn(2, 3, 32, 32))
