@@ -19,20 +19,35 @@ pytestmark = pytest.mark.skipif(not os.path.isdir(os.path.join(REF, "Compresssor
                                 reason="reference not installed (bash baseline/install_reference.sh)")
 
 
+_TOP = ("Compresssor", "model_ops", "optim", "nn_ops", "util")
+
+
 @pytest.fixture(scope="module")
 def ref():
-    """The reference's packages, imported from baseline/_ref under their own top-level names."""
-    sys.path.insert(0, REF)
+    """The reference's packages, imported from baseline/_ref under their own top-level names.  ewdml/compat offers modules
+    of the SAME names (tests/test_compat.py puts them on sys.path), so whatever is cached under those names is set aside
+    first and put back afterwards, and every imported module is checked to come from baseline/_ref."""
+    import importlib
+    saved = {n: sys.modules.pop(n) for n in list(sys.modules) if n.split(".")[0] in _TOP}
+    saved_path = list(sys.path)
+    # the reference's Compresssor/ has no __init__.py (a namespace package), and a regular package of that name anywhere
+    # on the path would win over it: the compat directory leaves the path while the reference is being imported
+    compat = os.path.join(ROOT, "ewdml", "compat")
+    sys.path[:] = [REF] + [p for p in sys.path if os.path.abspath(p or ".") != compat]
+    importlib.invalidate_caches()
     try:
-        import importlib
         mods = {n: importlib.import_module(n) for n in
                 ("Compresssor.TopK", "Compresssor.qsgd", "model_ops.lenet", "model_ops.vgg", "model_ops.resnet",
                  "optim.sgd", "optim.adam", "nn_ops")}
+        for n, m in mods.items():
+            assert os.path.abspath(m.__file__).startswith(REF + os.sep), (n, m.__file__)
         yield mods
     finally:
-        sys.path.remove(REF)
-        for n in [m for m in sys.modules if m.split(".")[0] in ("Compresssor", "model_ops", "optim", "nn_ops")]:
+        sys.path[:] = saved_path
+        importlib.invalidate_caches()
+        for n in [m for m in sys.modules if m.split(".")[0] in _TOP]:
             del sys.modules[n]
+        sys.modules.update(saved)
 
 
 def _distinct(n, seed):
