@@ -45,6 +45,12 @@ def main(a, ClockSampler, metric_name):
         dist.init_process_group("nccl", rank=rank, world_size=world, device_id=device)
     torch.manual_seed(1)
     torch.backends.cudnn.benchmark = True
+    # --dtype: bf16 = autocast over fp32 master weights; tf32 = fp32 tensors, tensor-core convolutions and GEMMs with
+    # 10-bit mantissa inputs (the fastest library mode that keeps the reference's fp32 storage); fp32 = no tensor cores.
+    if a.dtype not in ("bf16", "tf32", "fp32"):
+        raise SystemExit(f"--impl nccl: --dtype must be bf16, tf32 or fp32, got {a.dtype}")
+    torch.backends.cuda.matmul.allow_tf32 = a.dtype == "tf32"
+    torch.backends.cudnn.allow_tf32 = a.dtype == "tf32"
     dataset = "MNIST" if a.model.lower() in ("lenet", "mnistnet") else "Cifar10"
     model = build_model(a.model, 10).to(device).to(memory_format=torch.channels_last)
     model.train()
@@ -226,7 +232,8 @@ def main(a, ClockSampler, metric_name):
                           "data": "synthetic (CIFAR-10 shape, random-init weights)",
                           "config": {"model": a.model, "global_batch": a.batch_size * world, "per_gpu_batch": a.batch_size, "parallelism": f"dp{world}",
                                      "compressor": a.compressor, "topk_ratio": a.topk_ratio, "qsgd_levels": a.qsgd_levels,
-                                     "compute": "torch/cuDNN channels-last, bf16 autocast" if a.dtype == "bf16" else "torch/cuDNN channels-last fp32",
+                                     "compute": {"bf16": "torch/cuDNN channels-last, bf16 autocast", "tf32": "torch/cuDNN channels-last, fp32 tensors with TF32 tensor cores",
+                                                 "fp32": "torch/cuDNN channels-last fp32, TF32 off"}[a.dtype],
                                      "exchange": ("nccl all_gather_into_tensor, one call" if compress else "nccl all_reduce, 32 MB fused slices"),
                                      "cuda_graph": graph is not None,
                                      "l2": "none" if a.no_flush else "256 MiB buffer overwritten every step inside the timed region"},
