@@ -61,3 +61,26 @@ def test_batched_augmentation_is_a_crop_of_the_reflect_padded_image_optionally_f
         assert hits, "not a crop of the padded image"
         kinds.add(hits[0][2])
     assert torch.equal(gpu_augment(x[:, :, :, :], pad=0).flip(3).flip(3).abs().sum() > 0, torch.tensor(True))
+
+
+def test_data_prepare_reports_missing_datasets_without_failing(monkeypatch, capsys):
+    """src/data/data_prepare.py downloads the four datasets; offline, the tool names what is missing and exits 0."""
+    import pytest
+    from torchvision import datasets
+    from ewdml.cli import data_prepare
+
+    def offline(*a, **k):
+        raise RuntimeError("no network")
+
+    class Ready:
+        def __init__(self, *a, **k):
+            pass
+
+    monkeypatch.setattr(datasets, "MNIST", Ready)
+    for name in ("CIFAR10", "CIFAR100", "SVHN"):
+        monkeypatch.setattr(datasets, name, offline)
+    with pytest.raises(SystemExit) as e:
+        data_prepare.main()
+    assert e.value.code == 0
+    out = capsys.readouterr().out
+    assert "MNIST: ready" in out and "missing: CIFAR10, CIFAR100, SVHN" in out
