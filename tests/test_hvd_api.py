@@ -27,6 +27,47 @@ def test_launcher_tears_job_down_on_failure():
     assert out.returncode == 5 and "rank 1 exited with status 5" in out.stderr
 
 
+def test_launcher_passes_a_termination_signal_on_to_the_ranks(tmp_path):
+    """mpirun forwards SIGINT / SIGTERM to the job (orterun); here every rank has its own process group, so the launcher
+    has to do it: SIGTERM to the launcher ends the ranks AND what they started, and the exit status says which signal."""
+    import signal
+    import time
+    code = ("import os, subprocess, sys, time\n"
+            "child = subprocess.Popen([sys.executable, '-c', 'import time; time.sleep(120)'])\n"
+            "open(os.path.join(sys.argv[1], 'pids%s' % os.environ['RANK']), 'w').write('%d %d' % (os.getpid(), child.pid))\n"
+            "time.sleep(120)\n")
+    proc = subprocess.Popen([sys.executable, "-m", "ewdml.cli.launch", "-np", "2", "--grace-seconds", "1", "--",
+                             sys.executable, "-c", code, str(tmp_path)], stderr=subprocess.PIPE, text=True, cwd=ROOT)
+    deadline = time.time() + 60
+    while time.time() < deadline and not all((tmp_path / f"pids{r}").exists() and (tmp_path / f"pids{r}").read_text().count(" ") == 1
+                                             for r in range(2)):
+        time.sleep(0.1)
+    pids = [int(x) for r in range(2) for x in (tmp_path / f"pids{r}").read_text().split()]
+    assert len(pids) == 4
+    proc.send_signal(signal.SIGTERM)
+    _, err = proc.communicate(timeout=30)
+    assert proc.returncode == 128 + signal.SIGTERM, (proc.returncode, err)
+    assert "caught signal 15" in err
+    time.sleep(0.3)
+    for pid in pids:                       # ranks and their own children are gone (a zombie of a foreign parent counts as gone)
+        try:
+            with open(f"/proc/{pid}/stat") as f:
+                assert f.read().split(") ")[1][0] == "Z", pid
+        except FileNotFoundError:
+            pass
+
+
+def test_launcher_leaves_the_callers_other_children_alone():
+    """The watchdog waits for its own ranks only: a child the calling process started before is still there to be waited for."""
+    from ewdml.runtime import lib
+    other = subprocess.Popen([sys.executable, "-c", "import sys; sys.exit(7)"])
+    import time
+    time.sleep(1.0)                         # it has exited and is waiting to be reaped
+    status, failed = lib.launch(2, [sys.executable, "-c", "pass"], "127.0.0.1", 29500, 1.0)
+    assert (status, failed) == (0, -1)
+    assert other.wait(timeout=10) == 7
+
+
 def test_info_tool_and_adasum_pair():
     out = subprocess.run([sys.executable, "-m", "ewdml.cli.info"], capture_output=True, text=True, timeout=120, cwd=ROOT)
     info = json.loads(out.stdout)
