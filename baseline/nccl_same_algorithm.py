@@ -229,7 +229,7 @@ def main(a, ClockSampler, metric_name):
         print(json.dumps({"impl": "nccl", "metric": metric_name(a),
                           "value": value, "unit": "images/s", "n_gpus": world, "steps": a.steps, "warmup": W, "ms_per_step": ms / a.steps,
                           "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": a.dtype,
-                          "data": "synthetic (CIFAR-10 shape, random-init weights)",
+                          "data": "synthetic (%s shape, random-init weights)" % ("MNIST" if a.model.lower() in ("lenet", "mnistnet") else "CIFAR-10"),
                           "config": {"model": a.model, "global_batch": a.batch_size * world, "per_gpu_batch": a.batch_size, "parallelism": f"dp{world}",
                                      "compressor": a.compressor, "topk_ratio": a.topk_ratio, "qsgd_levels": a.qsgd_levels,
                                      "compute": {"bf16": "torch/cuDNN channels-last, bf16 autocast", "tf32": "torch/cuDNN channels-last, fp32 tensors with TF32 tensor cores",

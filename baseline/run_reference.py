@@ -125,7 +125,7 @@ def main(a, ClockSampler, metric_name):
         "value": value, "unit": "images/s", "n_gpus": a.gpus, "steps": K, "warmup": W, "ms_per_step": elapsed / K * 1e3,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "fp32",
         "reference_class": "gpu" if gpu_mode else "cpu",
-        "data": "synthetic (CIFAR-10 shape, random-init weights)", "mode": mode, "note": note,
+        "data": "synthetic (%s shape, random-init weights)" % ("MNIST" if a.model.lower() in ("lenet", "mnistnet") else "CIFAR-10"), "mode": mode, "note": note,
         "config": {"model": a.model, "global_batch": a.batch_size * a.gpus, "per_gpu_batch": a.batch_size,
                    "parallelism": f"ps: 1 server + {a.gpus} workers (gloo)", "compressor": "none (compression calls are commented out in the reference snapshot)"},
         "timed_with": "host clock on the reference's own per-step log line, max over workers",

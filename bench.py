@@ -234,7 +234,7 @@ def run_ewdml(a):
         "value": value, "unit": "images/s", "n_gpus": a.gpus, "steps": a.steps, "warmup": max(3, a.warmup),
         "ms_per_step": ms / a.steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None,      # BASELINE.md publishes no images/s figure (CPU-only Colab minutes and MB/iteration)
-        "dtype": a.dtype, "data": "synthetic (CIFAR-10 shape, random-init weights)", "impl": "ewdml",
+        "dtype": a.dtype, "data": "synthetic (%s shape, random-init weights)" % ("MNIST" if a.model.lower() in ("lenet", "mnistnet") else "CIFAR-10"), "impl": "ewdml",
         "config": {"model": a.model, "global_batch": a.batch_size * n_workers, "per_gpu_batch": a.batch_size,
                    "seq_len": None, "image": list(tr.input_spec()[1:]),
                    "parallelism": f"dp{world}" + ("(1 server)" if a.exchange == "ps" else ""),
