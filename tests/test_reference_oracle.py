@@ -205,3 +205,40 @@ def test_deeper_resnets_are_checkpoint_compatible_with_the_reference(ref, ctor):
     mk = getattr(ref["model_ops.resnet"], ctor)
     theirs = mk(10) if ctor == "ResNet34" else mk()
     _load_both_ways(theirs, getattr(M, ctor)(10), torch.randn(2, 3, 32, 32))
+
+
+def test_horovod_flavour_qsgd_agrees_with_the_reference_module(ref, capsys):
+    """horovod_compression.py needs ``horovod.torch`` only for the ``Compressor`` base class: with a two-line stand-in for
+    that absent package the reference module itself is the oracle for the static compress / decompress pair."""
+    import importlib
+    import types
+    from ewdml.compress import Compression
+    hv, hvt, hvc = types.ModuleType("horovod"), types.ModuleType("horovod.torch"), types.ModuleType("horovod.torch.compression")
+    hvc.Compressor = type("Compressor", (), {})
+    hv.torch, hvt.compression = hvt, hvc
+    stand_ins = {"horovod": hv, "horovod.torch": hvt, "horovod.torch.compression": hvc}
+    saved = {n: sys.modules.get(n) for n in list(stand_ins) + ["horovod_compression"]}
+    sys.modules.update(stand_ins)
+    sys.path.insert(0, REF)
+    try:
+        pytest.importorskip("torchvision")                      # imported (unused) by the reference module
+        mod = importlib.import_module("horovod_compression")
+        assert os.path.abspath(mod.__file__).startswith(REF + os.sep)
+        t = torch.randn(7, 33, generator=torch.Generator().manual_seed(5)) * 0.01
+        torch.manual_seed(21)
+        levels_ref, norm_ref = mod.QSGDCompressor.compress(t)
+        torch.manual_seed(21)
+        levels, norm = Compression.qsgd.compress(t)
+        assert torch.equal(norm.flatten().float(), norm_ref.flatten())
+        assert torch.equal(levels.float(), levels_ref)
+        assert torch.equal(Compression.qsgd.decompress(levels, norm), mod.QSGDCompressor.decompress(levels_ref, norm_ref))
+        # interchangeable across the wire: each side decodes what the other produced
+        assert torch.equal(Compression.qsgd.decompress(levels_ref.to(levels.dtype), norm_ref), mod.QSGDCompressor.decompress(levels.float(), norm))
+    finally:
+        sys.path.remove(REF)
+        for n, m in saved.items():
+            if m is None:
+                sys.modules.pop(n, None)
+            else:
+                sys.modules[n] = m
+    capsys.readouterr()                                          # the reference prints the norm on every call
