@@ -22,10 +22,7 @@ def _free_port():
     s = socket.socket(); s.bind(("127.0.0.1", 0)); p = s.getsockname()[1]; s.close(); return p
 
 
-def _run(rank, world, port, cfg_kwargs, out_dir):
-    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
-    torch.set_num_threads(1)
-    dist.init_process_group("gloo", rank=rank, world_size=world)
+def _one_job(rank, world, cfg_kwargs, out_dir):
     cfg_kwargs = dict(cfg_kwargs)
     factory = None
     if cfg_kwargs.pop("_factory", None) == "library":
@@ -53,25 +50,67 @@ def _run(rank, world, port, cfg_kwargs, out_dir):
     with open(os.path.join(out_dir, f"r{rank}.json"), "w") as f:
         json.dump(res, f)
     dist.barrier()
+
+
+def _run(rank, world, port, cfg_kwargs, out_dir):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    torch.set_num_threads(1)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    _one_job(rank, world, cfg_kwargs, out_dir)
     dist.destroy_process_group()
 
 
+def _run_many(rank, world, port, jobs, out_root):
+    """Several independent training jobs, one after the other, in ONE set of processes (process start-up is most of what a
+    small job costs); every job builds its own model, data and exchange from its configuration, with a barrier in between."""
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    torch.set_num_threads(1)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    for name, cfg_kwargs in jobs:
+        _one_job(rank, world, cfg_kwargs, os.path.join(out_root, name))
+    dist.destroy_process_group()
+
+
+_BASE = dict(network="LeNet", dataset="MNIST", batch_size=16, max_steps=8, epochs=2, lr=0.02,
+             momentum=0.9, synthetic_size=256, data="synthetic", eval_freq=4, log_interval=100)
+
+
+def _launch_many(world, root, jobs):
+    """jobs: {name: configuration overrides}; returns {name: [result of rank 0, 1, ...]}, files under root/name/."""
+    full = []
+    for name, kw in jobs.items():
+        os.makedirs(os.path.join(str(root), name), exist_ok=True)
+        base = dict(_BASE, train_dir=os.path.join(str(root), name) + "/")
+        base.update(kw)
+        full.append((name, base))
+    mp.spawn(_run_many, args=(world, _free_port(), full, str(root)), nprocs=world, join=True)
+    return {name: [json.load(open(os.path.join(str(root), name, f"r{r}.json"))) for r in range(world)] for name, _ in full}
+
+
 def _launch(world, tmp_path, **kw):
-    base = dict(network="LeNet", dataset="MNIST", batch_size=16, max_steps=8, epochs=2, lr=0.02,
-                momentum=0.9, synthetic_size=256, data="synthetic", eval_freq=4,
-                train_dir=str(tmp_path) + "/", log_interval=100)
+    base = dict(_BASE, train_dir=str(tmp_path) + "/")
     base.update(kw)
     mp.spawn(_run, args=(world, _free_port(), base, str(tmp_path)), nprocs=world, join=True)
     return [json.load(open(os.path.join(str(tmp_path), f"r{r}.json"))) for r in range(world)]
 
 
+@pytest.fixture(scope="module")
+def six_methods(tmp_path_factory):
+    root = tmp_path_factory.mktemp("six_methods")
+    jobs = {}
+    for method in range(1, 7):
+        extra = dict(topk_ratio=0.4) if method >= 5 else {}
+        if method == 6:
+            extra["sync_period"] = 4
+        jobs[f"m{method}"] = dict(method=method, **extra)
+    return root, _launch_many(3, root, jobs)
+
+
 @pytest.mark.parametrize("method", [1, 2, 3, 4, 5, 6])
-def test_ps_all_six_methods(tmp_path, method):
-    extra = dict(topk_ratio=0.4) if method >= 5 else {}
-    if method == 6:
-        extra["sync_period"] = 4
-    res = _launch(3, tmp_path, method=method, **extra)
-    server, w1, w2 = res
+def test_ps_all_six_methods(six_methods, method):
+    root, results = six_methods
+    tmp_path = os.path.join(str(root), f"m{method}")
+    server, w1, w2 = results[f"m{method}"]
     assert server["role"] == "server" and server["steps"] == 8
     for w in (w1, w2):
         assert len(w["loss"]) == 8 and all(l == l for l in w["loss"])       # no NaNs
@@ -98,10 +137,18 @@ def test_ps_world_size_2_loss_decreases(tmp_path):
     assert sum(losses[-5:]) / 5 < sum(losses[:5]) / 5 - 0.1
 
 
-@pytest.mark.parametrize("exchange,compressor", [("allgather", "topk-qsgd"), ("allgather", "qsgd"),
-                                                 ("allgather", "topk"), ("allreduce", "none")])
-def test_serverless_exchanges(tmp_path, exchange, compressor):
-    res = _launch(2, tmp_path, exchange=exchange, compressor=compressor, topk_ratio=0.1)
+_SERVERLESS = [("allgather", "topk-qsgd"), ("allgather", "qsgd"), ("allgather", "topk"), ("allreduce", "none")]
+
+
+@pytest.fixture(scope="module")
+def serverless(tmp_path_factory):
+    root = tmp_path_factory.mktemp("serverless")
+    return _launch_many(2, root, {f"{e}-{c}": dict(exchange=e, compressor=c, topk_ratio=0.1) for e, c in _SERVERLESS})
+
+
+@pytest.mark.parametrize("exchange,compressor", _SERVERLESS)
+def test_serverless_exchanges(serverless, exchange, compressor):
+    res = serverless[f"{exchange}-{compressor}"]
     assert res[0]["checksum"] == pytest.approx(res[1]["checksum"], rel=1e-9)
     assert len(res[0]["loss"]) == 8
 
@@ -117,14 +164,26 @@ def test_cli_entrypoint_under_torchrun(tmp_path):
     assert "I am the master" in out.stdout and "I am worker: 1 in all 1 workers" in out.stdout
 
 
-@pytest.mark.parametrize("exchange,method,compressor", [("allgather", 0, "topk"), ("allreduce", 3, ""), ("ps", 1, ""), ("ps", 3, "")])
-def test_library_only_arm_matches_plumbing(tmp_path, exchange, method, compressor):
+_LIBRARY = [("allgather", 0, "topk"), ("allreduce", 3, ""), ("ps", 1, ""), ("ps", 3, "")]
+
+
+@pytest.fixture(scope="module")
+def library_pairs(tmp_path_factory):
+    root = tmp_path_factory.mktemp("library")
+    jobs = {}
+    for e, m, c in _LIBRARY:
+        kw = dict(exchange=e, method=m, compressor=c, topk_ratio=0.25, max_steps=4)
+        jobs[f"{e}-{m}-plumbing"] = kw
+        jobs[f"{e}-{m}-library"] = dict(kw, _factory="library")
+    return _launch_many(3, root, jobs)
+
+
+@pytest.mark.parametrize("exchange,method,compressor", _LIBRARY)
+def test_library_only_arm_matches_plumbing(library_pairs, exchange, method, compressor):
     """The torch-ops + collectives classes behind --backend nccl compute the same updates as the packed gloo path
     (deterministic compressors only; run here on CPU tensors over gloo)."""
-    kw = dict(exchange=exchange, method=method, compressor=compressor, topk_ratio=0.25, max_steps=4)
-    (tmp_path / "a").mkdir(); (tmp_path / "b").mkdir()
-    a = _launch(3, tmp_path / "a", **kw)
-    b = _launch(3, tmp_path / "b", _factory="library", **kw)
+    a = library_pairs[f"{exchange}-{method}-plumbing"]
+    b = library_pairs[f"{exchange}-{method}-library"]
     wa = [r for r in a if r["role"] == "worker"]
     wb = [r for r in b if r["role"] == "worker"]
     assert wa[0]["checksum"] == pytest.approx(wb[0]["checksum"], rel=1e-6)
@@ -135,12 +194,9 @@ def test_library_only_arm_matches_plumbing(tmp_path, exchange, method, compresso
 def test_bucketed_overlapped_allgather_equals_monolithic(tmp_path):
     """--bucket-size/--overlap change when the exchange runs, not what it computes (per-tensor norms and top-k,
     element-indexed random numbers)."""
-    for d in ("a", "b", "c"):
-        (tmp_path / d).mkdir()
     kw = dict(exchange="allgather", compressor="topk-qsgd", topk_ratio=0.1, max_steps=5)
-    a = _launch(2, tmp_path / "a", **kw)
-    b = _launch(2, tmp_path / "b", bucket_size=100000, **kw)
-    c = _launch(2, tmp_path / "c", bucket_size=100000, overlap=True, **kw)
+    res = _launch_many(2, tmp_path, {"a": kw, "b": dict(kw, bucket_size=100000), "c": dict(kw, bucket_size=100000, overlap=True)})
+    a, b, c = res["a"], res["b"], res["c"]
     for other in (b, c):
         assert other[0]["checksum"] == pytest.approx(a[0]["checksum"], rel=1e-12)
         assert other[0]["loss"] == pytest.approx(a[0]["loss"], rel=1e-9)
