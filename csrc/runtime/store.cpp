@@ -64,6 +64,19 @@ bool recv_blob(int fd, std::string* s) {
 
 enum : uint8_t { OP_SET = 1, OP_GET = 2, OP_ADD = 3 };
 
+// Has the other end closed?  (Requests are strictly one at a time per connection, so while a reply is owed nothing but a
+// hang-up can arrive.)
+bool peer_gone(int fd) {
+    pollfd p{fd, (short)(POLLIN | POLLRDHUP), 0};
+    if (::poll(&p, 1, 0) <= 0) return false;
+    if (p.revents & (POLLRDHUP | POLLHUP | POLLERR | POLLNVAL)) return true;
+    if (p.revents & POLLIN) {
+        char c;
+        return ::recv(fd, &c, 1, MSG_PEEK | MSG_DONTWAIT) == 0;
+    }
+    return false;
+}
+
 struct Server {
     int listen_fd = -1;
     std::thread accept_thread;
@@ -89,8 +102,17 @@ struct Server {
                 if (!send_all(fd, &ok, 1)) break;
             } else if (op == OP_GET) {
                 std::unique_lock<std::mutex> lk(mu);
-                cv.wait(lk, [&] { return stop.load() || kv.count(key); });
-                if (stop.load() && !kv.count(key)) break;
+                // Wait for the key, but look at the connection now and then: a client that died while blocked here would
+                // otherwise keep this thread (and the server's shutdown, which waits for its connections) until the end.
+                bool gone = false;
+                while (!stop.load() && !kv.count(key) && !gone) {
+                    cv.wait_for(lk, std::chrono::milliseconds(250));
+                    if (stop.load() || kv.count(key)) break;
+                    lk.unlock();
+                    gone = peer_gone(fd);
+                    lk.lock();
+                }
+                if (!kv.count(key)) break;
                 std::string v = kv[key];
                 lk.unlock();
                 if (!send_blob(fd, v)) break;

@@ -10,6 +10,11 @@
 // linger-until-clients-leave logic exists for.
 //
 //   usage: store_stress PORT [WORLD=4] [ROUNDS=40]
+#include <arpa/inet.h>
+#include <netinet/in.h>
+#include <sys/socket.h>
+#include <unistd.h>
+
 #include <atomic>
 #include <chrono>
 #include <cstdarg>
@@ -52,11 +57,29 @@ static std::string value_of(int rank, int round) {
     return v;
 }
 
+// A client that asks for a key nobody will ever set and then dies: the server thread serving it has to notice the hang-up,
+// or the host's destroy() would wait out its whole linger period for a connection that is no longer there.
+static void dead_waiter(int port) {
+    int fd = socket(AF_INET, SOCK_STREAM, 0);
+    sockaddr_in sa{};
+    sa.sin_family = AF_INET; sa.sin_port = htons((uint16_t)port);
+    inet_pton(AF_INET, "127.0.0.1", &sa.sin_addr);
+    if (connect(fd, (sockaddr*)&sa, sizeof(sa)) == 0) {
+        const char key[] = "never-set";
+        uint8_t op = 2;                              // OP_GET
+        uint32_t n = sizeof(key) - 1;
+        (void)!send(fd, &op, 1, MSG_NOSIGNAL); (void)!send(fd, &n, 4, MSG_NOSIGNAL); (void)!send(fd, key, n, MSG_NOSIGNAL);
+        std::this_thread::sleep_for(std::chrono::milliseconds(50));
+    }
+    close(fd);
+}
+
 static void run_rank(int rank, int world, int port, int rounds) {
     ewdml_store* st = nullptr;
     int rc = ewdml_store_create(&st, "127.0.0.1", port, rank, world, 30.0);
     CHECK(rc == 0 && st, "create rc=%d", rc);
     std::vector<char> buf(1024);
+    if (rank == 1 || world == 1) dead_waiter(port);
     for (int r = 0; r < rounds; ++r) {
         std::string mine = value_of(rank, r);
         std::string key = "v/" + std::to_string(r) + "/" + std::to_string(rank);
@@ -84,8 +107,11 @@ static void run_rank(int rank, int world, int port, int rounds) {
     CHECK(rc == 0, "final barrier rc=%d", rc);
     // host leaves first; the others a little later, so its destroy() has live clients to wait for
     if (rank != 0) std::this_thread::sleep_for(std::chrono::milliseconds(20 * rank));
+    auto t0 = std::chrono::steady_clock::now();
     rc = ewdml_store_destroy(st);
+    double took = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
     CHECK(rc == 0, "destroy rc=%d", rc);
+    CHECK(took < 10.0, "destroy took %.1f s: the server waited for a connection that was gone", took);
 }
 
 int main(int argc, char** argv) {
