@@ -69,6 +69,8 @@ class NNTrainer:
         side = ckpt.load_sidecar(path)
         if side is not None:
             self.cur_step = int(side["step"])
+            if hasattr(self, "next_step"):
+                self.next_step = self.cur_step          # what the worker announces before it runs its first step
             if side.get("optimizer"):
                 try:
                     self.optimizer.load_state_dict(side["optimizer"])

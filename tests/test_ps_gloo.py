@@ -258,3 +258,17 @@ def test_asynchronous_parameter_server(tmp_path):
     assert max(server["staleness"]) >= 1 and min(server["staleness"]) == 0
     assert all(len(w["loss"]) == 8 and all(l == l for l in w["loss"]) for w in workers)
     assert workers[0]["loss"][-1] < workers[0]["loss"][0]
+
+
+def test_parameter_server_job_resumes_from_its_checkpoint(tmp_path):
+    """--resume on the distributed job: server and workers all pick the run up at the step recorded next to the checkpoint
+    (the weights, and the step counter that drives how many exchanges the server expects)."""
+    first = dict(method=3, max_steps=6, eval_freq=3, lr=0.05, synthetic_size=512, batch_size=32)
+    res = _launch_many(3, tmp_path, {"first": first,
+                                     "second": dict(first, max_steps=9, resume=os.path.join(str(tmp_path), "first", "model_step_"))})
+    a, b = res["first"], res["second"]
+    assert a[0]["steps"] == 6 and len(a[1]["loss"]) == 6
+    # checkpoints after steps 0 and 3 -> the sidecar says "next step 4" -> steps 4..8 remain
+    assert b[0]["steps"] == 5 and len(b[1]["loss"]) == 5 and len(b[2]["loss"]) == 5
+    assert b[1]["checksum"] == pytest.approx(b[2]["checksum"], rel=1e-9)
+    assert b[1]["loss"][0] < a[1]["loss"][0] - 0.05          # it did not start from fresh weights
