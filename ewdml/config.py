@@ -142,6 +142,13 @@ class TrainConfig:
             raise ValueError("--qsgd-levels must be in [1, 32768]")
         if not (0.0 < self.topk_ratio <= 1.0):
             raise ValueError("--topk-ratio must be in (0, 1]")
+        if self.overlap and self.error_feedback:
+            # the residual is folded into the gradient after backward, the overlapped exchange starts during it
+            raise ValueError("--overlap and --error-feedback cannot be combined")
+        if self.batch_size < 1 or self.max_steps < 0 or self.sync_period < 0:
+            raise ValueError("--batch-size must be >= 1, --max-steps and --sync-period >= 0")
+        if self.lr < 0 or not (0.0 <= self.momentum < 1.0):
+            raise ValueError("--lr must be >= 0 and --momentum in [0, 1)")
         return self
 
     def as_dict(self) -> Dict[str, Any]:

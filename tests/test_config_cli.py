@@ -141,3 +141,13 @@ def test_cloud_tool_plan_and_dry_run(tmp_path):
     import pytest
     with pytest.raises(ValueError):
         mod.resolve({"a": "%(b)s", "b": "%(a)sx"})
+
+
+def test_validate_rejects_contradictory_or_out_of_range_flags():
+    import pytest
+    from ewdml.config import TrainConfig
+    TrainConfig().validate()
+    for kw in (dict(overlap=True, error_feedback=True), dict(batch_size=0), dict(momentum=1.0), dict(lr=-0.1),
+               dict(topk_ratio=0.0), dict(qsgd_levels=0), dict(mode="sometimes"), dict(network="AlexNet")):
+        with pytest.raises(ValueError):
+            TrainConfig(**kw).validate()
