@@ -173,7 +173,8 @@ class DistributedWorker(NNTrainer):
                 if self.cur_step >= total:
                     done = True
                     break
-                if cfg.fault_inject_step == self.cur_step and cfg.fault_inject_rank == self.rank:
+                if (cfg.fault_inject_step == self.cur_step and cfg.fault_inject_rank == self.rank
+                        and os.environ.get("EWDML_RESTART_COUNT", "0") == "0"):       # once: not again after a supervised restart
                     logger.error("fault injection: rank %d exits at step %d", self.rank, self.cur_step)
                     os._exit(17)
                 if cfg.straggler_rank == self.rank and cfg.straggler_delay_s > 0:

@@ -68,6 +68,26 @@ def test_launcher_leaves_the_callers_other_children_alone():
     assert other.wait(timeout=10) == 7
 
 
+def test_launcher_restarts_a_failed_job_from_its_last_checkpoint(tmp_path):
+    """--max-restarts / --checkpoint-dir: a worker dies at step 5 (test hook), the watchdog tears the job down, the launcher
+    starts it again with --resume <newest checkpoint> and the job finishes its 8 steps with exit status 0."""
+    import socket
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
+    cmd = [sys.executable, "-m", "ewdml.cli.launch", "-np", "3", "--master-port", str(port), "--grace-seconds", "2",
+           "--max-restarts", "1", "--checkpoint-dir", str(tmp_path), "--",
+           sys.executable, os.path.join(ROOT, "distributed_nn.py"), "--network", "LeNet", "--dataset", "MNIST", "--data", "synthetic",
+           "--synthetic-size", "128", "--batch-size", "16", "--max-steps", "8", "--epochs", "10", "--eval-freq", "2",
+           f"--train-dir={tmp_path}/", "--method", "3", "--fault-inject-step", "5", "--fault-inject-rank", "1"]
+    out = subprocess.run(cmd, capture_output=True, text=True, timeout=300, cwd=ROOT)
+    assert out.returncode == 0, out.stderr[-2000:]
+    assert "rank 1 exited with status 17" in out.stderr
+    assert f"restart 1/1: resuming from {tmp_path}/model_step_" in out.stderr
+    assert "resumed from" in out.stderr and "at step 5" in out.stderr
+    from ewdml.cli.launch import latest_checkpoint, with_resume
+    assert latest_checkpoint(str(tmp_path)) == os.path.join(str(tmp_path), "model_step_")
+    assert with_resume(["x.py", "--resume", "old", "--lr", "1", "--resume=older"], "new") == ["x.py", "--lr", "1", "--resume", "new"]
+
+
 def test_info_tool_and_adasum_pair():
     out = subprocess.run([sys.executable, "-m", "ewdml.cli.info"], capture_output=True, text=True, timeout=120, cwd=ROOT)
     info = json.loads(out.stdout)
