@@ -23,9 +23,25 @@ def sparsify(tensor: torch.Tensor, compress_ratio: float) -> Tuple[torch.Tensor,
     flat = tensor.detach().reshape(-1)
     k = topk_count(flat.numel(), compress_ratio)
     mag = flat.abs()
-    # stable descending sort => ties broken by lowest index
-    order = torch.sort(mag, descending=True, stable=True).indices[:k]
-    order = torch.sort(order).values
+    n = mag.numel()
+    if k >= n:
+        order = torch.arange(n, device=flat.device)
+        return flat[order], order
+    # Selection instead of a full sort: the k-th largest magnitude is the threshold, everything above it is kept and the
+    # remaining slots go to the LOWEST indices among the elements equal to it -- the same set a stable descending sort
+    # would give, in O(n).
+    if bool(torch.isnan(mag).any()):
+        # NaNs order above every number and compare false with everything: keep the sort's treatment of them
+        order = torch.sort(mag, descending=True, stable=True).indices[:k]
+        order = torch.sort(order).values
+        return flat[order], order
+    thr = torch.kthvalue(mag, n - k + 1).values
+    keep = mag > thr
+    need = k - int(keep.sum())
+    if need > 0:
+        ties = torch.nonzero(mag == thr).flatten()[:need]
+        keep[ties] = True
+    order = torch.nonzero(keep).flatten()
     return flat[order], order
 
 
