@@ -151,3 +151,38 @@ def test_validate_rejects_contradictory_or_out_of_range_flags():
                dict(topk_ratio=0.0), dict(qsgd_levels=0), dict(mode="sometimes"), dict(network="AlexNet")):
         with pytest.raises(ValueError):
             TrainConfig(**kw).validate()
+
+
+def test_report_tool_reduces_metrics_files_to_the_reports_table(tmp_path, capsys):
+    """ewdml.cli.report: accuracy / communication vs compute minutes / MB per iteration / steps to a target accuracy
+    (Report.zip!main.tex:143-158) from --metrics-file records; the slowest worker defines the times."""
+    import json
+    from ewdml.cli import report
+
+    def write(path, mb, comm_ms, acc_at):
+        with open(path, "w") as f:
+            for step in range(20):
+                for rank, slow in ((1, 1.0), (2, 2.0)):
+                    f.write(json.dumps({"rank": rank, "step": step, "loss": 2.0 / (step + 1), "prec1": acc_at(step), "prec5": 100.0,
+                                        "bytes_sent": int(mb * 5e5), "bytes_recv": int(mb * 5e5), "compression_ratio": 4.0 / mb,
+                                        "ms_send": comm_ms * slow / 2, "ms_recv": comm_ms * slow / 2, "ms_compute": 60.0 * slow,
+                                        "time": 1000.0 + step * 0.2}) + "\n")
+            f.write('{"rank": 1, "step": 20, "lo')            # a record cut short by a killed job is skipped
+
+    dense, sparse = str(tmp_path / "dense.jsonl"), str(tmp_path / "sparse.jsonl")
+    write(dense, 4.0, 30.0, lambda s: min(100.0, 10.0 * s))
+    write(sparse, 0.5, 6.0, lambda s: min(100.0, 8.0 * s))
+    d = report.summarize(report.load(dense), tail=5, target=90.0)
+    s = report.summarize(report.load(sparse), tail=5, target=90.0)
+    assert d["workers"] == 2 and d["steps"] == 20 and d["top1_final"] == 100.0
+    assert d["mb_per_iteration"] == pytest.approx(4.0) and s["mb_per_iteration"] == pytest.approx(0.5)
+    assert d["comm_minutes"] == pytest.approx(20 * 60.0 / 60e3) and d["compute_minutes"] == pytest.approx(20 * 120.0 / 60e3)   # rank 2
+    assert d["comm_fraction"] == pytest.approx(60.0 / 180.0)
+    assert d["wall_minutes"] == pytest.approx(19 * 0.2 / 60.0)
+    assert d["steps_to_target"] == 12 and s["steps_to_target"] == 14        # first window of 5 whose mean reaches 90 %
+    assert report.main([f"dense={dense}", f"sparse={sparse}", "--tail", "5", "--target", "90"]) == 0
+    out = capsys.readouterr().out
+    assert "dense" in out and "sparse" in out and "8.0x" in out and "steps to 90 %" in out
+    assert report.main([dense, "--json"]) == 0
+    assert json.loads(capsys.readouterr().out)[0]["run"] == dense
+    assert report.summarize([]) == {"steps": 0, "workers": 0}
