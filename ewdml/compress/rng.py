@@ -37,21 +37,45 @@ def philox4x32(c0, c1, c2, c3, k0, k1, rounds: int = 10):
     return c0, c1, c2, c3
 
 
-def uniform_for_indices(index: torch.Tensor, seed: int, step: int, stream: int = 0) -> torch.Tensor:
-    """u in [0,1) (float32, 24-bit) for each global element index (any int tensor)."""
-    idx = index.detach().cpu().numpy().astype(np.uint64)
-    ctr = idx >> np.uint64(2)
-    lane = (idx & np.uint64(3)).astype(np.int64)
+def _uniform_of_counters(ctr: np.ndarray, seed: int, step: int, stream: int) -> np.ndarray:
+    """The four 24-bit uniforms of each 64-bit counter: float32 array of shape (len(ctr), 4)."""
     zeros = np.zeros_like(ctr)
     r = philox4x32(ctr & _MASK, zeros + np.uint64(stream & 0xFFFFFFFF), ctr >> np.uint64(32), zeros,
                    seed & 0xFFFFFFFF, step & 0xFFFFFFFF)
-    stacked = np.stack(r, axis=-1)
-    x = np.take_along_axis(stacked, lane[..., None], axis=-1)[..., 0]
-    u = (x >> np.uint64(8)).astype(np.float32) * np.float32(2.0 ** -24)
-    return torch.from_numpy(u)
+    x = np.stack(r, axis=-1)
+    return (x >> np.uint64(8)).astype(np.float32) * np.float32(2.0 ** -24)
+
+
+def uniform_for_indices(index: torch.Tensor, seed: int, step: int, stream: int = 0) -> torch.Tensor:
+    """u in [0,1) (float32, 24-bit) for each global element index (any int tensor).  Element i uses lane i & 3 of the
+    Philox block with counter i >> 2, so neighbouring indices share a block: each distinct counter is evaluated once."""
+    idx = index.detach().cpu().numpy().astype(np.uint64)
+    shape = idx.shape
+    idx = idx.reshape(-1)
+    if idx.size == 0:
+        return torch.zeros(shape, dtype=torch.float32)
+    ctr = idx >> np.uint64(2)
+    lane = (idx & np.uint64(3)).astype(np.int64)
+    if idx.size > 1 and bool(np.all(ctr[1:] >= ctr[:-1])):          # sorted indices (top-k lists, ranges): one linear pass
+        first = np.empty(ctr.size, dtype=bool)
+        first[0] = True
+        np.not_equal(ctr[1:], ctr[:-1], out=first[1:])
+        uniq = ctr[first]
+        inverse = np.cumsum(first) - 1
+    else:
+        uniq, inverse = np.unique(ctr, return_inverse=True)
+    u4 = _uniform_of_counters(uniq, seed, step, stream)
+    u = u4[inverse, lane]
+    return torch.from_numpy(np.ascontiguousarray(u)).view(shape)
 
 
 def uniform_like(t: torch.Tensor, seed: int, step: int, stream: int = 0, offset: int = 0) -> torch.Tensor:
-    """Uniforms for a tensor whose first element has global index ``offset``."""
-    idx = torch.arange(offset, offset + t.numel(), dtype=torch.int64)
-    return uniform_for_indices(idx, seed, step, stream).view(t.shape)
+    """Uniforms for a tensor whose first element has global index ``offset``: the blocks of the counters
+    offset >> 2 .. (offset + n - 1) >> 2, laid end to end and cut to the range."""
+    n = t.numel()
+    if n == 0:
+        return torch.zeros(t.shape, dtype=torch.float32)
+    c0, c1 = offset >> 2, (offset + n - 1) >> 2
+    u4 = _uniform_of_counters(np.arange(c0, c1 + 1, dtype=np.uint64), seed, step, stream)
+    lead = offset & 3
+    return torch.from_numpy(np.ascontiguousarray(u4.reshape(-1)[lead:lead + n])).view(t.shape)
