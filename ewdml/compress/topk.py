@@ -20,6 +20,8 @@ def topk_count(numel: int, ratio: float) -> int:
 
 
 def sparsify(tensor: torch.Tensor, compress_ratio: float) -> Tuple[torch.Tensor, torch.Tensor]:
+    """(values, flat indices) of the k largest magnitudes; the indices come back in ASCENDING order (the host wire format
+    stores them that way and relies on it)."""
     flat = tensor.detach().reshape(-1)
     k = topk_count(flat.numel(), compress_ratio)
     mag = flat.abs()

@@ -32,7 +32,7 @@ import numpy as np
 import torch
 
 from ..compress.qsgd import qsgd_dequantize, qsgd_quantize
-from ..compress.rng import uniform_for_indices
+from ..compress.rng import uniform_for_indices, uniform_like
 from ..compress.topk import sparsify, topk_count
 from .flat import Segment
 
@@ -161,24 +161,22 @@ class HostCodec:
             if c == "none":
                 dst.copy_(g.contiguous().view(torch.uint8))
             elif c == "qsgd":
-                idx = torch.arange(seg.offset, seg.offset + seg.numel)
-                q, norm = qsgd_quantize(g, self.s, self._uniform(idx, step), norm=self._norm(g))
+                u = uniform_like(g, self.seed, step, stream=self.rank, offset=seg.offset)
+                q, norm = qsgd_quantize(g, self.s, u, norm=self._norm(g))
                 dst[:4].copy_(norm.view(torch.uint8))
                 dst[4:].copy_(_pack_levels(q, self.s))
             elif c == "topk":
-                vals, idx = sparsify(g, self.ratio)
+                vals, idx = sparsify(g, self.ratio)          # indices come back ascending
                 k = vals.numel()
-                idx, order = torch.sort(idx)
-                dst[:4 * k].copy_(vals[order].contiguous().view(torch.uint8))
+                dst[:4 * k].copy_(vals.contiguous().view(torch.uint8))
                 dst[4 * k:].copy_(_pack_index(idx, seg.numel, k))
             else:  # topk-qsgd
                 vals, idx = sparsify(g, self.ratio)
                 k = vals.numel()
                 norm = self._norm(vals)
                 if norm is None:
-                    norm = vals.norm()                  # before sorting: the same summation order as the unsorted oracle
-                idx, order = torch.sort(idx)
-                q, norm = qsgd_quantize(vals[order], self.s, self._uniform(idx + seg.offset, step), norm=norm)
+                    norm = vals.norm()
+                q, norm = qsgd_quantize(vals, self.s, self._uniform(idx + seg.offset, step), norm=norm)      # idx is ascending
                 lb = _levels_nbytes(k, self.s)
                 dst[:4].copy_(norm.view(torch.uint8))
                 dst[4:4 + lb].copy_(_pack_levels(q, self.s))
