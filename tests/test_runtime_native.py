@@ -221,3 +221,30 @@ def test_store_under_sanitizers(tmp_path, sanitizer):
     assert run.returncode == 0, (run.stdout + run.stderr)[-3000:]
     assert "store_stress ok" in run.stdout
     assert "Sanitizer" not in run.stderr, run.stderr[-3000:]
+
+
+def test_c_abi_header_library_and_binding_agree():
+    """Every function declared in include/ewdml.h is exported by libewdml.so, everything the library exports beyond that is
+    one of the two internal helpers, and every function the ctypes binding names exists (the C ABI is the public surface
+    for non-Python users)."""
+    import re
+    import shutil
+    import subprocess
+    from ewdml.runtime import lib as L
+    if shutil.which("nm") is None:
+        pytest.skip("no nm")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    L.load()
+    so = os.path.join(root, "ewdml", "_C", "libewdml.so")
+    header = open(os.path.join(root, "include", "ewdml.h")).read()
+    header = re.sub(r"/\*.*?\*/", "", header, flags=re.S)
+    header = re.sub(r"//[^\n]*", "", header)
+    declared = set(re.findall(r"\b(ewdml_[a-z0-9_]+)\s*\(", header))
+    out = subprocess.run(["nm", "-D", "--defined-only", so], capture_output=True, text=True, check=True).stdout
+    exported = {ln.split()[-1] for ln in out.splitlines() if ln.split() and ln.split()[-1].startswith("ewdml_")}
+    assert declared - exported == set(), sorted(declared - exported)
+    assert exported - declared <= {"ewdml_device_error_word", "ewdml_spin_limit"}, sorted(exported - declared)
+    assert len(declared) > 90
+    src = open(os.path.join(root, "ewdml", "runtime", "lib.py")).read()
+    bound = set(re.findall(r"\"(ewdml_[a-z0-9_]+)\"\s*:", src))
+    assert bound and bound <= exported, sorted(bound - exported)
