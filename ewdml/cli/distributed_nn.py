@@ -66,6 +66,10 @@ def main(argv=None):
     if ps_mode and world_size < 2:
         raise SystemExit("--exchange ps needs WORLD_SIZE >= 2 (rank 0 is the server)")
     n_workers = world_size - 1 if ps_mode else world_size
+    if backend != "gloo" and rank == 0 and (cfg.mode != "normal" or (ps_mode and 0 < cfg.num_aggregate < n_workers)):
+        # backup workers, the straggler cut-off and the asynchronous server live in the gloo parameter server only
+        logger.warning("--mode %s / --num-aggregate %d act on --backend gloo only: the %s backend waits for all %d workers "
+                       "every step", cfg.mode, cfg.num_aggregate, backend, n_workers)
     shard = (rank - 1) if ps_mode else rank
     train_set, _ = build_datasets(cfg)
     total = planned_steps(cfg, len(train_set), n_workers)
